@@ -1,0 +1,167 @@
+/* vlgb200.h — C ABI of libvlgb200.so, the B200 (sm_100a) variable-length-gap matcher.
+ *
+ * The reference (olydis/vlg_matching, an sdsl-lite fork) has no FFI boundary: its callers bind at
+ * compile time to C++ templates.  These entry points are what a binding for that path would call;
+ * each one names the reference interface it replaces (paths relative to /root/reference).
+ * The C++ header vlg_matching_b200/csrc/host/vlg_b200.hpp wraps this ABI behind the reference's own
+ * names (vlg_index / construct / locate / count and the benchmark's 7-method index interface);
+ * INTEGRATION.md shows the binding a maintainer would add.
+ *
+ * Conventions
+ *  - every call returns VLGB_OK (0) or a negative code and never throws across the ABI;
+ *    vlgb_last_error() gives the text for the calling thread;
+ *  - plain pointers and sizes only; inputs are HOST memory owned by the caller unless a name says
+ *    "_device"; outputs are owned by the library until the matching *_free call;
+ *  - all searching runs in CUDA kernels.  There is no CPU fallback: without a usable GPU every
+ *    compute entry point fails with VLGB_ERR_CUDA.
+ *  - positions are 0-based byte offsets into the WHOLE text (uint64), ascending per query.
+ */
+#ifndef VLGB200_H
+#define VLGB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VLGB_ABI_VERSION 1
+
+enum vlgb_status {
+    VLGB_OK = 0,
+    VLGB_ERR_CUDA = -1,       /* no device / CUDA runtime failure */
+    VLGB_ERR_ARG = -2,        /* null pointer, bad size, bad handle */
+    VLGB_ERR_LAZY = -3,       /* std::runtime_error "invalid gap description: expected '?' (lazy semantics)"  include/sdsl/vlg_index.hpp:97-99 */
+    VLGB_ERR_MINMAX = -4,     /* std::runtime_error "invalid gap description: min-gap > max-gap"              include/sdsl/vlg_index.hpp:92-94 */
+    VLGB_ERR_NUMBER = -5,     /* std::stoull failure inside the gap                                            include/sdsl/vlg_index.hpp:90-91 */
+    VLGB_ERR_EMPTY_SUB = -6,  /* FENCED: empty subpattern (reference matches every suffix)          */
+    VLGB_ERR_ZERO_SYMBOL = -7,/* std::logic_error "... contains zero symbol."                                  include/sdsl/construct.hpp:35-45 */
+    VLGB_ERR_NOMEM = -8,
+    VLGB_ERR_IO = -9,
+    VLGB_ERR_TOO_LARGE = -10, /* a query span or shard exceeds what one device segment can hold */
+    VLGB_ERR_RERUN = -11      /* vlgb_result_fixup: orbit did not merge inside the retained window */
+};
+
+typedef struct vlgb_index vlgb_index;   /* a text shard resident in HBM  — replaces sdsl::vlg_index<> (vlg_index.hpp:116-199) */
+typedef struct vlgb_result vlgb_result; /* the matches of one batch       — replaces container<vlg_iterator> (vlg_index.hpp:395-401) */
+
+/* ---- device ------------------------------------------------------------------------------- */
+
+/* Number of CUDA devices visible to this process (0 without a GPU; never an error). */
+int vlgb_device_count(void);
+/* Bind the calling process to one device (one process per GPU).  Idempotent. */
+int vlgb_init(int device);
+const char* vlgb_last_error(void);
+const char* vlgb_version(void);
+
+/* ---- query parsing  (replaces gapped_pattern_query ctor, vlg_index.hpp:54-105, and the benchmark's
+ *      gapped_pattern ctor, benchmark/gapped-matching/include/utils.hpp:19-71) ---------------------- */
+
+#define VLGB_SYNTAX_LIBRARY   0  /* P1.{a,b}?P2 ... : lazy '?' mandatory */
+#define VLGB_SYNTAX_BENCHMARK 1  /* P1.{a,b}P2  ... : no '?'             */
+
+/* A batch of parsed queries in CSR form.
+ *   query q owns subpatterns s in [sub_off[q], sub_off[q+1])
+ *   subpattern s owns bytes  pat_bytes[pat_off[s] .. pat_off[s+1])   (literal bytes, no escapes)
+ *   gap_min[s], gap_max[s]   RAW gap {a,b} FOLLOWING subpattern s (ignored for a query's last one);
+ *                            the library forms the start-to-start bounds a+|P_s|, b+|P_s| exactly
+ *                            as vlg_index.hpp:95 does. */
+typedef struct {
+    uint32_t n_queries;
+    const uint32_t* sub_off;  /* n_queries+1 */
+    const uint64_t* pat_off;  /* n_subs+1    */
+    const uint8_t* pat_bytes;
+    const uint64_t* gap_min;  /* n_subs */
+    const uint64_t* gap_max;  /* n_subs */
+} vlgb_batch;
+
+/* Parse ONE query string into a one-query batch owned by the library (free with vlgb_batch_free).
+ * Returns VLGB_OK or VLGB_ERR_LAZY / _MINMAX / _NUMBER (same conditions, same order of checks as the
+ * reference parser).  Empty subpatterns parse fine and are fenced at search time. */
+int vlgb_parse_query(const char* str, size_t len, int syntax, vlgb_batch** out);
+void vlgb_batch_free(vlgb_batch* b);
+
+/* ---- index  (replaces construct(vlg_index&, file, cfg, num_bytes), vlg_index.hpp:375-392; the
+ *      benchmark's index_wcsearch3(collection&), index_wcsearch3.hpp:365-369; serialize/load,
+ *      vlg_index.hpp:183-198) ---------------------------------------------------------------------- */
+
+/* Copy a text shard to the device.
+ *   text[0 .. n)      host bytes of the shard INCLUDING its right halo
+ *   global_offset     position of text[0] in the whole text
+ *   owned_len         text[0 .. owned_len) is owned by this shard (matches whose FIRST subpattern
+ *                     starts there are reported by it); text[owned_len .. n) is halo, read only to
+ *                     complete owned starts.  Whole text on one GPU: global_offset=0, owned_len=n.
+ *   total_len         length of the whole text (tells the shard whether its halo is truncated)
+ * Fails with VLGB_ERR_ZERO_SYMBOL if a 0 byte is present (construct.hpp:35-45). */
+int vlgb_index_build(const uint8_t* text, uint64_t n, uint64_t global_offset, uint64_t owned_len,
+                     uint64_t total_len, vlgb_index** out);
+/* Same, from a raw byte file (the `construct(idx, file, 1)` call of examples/vlg_matching.cpp:34). */
+int vlgb_index_build_file(const char* path, vlgb_index** out);
+/* Same, the text is already in device memory (device pointer stays owned by the caller and must
+ * outlive the index; >= n+64 bytes must be readable). */
+int vlgb_index_build_device(const uint8_t* text_device, uint64_t n, uint64_t global_offset, uint64_t owned_len,
+                            uint64_t total_len, vlgb_index** out);
+int vlgb_index_save(const vlgb_index* idx, const char* path);
+int vlgb_index_load(const char* path, vlgb_index** out);
+uint64_t vlgb_index_size(const vlgb_index* idx);          /* n (shard bytes incl. halo) */
+/* Copy text[pos .. pos+len) of the shard back to the host (vlg_index::text, vlg_index.hpp:141). */
+int vlgb_index_extract(const vlgb_index* idx, uint64_t pos, uint64_t len, uint8_t* out);
+void vlgb_index_free(vlgb_index* idx);
+
+/* ---- search  (replaces vlg_iterator ctor/next/operator++, vlg_index.hpp:227-356; locate/count,
+ *      vlg_index.hpp:395-411; index_wcsearch3::search/info, index_wcsearch3.hpp:388-423) ---------- */
+
+#define VLGB_WANT_COUNT  0u  /* counts only            (count(),           vlg_index.hpp:404-411)        */
+#define VLGB_WANT_STARTS 1u  /* + match starts         (search().positions, index_wcsearch3.hpp:418-420) */
+#define VLGB_WANT_TUPLES 2u  /* + all k positions/match (it[i],             vlg_index.hpp:337-340)        */
+#define VLGB_KEEP_ON_DEVICE 16u /* do not copy starts/tuples to the host (counts still are)            */
+
+/* Run a whole batch.  entry_cursor (nullable, n_queries entries, whole-text positions): the
+ * non-overlap cursor each query enters this shard with (pull_forward state, vlg_index.hpp:253-264);
+ * NULL means 0 = "search from the beginning".  Queries that hit a fence get a per-query status and
+ * zero matches; the call itself still returns VLGB_OK. */
+int vlgb_search_batch(const vlgb_index* idx, const vlgb_batch* batch, const uint64_t* entry_cursor,
+                      uint32_t want, vlgb_result** out);
+
+uint32_t vlgb_result_queries(const vlgb_result* r);
+int32_t vlgb_result_status(const vlgb_result* r, uint32_t q);      /* VLGB_OK or a fence code        */
+uint64_t vlgb_result_count(const vlgb_result* r, uint32_t q);      /* number of matches of query q    */
+uint64_t vlgb_result_total(const vlgb_result* r);                  /* sum over the batch              */
+const uint64_t* vlgb_result_counts(const vlgb_result* r);          /* n_queries counts                */
+const uint64_t* vlgb_result_starts(const vlgb_result* r, uint32_t q);  /* host, ascending; NULL if not wanted */
+const uint64_t* vlgb_result_tuples(const vlgb_result* r, uint32_t q);  /* host, k(q) per match            */
+/* Non-overlap cursor each query leaves this shard with (= entry cursor of the next shard). */
+const uint64_t* vlgb_result_exit_cursors(const vlgb_result* r);
+/* Sum over subpatterns of the occurrence-list sizes (what index_wcsearch3::info prints,
+ * index_wcsearch3.hpp:388-397: the total SA-range size). */
+uint64_t vlgb_result_occurrences(const vlgb_result* r, uint32_t q);
+/* Multi-shard exactness: re-enter the shard with the true cursors gathered from the left
+ * neighbour.  Only queries whose cursor lies beyond their first selected start change.  Updates
+ * counts / starts / tuples / exit cursors in place; *n_changed = number of queries that changed. */
+int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, uint32_t* n_changed);
+void vlgb_result_free(vlgb_result* r);
+
+/* ---- measurement hooks (bench.py / profiles; no effect on results) ------------------------------ */
+
+/* Per-stage device time (CUDA events on the library's stream) and algorithmic byte counts of the
+ * last vlgb_search_batch on this thread.  stage names: see vlgb_stage_name(). */
+#define VLGB_MAX_STAGES 16
+typedef struct {
+    uint32_t n_stages;
+    float ms[VLGB_MAX_STAGES];          /* device time per stage, summed over launches */
+    uint64_t bytes[VLGB_MAX_STAGES];    /* algorithmic bytes per stage   */
+    uint32_t launches[VLGB_MAX_STAGES]; /* kernel launches per stage                    */
+    uint64_t h2d_bytes, d2h_bytes;
+    uint32_t distinct_patterns, scan_passes, segments, query_chunks;
+    uint64_t total_occurrences;         /* sum of list sizes of the distinct patterns   */
+    uint64_t join_slots;                /* sum over (query, level) of |L_i|             */
+} vlgb_stats;
+int vlgb_last_stats(vlgb_stats* out);
+const char* vlgb_stage_name(uint32_t stage);
+/* Tunables (0 = keep default): bytes per device segment, device memory budget for join state. */
+int vlgb_set_tuning(uint64_t segment_bytes, uint64_t join_budget_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VLGB200_H */

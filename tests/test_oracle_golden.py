@@ -1,0 +1,85 @@
+"""CPU: the oracle (oracle/vlg_oracle.c) against vectors generated from the UNMODIFIED reference
+(tests/golden/*.json, made by tests/golden/make_golden.py from oracle/_ref/ref_vlg) and, when the
+reference binary is present (build container), against the reference run live."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as O
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def load(name):
+    with open(os.path.join(HERE, "golden", name)) as f:
+        return json.load(f)["vectors"]
+
+
+def check_vectors(vectors):
+    n = 0
+    for v in vectors:
+        text = np.frombuffer(v["text"].encode("latin-1"), dtype=np.uint8)
+        qs = [c["query"] for c in v["cases"]]
+        res = O.search(text, qs, want_tuples=True)
+        for c, (st, starts, tup) in zip(v["cases"], res):
+            if "error" in c:
+                want = -1 if "lazy" in c["error"] else (-2 if "min-gap" in c["error"] else -3)
+                assert st == want, (v["text"], c, st)
+                continue
+            rc, subs, _ = O.parse(c["query"], 0)
+            if any(len(s) == 0 for s in subs):
+                assert st == -4  # fenced: the reference matches every suffix here
+                continue
+            assert st == 0
+            assert len(starts) == c["count"], (v["text"], c["query"])
+            assert tup.tolist() == c["tuples"], (v["text"], c["query"])
+            n += 1
+    return n
+
+
+def test_appendix_b():
+    assert check_vectors(load("appendix_b.json")) >= 40
+
+
+def test_random_reference_vectors():
+    assert check_vectors(load("random_ref.json")) >= 1500
+
+
+def test_parser_benchmark_syntax():
+    # benchmark parser: no '?', raw gaps (benchmark/gapped-matching/include/utils.hpp:40-66)
+    rc, subs, gaps = O.parse("the.{10,100}and", 1)
+    assert rc == 0 and subs == [b"the", b"and"] and gaps == [(10, 100)]
+    rc, subs, gaps = O.parse("the.{10,100}?and", 1)
+    assert rc == 0 and subs == [b"the", b"?and"]
+    rc, subs, gaps = O.parse("the.{10,100}and", 0)
+    assert rc == -1
+
+
+@pytest.mark.skipif(not O.have_reference(), reason="reference binary not built (GPU box)")
+def test_live_reference_differential():
+    rng = random.Random(7)
+    for _ in range(6):
+        sigma = rng.choice([2, 3, 4, 26])
+        n = rng.choice([50, 300, 3000])
+        alpha = "abcdefghijklmnopqrstuvwxyz"[:sigma]
+        text = "".join(rng.choice(alpha) for _ in range(n))
+        qs = []
+        for _ in range(60):
+            k = rng.choice([1, 2, 2, 3, 4])
+            parts = []
+            for i in range(k):
+                m = rng.choice([1, 2, 3, 5])
+                o = rng.randrange(0, n - m + 1)
+                parts.append(text[o:o + m])
+                if i + 1 < k:
+                    a = rng.choice([0, 1, 3, 10, 50])
+                    parts.append(".{%d,%d}?" % (a, a + rng.choice([0, 2, 10, 100])))
+            qs.append("".join(parts))
+        ref = O.reference_locate(text.encode(), qs)
+        got = O.search(np.frombuffer(text.encode(), dtype=np.uint8), qs, want_tuples=True)
+        for q, r, (st, starts, tup) in zip(qs, ref, got):
+            assert r[0] == "Q" and st == 0
+            assert [list(t) for t in r[2]] == tup.tolist(), (text, q)

@@ -1,0 +1,230 @@
+// common.cuh — error handling, per-thread context (stream, arena, stage timers) for libvlgb200.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/vlgb200.h"
+
+namespace vlgb {
+
+// ---------------------------------------------------------------------------------------------
+// error state (thread local; never throws across the ABI)
+// ---------------------------------------------------------------------------------------------
+inline std::string& last_error()
+{
+    static thread_local std::string e;
+    return e;
+}
+
+inline int fail(int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    last_error() = buf;
+    return code;
+}
+
+struct CudaError {
+    cudaError_t e;
+    const char* file;
+    int line;
+};
+
+#define VLGB_CUDA(call)                                                        \
+    do {                                                                       \
+        cudaError_t e__ = (call);                                              \
+        if (e__ != cudaSuccess) throw ::vlgb::CudaError{e__, __FILE__, __LINE__}; \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// stages (vlgb_stats)
+// ---------------------------------------------------------------------------------------------
+enum Stage : uint32_t {
+    ST_SCAN_COUNT = 0,  // text scan, pass 1: per-(chunk, pattern) occurrence counts
+    ST_SCAN_OFFSETS,    // count-matrix column scans
+    ST_SCAN_FILL,       // text scan, pass 2: write sorted occurrence lists
+    ST_JOIN_PROBE,      // gap join: lower_bound of x+lo in the right-hand viable list
+    ST_JOIN_COMPACT,    // gap join: compaction of viable elements (+ prefix sums)
+    ST_SELECT_SUCC,     // non-overlap successor of every viable start
+    ST_SELECT_TILE,     // in-tile pointer doubling
+    ST_SELECT_WALK,     // tile-to-tile walk + marking
+    ST_EMIT,            // compaction of selected matches + tuple chain resolve
+    ST_PREFIX,          // stand-alone device prefix sums
+    ST_COUNT
+};
+
+inline const char* stage_name(uint32_t s)
+{
+    static const char* names[ST_COUNT] = {"scan_count", "scan_offsets", "scan_fill", "join_probe", "join_compact",
+                                          "select_succ", "select_tile", "select_walk", "emit", "prefix"};
+    return s < ST_COUNT ? names[s] : "";
+}
+
+// ---------------------------------------------------------------------------------------------
+// device arena: one growing allocation per purpose, reused across calls (no cudaMalloc in steady state)
+// ---------------------------------------------------------------------------------------------
+struct DeviceBuffer {
+    void* p = nullptr;
+    size_t cap = 0;
+    void* get(size_t bytes)
+    {
+        if (bytes > cap) {
+            if (p) cudaFree(p);
+            p = nullptr;
+            size_t want = bytes + bytes / 8 + 256;
+            cudaError_t e = cudaMalloc(&p, want);
+            if (e != cudaSuccess) {
+                p = nullptr;
+                cap = 0;
+                throw CudaError{e, __FILE__, __LINE__};
+            }
+            cap = want;
+        }
+        return p;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// Bump allocator over one DeviceBuffer.
+struct Arena {
+    DeviceBuffer buf;
+    size_t used = 0;
+    size_t planned = 0;
+    void reserve(size_t bytes)
+    {
+        buf.get(bytes);
+        used = 0;
+    }
+    template <class T>
+    T* take(size_t n)
+    {
+        size_t bytes = (n * sizeof(T) + 255) & ~size_t(255);
+        if (used + bytes > buf.cap) throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
+        T* r = reinterpret_cast<T*>(static_cast<char*>(buf.p) + used);
+        used += bytes;
+        return r;
+    }
+    static size_t padded(size_t n, size_t elem) { return (n * elem + 255) & ~size_t(255); }
+};
+
+struct PinnedBuffer {
+    void* p = nullptr;
+    size_t cap = 0;
+    void* get(size_t bytes)
+    {
+        if (bytes > cap) {
+            if (p) cudaFreeHost(p);
+            p = nullptr;
+            size_t want = bytes + bytes / 8 + 256;
+            cudaError_t e = cudaMallocHost(&p, want);
+            if (e != cudaSuccess) {
+                p = nullptr;
+                cap = 0;
+                throw CudaError{e, __FILE__, __LINE__};
+            }
+            cap = want;
+        }
+        return p;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// per-thread context
+// ---------------------------------------------------------------------------------------------
+struct Context {
+    int device = -1;
+    bool ready = false;
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    Arena scan_arena;    // count matrix, pattern tables
+    Arena list_arena;    // occurrence lists of the current segment
+    Arena join_arena;    // per-chunk join / selection state
+    PinnedBuffer pinned; // small host staging
+    // timers
+    cudaEvent_t ev[2 * 64] = {};
+    bool ev_ready = false;
+    struct Span {
+        uint32_t stage;
+        int e0, e1;
+    };
+    std::vector<Span> spans;
+    int ev_used = 0;
+    vlgb_stats stats;
+    uint64_t segment_bytes = 0;  // 0 = default
+    uint64_t join_budget = 0;    // 0 = default
+
+    void begin(uint32_t stage)
+    {
+        if (!ev_ready) {
+            for (auto& e : ev) cudaEventCreate(&e);
+            ev_ready = true;
+        }
+        if (ev_used + 2 > 128) flush_timers();
+        cudaEventRecord(ev[ev_used], stream);
+        spans.push_back({stage, ev_used, ev_used + 1});
+        ev_used += 2;
+    }
+    void end(uint32_t stage, uint32_t launches, uint64_t bytes)
+    {
+        cudaEventRecord(ev[spans.back().e1], stream);
+        stats.launches[stage] += launches;
+        stats.bytes[stage] += bytes;
+    }
+    void flush_timers()
+    {
+        if (spans.empty()) return;
+        cudaStreamSynchronize(stream);
+        for (auto& s : spans) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, ev[s.e0], ev[s.e1]);
+            stats.ms[s.stage] += ms;
+        }
+        spans.clear();
+        ev_used = 0;
+    }
+};
+
+inline Context& ctx()
+{
+    static thread_local Context c;
+    return c;
+}
+
+inline void ensure_ready()
+{
+    Context& c = ctx();
+    if (c.ready) return;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) throw CudaError{e == cudaSuccess ? cudaErrorNoDevice : e, __FILE__, __LINE__};
+    if (c.device < 0) c.device = 0;
+    VLGB_CUDA(cudaSetDevice(c.device));
+    VLGB_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    cudaDeviceProp prop;
+    VLGB_CUDA(cudaGetDeviceProperties(&prop, c.device));
+    c.sm_count = prop.multiProcessorCount;
+    c.ready = true;
+}
+
+__host__ __device__ inline uint64_t sat_add64(uint64_t a, uint64_t b)
+{
+    return a > ~uint64_t(0) - b ? ~uint64_t(0) : a + b;
+}
+
+constexpr uint32_t NONE32 = 0xFFFFFFFFu;
+
+}  // namespace vlgb
