@@ -38,8 +38,8 @@ enum vlgb_status {
     VLGB_ERR_ZERO_SYMBOL = -7,/* std::logic_error "... contains zero symbol."                                  include/sdsl/construct.hpp:35-45 */
     VLGB_ERR_NOMEM = -8,
     VLGB_ERR_IO = -9,
-    VLGB_ERR_TOO_LARGE = -10, /* a query span or shard exceeds what one device segment can hold */
-    VLGB_ERR_RERUN = -11      /* vlgb_result_fixup: orbit did not merge inside the retained window */
+    VLGB_ERR_TOO_LARGE = -10  /* shard > 4 GiB - 4 KiB, query with > 64 subpatterns, or a query span that
+                                 does not fit the shard's halo */
 };
 
 typedef struct vlgb_index vlgb_index;   /* a text shard resident in HBM  — replaces sdsl::vlg_index<> (vlg_index.hpp:116-199) */
@@ -132,12 +132,15 @@ const uint64_t* vlgb_result_starts(const vlgb_result* r, uint32_t q);  /* host, 
 const uint64_t* vlgb_result_tuples(const vlgb_result* r, uint32_t q);  /* host, k(q) per match            */
 /* Non-overlap cursor each query leaves this shard with (= entry cursor of the next shard). */
 const uint64_t* vlgb_result_exit_cursors(const vlgb_result* r);
+/* Whole-text position of the first reported match of every query (~0 if none). */
+const uint64_t* vlgb_result_first_starts(const vlgb_result* r);
 /* Sum over subpatterns of the occurrence-list sizes (what index_wcsearch3::info prints,
  * index_wcsearch3.hpp:388-397: the total SA-range size). */
 uint64_t vlgb_result_occurrences(const vlgb_result* r, uint32_t q);
 /* Multi-shard exactness: re-enter the shard with the true cursors gathered from the left
- * neighbour.  Only queries whose cursor lies beyond their first selected start change.  Updates
- * counts / starts / tuples / exit cursors in place; *n_changed = number of queries that changed. */
+ * neighbour.  Only queries whose cursor lies beyond their first reported start can change; those are
+ * searched again on the device.  Updates counts / starts / tuples / exit cursors in place;
+ * *n_changed = number of queries searched again.  The index must still be alive. */
 int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, uint32_t* n_changed);
 void vlgb_result_free(vlgb_result* r);
 
@@ -158,6 +161,9 @@ typedef struct {
 } vlgb_stats;
 int vlgb_last_stats(vlgb_stats* out);
 const char* vlgb_stage_name(uint32_t stage);
+/* The CUDA stream (cudaStream_t) every kernel of the calling thread is launched on, for callers that
+ * bracket calls with their own CUDA events.  NULL before the first device call. */
+void* vlgb_stream_handle(void);
 /* Tunables (0 = keep default): bytes per device segment, device memory budget for join state. */
 int vlgb_set_tuning(uint64_t segment_bytes, uint64_t join_budget_bytes);
 

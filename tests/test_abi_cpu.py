@@ -1,0 +1,74 @@
+"""CPU: the C-ABI library loads and exports every symbol include/vlgb200.h declares; host-only entry
+points (parser, argument checks) behave like the reference parser.  No compute call is made."""
+import os
+import re
+
+import pytest
+
+from vlg_matching_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "vlgb200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(vlgb_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_every_declared_symbol_is_exported():
+    decl = declared_symbols()
+    assert len(decl) >= 28
+    for s in decl:
+        assert hasattr(capi.lib, s), s
+    assert sorted(capi.SYMBOLS) == decl
+
+
+def test_parser_matches_reference_rules():
+    # vlg_index.hpp:54-105
+    subs, gaps = capi.parse_query("ac.{2,5}?a.{4,8}?b")
+    assert subs == [b"ac", b"a", b"b"] and gaps == [(2, 5), (4, 8)]
+    for q, code in [("a.{1,2}b", capi.ERR_LAZY), ("a.{3,2}?b", capi.ERR_MINMAX), ("a.{x,2}?b", capi.ERR_NUMBER),
+                    ("a.{3,2}b", capi.ERR_MINMAX)]:  # min/max is checked before the '?' (vlg_index.hpp:92-99)
+        with pytest.raises(capi.VlgbError) as e:
+            capi.parse_query(q)
+        assert e.value.code == code, q
+    # benchmark parser (utils.hpp:40-66): no '?', a '?' belongs to the next subpattern
+    subs, gaps = capi.parse_query("the.{10,100}?and", capi.SYNTAX_BENCHMARK)
+    assert subs == [b"the", b"?and"] and gaps == [(10, 100)]
+    subs, gaps = capi.parse_query("plain")
+    assert subs == [b"plain"] and gaps == []
+
+
+def test_parser_agrees_with_oracle_parser():
+    from oracle import pyoracle as O
+    import random
+    rng = random.Random(3)
+    alphabet = "ab.{}?,0123456789 -+x"
+    code_map = {O_code: c for O_code, c in [(-1, capi.ERR_LAZY), (-2, capi.ERR_MINMAX), (-3, capi.ERR_NUMBER)]}
+    for _ in range(3000):
+        q = "".join(rng.choice(alphabet) for _ in range(rng.randrange(0, 18)))
+        if rng.random() < 0.5:
+            q = "a.{%s,%s}%sb" % (rng.choice(["1", " 2", "x", "", "-1", "+3", "9" * 25]), rng.choice(["5", "0", "", "7x"]),
+                                  rng.choice(["?", ""])) + q
+        for syntax in (0, 1):
+            rc, subs, gaps = O.parse(q, syntax)
+            try:
+                s2, g2 = capi.parse_query(q, syntax)
+                assert rc == 0 and s2 == subs and g2 == gaps, q
+            except capi.VlgbError as e:
+                assert rc != 0 and code_map[rc] == e.code, (q, rc, e.code)
+
+
+def test_no_gpu_means_loud_failure():
+    if capi.device_count() > 0:
+        pytest.skip("GPU present")
+    with pytest.raises(capi.VlgbError) as e:
+        capi.Index.build(b"abracadabra")
+    assert e.value.code == capi.ERR_CUDA
+
+
+def test_zero_symbol_rejected_before_any_device_work():
+    with pytest.raises(capi.VlgbError) as e:
+        capi.Index.build(b"abc\0def")
+    assert e.value.code == capi.ERR_ZERO_SYMBOL  # construct.hpp:35-45

@@ -1,0 +1,225 @@
+"""GPU: the CUDA path, called through the C ABI (libvlgb200.so), against
+  * the vectors generated from the unmodified reference (tests/golden/*.json), and
+  * the CPU oracle (oracle/vlg_oracle.c) on seeded synthetic inputs.
+Integer positions: the bar is bit-exact equality of every tuple."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as O
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def V():
+    import vlg_matching_b200 as V
+    from vlg_matching_b200 import capi
+    assert capi.device_count() > 0
+    capi.init(0)
+    return V
+
+
+def golden(name):
+    with open(os.path.join(HERE, "golden", name)) as f:
+        return json.load(f)["vectors"]
+
+
+def run_vectors(V, vectors):
+    from vlg_matching_b200 import capi
+    n_checked = 0
+    for v in vectors:
+        text = v["text"].encode("latin-1")
+        idx = V.Index.build(text)
+        parsed, cases = [], []
+        for c in v["cases"]:
+            try:
+                subs, gaps = capi.parse_query(c["query"])
+            except capi.VlgbError as e:
+                assert "error" in c, c
+                want = capi.ERR_LAZY if "lazy" in c["error"] else (capi.ERR_MINMAX if "min-gap" in c["error"] else capi.ERR_NUMBER)
+                assert e.code == want
+                continue
+            assert "error" not in c, c
+            parsed.append((subs, gaps))
+            cases.append(c)
+        if not parsed:
+            continue
+        b = V.PackedBatch(parsed)
+        r = idx.search(b, capi.WANT_TUPLES)
+        rc = idx.search(b, capi.WANT_COUNT)
+        for q, c in enumerate(cases):
+            if any(len(s) == 0 for s in parsed[q][0]):
+                assert r.status(q) == capi.ERR_EMPTY_SUB  # fenced, SURVEY A.4
+                continue
+            assert r.status(q) == 0
+            assert int(r.counts()[q]) == c["count"] == int(rc.counts()[q]), (v["text"], c["query"])
+            assert r.tuples(q).tolist() == c["tuples"], (v["text"], c["query"])
+            assert r.starts(q).tolist() == [t[0] for t in c["tuples"]]
+            n_checked += 1
+        idx.free()
+    return n_checked
+
+
+def test_reference_appendix_b(V):
+    assert run_vectors(V, golden("appendix_b.json")) >= 40
+
+
+def test_reference_random_vectors(V):
+    assert run_vectors(V, golden("random_ref.json")) >= 1500
+
+
+def compare_with_oracle(V, text, queries, want_tuples=True, **build_kw):
+    from vlg_matching_b200 import capi
+    idx = V.Index.build(text, **build_kw)
+    r = idx.search(V.PackedBatch(queries), capi.WANT_TUPLES if want_tuples else capi.WANT_STARTS)
+    ref = O.search(text, queries, want_tuples=want_tuples, threads=8)
+    total = 0
+    for q, (st, starts, tup) in enumerate(ref):
+        assert st == 0 and r.status(q) == 0
+        assert np.array_equal(r.starts(q), starts), (q, queries[q])
+        if want_tuples:
+            assert np.array_equal(r.tuples(q), tup), (q, queries[q])
+        total += len(starts)
+    idx.free()
+    return total
+
+
+@pytest.mark.parametrize("cfg,n,nq", [(1, 1_000_000, 1), (2, 4 << 20, 300), (3, 4 << 20, 200), (5, 1 << 20, 64)])
+def test_configs_scaled_vs_oracle(V, cfg, n, nq):
+    from vlg_matching_b200 import synth
+    text = synth.make_text(cfg, n)
+    queries = synth.make_queries(cfg, text, nq)
+    assert compare_with_oracle(V, text, queries) > 0
+
+
+def test_many_patterns_multi_pass(V):
+    # > 1024 distinct subpatterns -> several scan passes; long (> 8 byte) subpatterns share prefixes
+    from vlg_matching_b200 import synth
+    text = synth.make_text(2, 2 << 20)
+    queries = synth.sample_queries(text, 900, 2, (2, 14), [(0, 30), (5, 200)], 77, True)
+    queries += synth.sample_queries(text, 200, 4, (1, 4), [(0, 10), (3, 60)], 78, False)
+    queries += synth.sample_queries(text, 100, 1, (1, 20), [(0, 0)], 79, False)
+    assert compare_with_oracle(V, text, queries) > 0
+
+
+def test_small_alphabet_dense_lists(V):
+    rng = np.random.default_rng(5)
+    text = rng.integers(97, 99, size=300_000, dtype=np.uint8)  # 'a','b' only: every list is huge
+    queries = [([b"a"], []), ([b"b"], []), ([b"ab"], []), ([b"a", b"b"], [(0, 0)]), ([b"a", b"a", b"a"], [(0, 1), (0, 3)]),
+               ([b"ab", b"ba", b"ab", b"b"], [(0, 2), (1, 1), (0, 7)]), ([b"aaaaaaaaaaaa"], []),
+               ([b"abababab", b"b"], [(5, 9)]), ([b"b", b"a"], [(1000, 2000)])]
+    assert compare_with_oracle(V, text, queries) > 0
+
+
+def test_edge_cases(V):
+    from vlg_matching_b200 import capi
+    idx = V.Index.build(b"abracadabrasimsalabim")
+    b = V.PackedBatch([([b"a"], []), ([b""], []), ([b"a", b""], [(0, 3)]), ([b"zzz", b"a"], [(0, 5)]),
+                       ([b"abracadabrasimsalabimX"], []), ([b"a", b"a"], [(2**63, 2**64 - 1)]), ([b"abracadabrasimsalabim"], [])])
+    r = idx.search(b, capi.WANT_TUPLES)
+    assert r.status(0) == 0 and r.tuples(0)[:, 0].tolist() == [0, 3, 5, 7, 10, 15, 17]
+    assert r.status(1) == capi.ERR_EMPTY_SUB and r.status(2) == capi.ERR_EMPTY_SUB
+    assert r.status(3) == 0 and r.counts()[3] == 0
+    assert r.status(4) == 0 and r.counts()[4] == 0       # longer than the text
+    assert r.status(5) == 0 and r.counts()[5] == 0       # saturating gap arithmetic
+    assert r.counts()[6] == 1 and r.tuples(6).tolist() == [[0]]
+    assert r.occurrences(0) == 7
+    # empty batch, one-byte text
+    r0 = idx.search(V.PackedBatch([]), capi.WANT_TUPLES)
+    assert r0.n == 0 and r0.total() == 0
+    one = V.Index.build(b"a")
+    r1 = one.search(V.PackedBatch([([b"a"], []), ([b"b"], []), ([b"a", b"a"], [(0, 0)])]), capi.WANT_TUPLES)
+    assert r1.counts().tolist() == [1, 0, 0]
+    assert idx.extract(4, 7) == b"cadabra" and idx.size() == 21
+
+
+def test_library_and_benchmark_surfaces(V, tmp_path):
+    idx = V.construct(b"abracadabrasimsalabim")
+    assert V.count(idx, "ac.{2,5}?a.{4,8}?b") == 1                      # examples/vlg_matching.cpp:40
+    assert V.locate(idx, "a.{0,10}?a.{0,10}?a").tolist() == [[0, 3, 5], [7, 10, 15]]
+    assert V.count(idx, "foo.{0,10}?bar") == 0
+    with pytest.raises(ValueError, match="lazy"):
+        V.locate(idx, "a.{1,2}b")
+    with pytest.raises(ValueError, match="min-gap > max-gap"):
+        V.locate(idx, "a.{3,2}?b")
+    with pytest.raises(ValueError, match="zero symbol"):
+        V.construct(b"ab\0c")
+    bidx = V.IndexB200(b"abracadabrasimsalabim")
+    assert bidx.search("a.{0,10}a").tolist() == [0, 5, 10]
+    assert bidx.info("a.{0,10}b") == "10"
+    p = str(tmp_path / "index.vlgb")
+    bidx.serialize(p)
+    other = V.IndexB200()
+    other.load(p)
+    assert other.search("a.{0,10}a").tolist() == [0, 5, 10]
+
+
+def test_entry_cursor_and_sharded_equivalence(V):
+    """Text cut into overlapping shards (owned part + halo >= max span): per-shard results, chained
+    through exit cursors with vlgb_result_fixup, equal the single-shard result."""
+    from vlg_matching_b200 import capi, synth
+    text = synth.make_text(2, 1 << 20)
+    queries = synth.make_queries(2, text, 120) + synth.sample_queries(text, 60, 3, (1, 3), [(0, 40), (100, 1000)], 5, False)
+    queries += [([b"e"], []), ([b" "], []), ([b"th"], [])]
+    span = max(sum(len(s) for s in subs) + sum(g[1] for g in gaps) for subs, gaps in queries)
+    whole = V.Index.build(text)
+    b = V.PackedBatch(queries)
+    rw = whole.search(b, capi.WANT_TUPLES)
+    G = 5
+    n = text.size
+    cuts = [n * g // G for g in range(G + 1)]
+    cuts[2] += 1  # odd boundary: the k = 1 parity quirk must use whole-text parity
+    cursor = np.zeros(len(queries), dtype=np.uint64)
+    parts = [[] for _ in queries]
+    changed = 0
+    for g in range(G):
+        lo, hi = cuts[g], cuts[g + 1]
+        end = min(n, hi + span)
+        shard = V.Index.build(text[lo:end], global_offset=lo, owned_len=hi - lo, total_len=n)
+        r = shard.search(b, capi.WANT_TUPLES)          # speculative: entry cursor 0
+        changed += r.fixup(cursor)                     # true cursors from the left neighbour
+        cursor = r.exit_cursors()
+        for q in range(len(queries)):
+            assert r.status(q) == 0
+            parts[q].append(r.tuples(q))
+        r2 = shard.search(b, capi.WANT_TUPLES, entry_cursor=np.asarray([c for c in r.exit_cursors()]))
+        del r2
+    for q in range(len(queries)):
+        got = np.concatenate(parts[q], axis=0)
+        assert np.array_equal(got, rw.tuples(q)), (q, queries[q])
+    assert changed > 0  # the single-byte queries straddle every boundary
+
+
+def test_full_size_properties_config2(V):
+    """Config 2 at full size (200 MiB, 1000 queries): size-independent properties instead of the oracle:
+    every reported tuple really occurs in the text with gaps inside bounds, starts strictly ascending and
+    non-overlapping, count-only and tuple runs agree, and a 1 MiB prefix agrees with the oracle."""
+    from vlg_matching_b200 import capi, synth
+    text = synth.make_text(2)
+    queries = synth.make_queries(2, text)
+    idx = V.Index.build(text)
+    b = V.PackedBatch(queries)
+    r = idx.search(b, capi.WANT_TUPLES)
+    rc = idx.search(b, capi.WANT_COUNT)
+    assert np.array_equal(r.counts(), rc.counts())
+    assert r.total() > 0
+    for q, (subs, gaps) in enumerate(queries[:200]):
+        t = r.tuples(q)
+        if t.shape[0] == 0:
+            continue
+        t = t.astype(np.int64)
+        for i, s in enumerate(subs):
+            pos = t[:, i]
+            for j, ch in enumerate(s):
+                assert (text[pos + j] == ch).all()
+        for i, (a, bb) in enumerate(gaps):
+            d = t[:, i + 1] - t[:, i] - len(subs[i])
+            assert (d >= a).all() and (d <= bb).all()
+        assert (t[1:, 0] >= t[:-1, -1] + len(subs[-1])).all()
+    idx.free()
+    small = text[:1 << 20]
+    assert compare_with_oracle(V, small, queries[:100]) >= 0

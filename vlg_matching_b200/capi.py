@@ -1,0 +1,292 @@
+"""ctypes binding of libvlgb200.so (include/vlgb200.h).
+
+This is the binding the tests and bench.py use; the reference-facing host layer is the C++ header
+vlg_matching_b200/csrc/host/vlg_b200.hpp.  There is no CPU fallback: importing works everywhere (so
+the symbol table can be checked on a CPU box), every compute call needs a CUDA device and raises
+VlgbError otherwise; a missing library raises at import time.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libvlgb200.so")
+
+OK, ERR_CUDA, ERR_ARG, ERR_LAZY, ERR_MINMAX, ERR_NUMBER, ERR_EMPTY_SUB, ERR_ZERO_SYMBOL, ERR_NOMEM, ERR_IO, \
+    ERR_TOO_LARGE = 0, -1, -2, -3, -4, -5, -6, -7, -8, -9, -10
+SYNTAX_LIBRARY, SYNTAX_BENCHMARK = 0, 1
+WANT_COUNT, WANT_STARTS, WANT_TUPLES, KEEP_ON_DEVICE = 0, 1, 2, 16
+MAX_STAGES = 16
+
+# every symbol include/vlgb200.h declares
+SYMBOLS = [
+    "vlgb_device_count", "vlgb_init", "vlgb_last_error", "vlgb_version", "vlgb_parse_query", "vlgb_batch_free",
+    "vlgb_index_build", "vlgb_index_build_file", "vlgb_index_build_device", "vlgb_index_save", "vlgb_index_load",
+    "vlgb_index_size", "vlgb_index_extract", "vlgb_index_free", "vlgb_search_batch", "vlgb_result_queries",
+    "vlgb_result_status", "vlgb_result_count", "vlgb_result_total", "vlgb_result_counts", "vlgb_result_starts",
+    "vlgb_result_tuples", "vlgb_result_exit_cursors", "vlgb_result_first_starts", "vlgb_result_occurrences",
+    "vlgb_result_fixup", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
+    "vlgb_stream_handle",
+]
+
+
+class VlgbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"vlgb error {code}: {msg}")
+        self.code = code
+
+
+class Batch(C.Structure):
+    _fields_ = [("n_queries", C.c_uint32), ("sub_off", C.c_void_p), ("pat_off", C.c_void_p),
+                ("pat_bytes", C.c_void_p), ("gap_min", C.c_void_p), ("gap_max", C.c_void_p)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_stages", C.c_uint32), ("ms", C.c_float * MAX_STAGES), ("bytes", C.c_uint64 * MAX_STAGES),
+                ("launches", C.c_uint32 * MAX_STAGES), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("distinct_patterns", C.c_uint32), ("scan_passes", C.c_uint32), ("segments", C.c_uint32),
+                ("query_chunks", C.c_uint32), ("total_occurrences", C.c_uint64), ("join_slots", C.c_uint64)]
+
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                      "(there is no CPU fallback)")
+lib = C.CDLL(LIB_PATH)
+
+_P = C.c_void_p
+lib.vlgb_device_count.restype = C.c_int
+lib.vlgb_init.argtypes = [C.c_int]
+lib.vlgb_last_error.restype = C.c_char_p
+lib.vlgb_version.restype = C.c_char_p
+lib.vlgb_parse_query.argtypes = [C.c_char_p, C.c_size_t, C.c_int, C.POINTER(C.POINTER(Batch))]
+lib.vlgb_batch_free.argtypes = [C.POINTER(Batch)]
+lib.vlgb_index_build.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_P)]
+lib.vlgb_index_build_file.argtypes = [C.c_char_p, C.POINTER(_P)]
+lib.vlgb_index_build_device.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_P)]
+lib.vlgb_index_save.argtypes = [_P, C.c_char_p]
+lib.vlgb_index_load.argtypes = [C.c_char_p, C.POINTER(_P)]
+lib.vlgb_index_size.argtypes = [_P]
+lib.vlgb_index_size.restype = C.c_uint64
+lib.vlgb_index_extract.argtypes = [_P, C.c_uint64, C.c_uint64, _P]
+lib.vlgb_index_free.argtypes = [_P]
+lib.vlgb_search_batch.argtypes = [_P, C.POINTER(Batch), _P, C.c_uint32, C.POINTER(_P)]
+lib.vlgb_result_queries.argtypes = [_P]
+lib.vlgb_result_queries.restype = C.c_uint32
+lib.vlgb_result_status.argtypes = [_P, C.c_uint32]
+lib.vlgb_result_status.restype = C.c_int32
+lib.vlgb_result_count.argtypes = [_P, C.c_uint32]
+lib.vlgb_result_count.restype = C.c_uint64
+lib.vlgb_result_total.argtypes = [_P]
+lib.vlgb_result_total.restype = C.c_uint64
+for _f in ("vlgb_result_counts", "vlgb_result_exit_cursors", "vlgb_result_first_starts"):
+    getattr(lib, _f).argtypes = [_P]
+    getattr(lib, _f).restype = C.POINTER(C.c_uint64)
+for _f in ("vlgb_result_starts", "vlgb_result_tuples"):
+    getattr(lib, _f).argtypes = [_P, C.c_uint32]
+    getattr(lib, _f).restype = C.POINTER(C.c_uint64)
+lib.vlgb_result_occurrences.argtypes = [_P, C.c_uint32]
+lib.vlgb_result_occurrences.restype = C.c_uint64
+lib.vlgb_result_fixup.argtypes = [_P, _P, C.POINTER(C.c_uint32)]
+lib.vlgb_result_free.argtypes = [_P]
+lib.vlgb_last_stats.argtypes = [C.POINTER(Stats)]
+lib.vlgb_stage_name.argtypes = [C.c_uint32]
+lib.vlgb_stage_name.restype = C.c_char_p
+lib.vlgb_set_tuning.argtypes = [C.c_uint64, C.c_uint64]
+lib.vlgb_stream_handle.restype = C.c_void_p
+
+
+def check(rc):
+    if rc != 0:
+        raise VlgbError(rc, lib.vlgb_last_error().decode("latin-1"))
+
+
+def device_count() -> int:
+    return lib.vlgb_device_count()
+
+
+def init(device: int = 0):
+    check(lib.vlgb_init(device))
+
+
+def last_stats() -> dict:
+    s = Stats()
+    check(lib.vlgb_last_stats(C.byref(s)))
+    stages = {}
+    for i in range(s.n_stages):
+        stages[lib.vlgb_stage_name(i).decode()] = {"ms": float(s.ms[i]), "bytes": int(s.bytes[i]),
+                                                   "launches": int(s.launches[i])}
+    return {"stages": stages, "h2d_bytes": int(s.h2d_bytes), "d2h_bytes": int(s.d2h_bytes),
+            "distinct_patterns": int(s.distinct_patterns), "scan_passes": int(s.scan_passes),
+            "segments": int(s.segments), "query_chunks": int(s.query_chunks),
+            "total_occurrences": int(s.total_occurrences), "join_slots": int(s.join_slots)}
+
+
+def parse_query(q: bytes | str, syntax: int = SYNTAX_LIBRARY):
+    """-> (subpatterns: list[bytes], gaps: list[(a, b)]); raises VlgbError with the reference's codes."""
+    if isinstance(q, str):
+        q = q.encode("latin-1")
+    pb = C.POINTER(Batch)()
+    check(lib.vlgb_parse_query(q, len(q), syntax, C.byref(pb)))
+    b = pb.contents
+    k = C.cast(b.sub_off, C.POINTER(C.c_uint32))[1]
+    po = C.cast(b.pat_off, C.POINTER(C.c_uint64))
+    by = C.cast(b.pat_bytes, C.POINTER(C.c_uint8))
+    gmin = C.cast(b.gap_min, C.POINTER(C.c_uint64))
+    gmax = C.cast(b.gap_max, C.POINTER(C.c_uint64))
+    subs = [bytes(bytearray(by[po[i]:po[i + 1]])) for i in range(k)]
+    gaps = [(int(gmin[i]), int(gmax[i])) for i in range(k - 1)]
+    lib.vlgb_batch_free(pb)
+    return subs, gaps
+
+
+class PackedBatch:
+    """Queries [(subs, gaps), ...] in the CSR layout of vlgb_batch (numpy arrays kept alive here)."""
+
+    def __init__(self, queries):
+        sub_off, pat_off, gmin, gmax = [0], [0], [], []
+        blob = bytearray()
+        self.k = []
+        for subs, gaps in queries:
+            self.k.append(len(subs))
+            for i, s in enumerate(subs):
+                blob += s
+                pat_off.append(len(blob))
+                a, b = gaps[i] if i < len(gaps) else (0, 0)
+                gmin.append(a)
+                gmax.append(b)
+            sub_off.append(len(pat_off) - 1)
+        self.sub_off = np.asarray(sub_off, dtype=np.uint32)
+        self.pat_off = np.asarray(pat_off, dtype=np.uint64)
+        self.blob = np.frombuffer(bytes(blob) or b"\0", dtype=np.uint8).copy()
+        self.gmin = np.asarray(gmin or [0], dtype=np.uint64)
+        self.gmax = np.asarray(gmax or [0], dtype=np.uint64)
+        self.c = Batch(len(queries), self.sub_off.ctypes.data, self.pat_off.ctypes.data, self.blob.ctypes.data,
+                       self.gmin.ctypes.data, self.gmax.ctypes.data)
+
+    def __len__(self):
+        return len(self.k)
+
+
+class Result:
+    def __init__(self, handle, batch: PackedBatch, want: int):
+        self.h = handle
+        self.batch = batch
+        self.want = want
+
+    def __del__(self):
+        self.free()
+
+    def free(self):
+        if self.h:
+            lib.vlgb_result_free(self.h)
+            self.h = None
+
+    @property
+    def n(self):
+        return lib.vlgb_result_queries(self.h)
+
+    def status(self, q):
+        return lib.vlgb_result_status(self.h, q)
+
+    def counts(self) -> np.ndarray:
+        return np.ctypeslib.as_array(lib.vlgb_result_counts(self.h), shape=(max(self.n, 1),))[:self.n].copy()
+
+    def total(self) -> int:
+        return lib.vlgb_result_total(self.h)
+
+    def exit_cursors(self) -> np.ndarray:
+        return np.ctypeslib.as_array(lib.vlgb_result_exit_cursors(self.h), shape=(max(self.n, 1),))[:self.n].copy()
+
+    def first_starts(self) -> np.ndarray:
+        return np.ctypeslib.as_array(lib.vlgb_result_first_starts(self.h), shape=(max(self.n, 1),))[:self.n].copy()
+
+    def occurrences(self, q) -> int:
+        return lib.vlgb_result_occurrences(self.h, q)
+
+    def starts(self, q) -> np.ndarray:
+        c = lib.vlgb_result_count(self.h, q)
+        p = lib.vlgb_result_starts(self.h, q)
+        if not p or c == 0:
+            return np.zeros(0, dtype=np.uint64)
+        return np.ctypeslib.as_array(p, shape=(c,)).copy()
+
+    def tuples(self, q) -> np.ndarray:
+        c = lib.vlgb_result_count(self.h, q)
+        k = self.batch.k[q]
+        p = lib.vlgb_result_tuples(self.h, q)
+        if not p or c == 0:
+            return np.zeros((0, k), dtype=np.uint64)
+        return np.ctypeslib.as_array(p, shape=(c * k,)).copy().reshape(c, k)
+
+    def fixup(self, entry_cursor: np.ndarray) -> int:
+        e = np.ascontiguousarray(entry_cursor, dtype=np.uint64)
+        n = C.c_uint32(0)
+        check(lib.vlgb_result_fixup(self.h, e.ctypes.data, C.byref(n)))
+        return n.value
+
+
+class Index:
+    """A text shard resident in HBM (vlgb_index)."""
+
+    def __init__(self, handle):
+        self.h = handle
+
+    @classmethod
+    def build(cls, text, global_offset=0, owned_len=None, total_len=None):
+        if isinstance(text, (bytes, bytearray)):
+            text = np.frombuffer(bytes(text), dtype=np.uint8)
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        n = text.size
+        h = _P()
+        check(lib.vlgb_index_build(text.ctypes.data if n else None, n, global_offset, n if owned_len is None else owned_len,
+                                   (global_offset + n) if total_len is None else total_len, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def build_device(cls, ptr: int, n: int, global_offset=0, owned_len=None, total_len=None):
+        h = _P()
+        check(lib.vlgb_index_build_device(ptr, n, global_offset, n if owned_len is None else owned_len,
+                                          (global_offset + n) if total_len is None else total_len, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def build_file(cls, path: str):
+        h = _P()
+        check(lib.vlgb_index_build_file(path.encode(), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def load(cls, path: str):
+        h = _P()
+        check(lib.vlgb_index_load(path.encode(), C.byref(h)))
+        return cls(h)
+
+    def save(self, path: str):
+        check(lib.vlgb_index_save(self.h, path.encode()))
+
+    def size(self) -> int:
+        return lib.vlgb_index_size(self.h)
+
+    def extract(self, pos: int, length: int) -> bytes:
+        out = np.zeros(max(length, 1), dtype=np.uint8)
+        check(lib.vlgb_index_extract(self.h, pos, length, out.ctypes.data))
+        return out[:length].tobytes()
+
+    def search(self, batch: PackedBatch, want=WANT_TUPLES, entry_cursor=None) -> Result:
+        e = None
+        if entry_cursor is not None:
+            e = np.ascontiguousarray(entry_cursor, dtype=np.uint64)
+        r = _P()
+        check(lib.vlgb_search_batch(self.h, C.byref(batch.c), e.ctypes.data if e is not None else None, want, C.byref(r)))
+        return Result(r, batch, want)
+
+    def free(self):
+        if self.h:
+            lib.vlgb_index_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.free()

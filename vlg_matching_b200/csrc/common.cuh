@@ -153,9 +153,10 @@ struct Context {
     Arena scan_arena;    // count matrix, pattern tables
     Arena list_arena;    // occurrence lists of the current segment
     Arena join_arena;    // per-chunk join / selection state
+    DeviceBuffer out_buf; // starts / tuples of the current chunk before they go to the host
     PinnedBuffer pinned; // small host staging
     // timers
-    cudaEvent_t ev[2 * 64] = {};
+    cudaEvent_t ev[2 * 512] = {};
     bool ev_ready = false;
     struct Span {
         uint32_t stage;
@@ -173,7 +174,7 @@ struct Context {
             for (auto& e : ev) cudaEventCreate(&e);
             ev_ready = true;
         }
-        if (ev_used + 2 > 128) flush_timers();
+        if (ev_used + 2 > 2 * 512) flush_timers();
         cudaEventRecord(ev[ev_used], stream);
         spans.push_back({stage, ev_used, ev_used + 1});
         ev_used += 2;

@@ -1,0 +1,607 @@
+// engine.cu — libvlgb200.so: the C ABI of include/vlgb200.h on top of the sm_100a kernels
+// (scan.cuh -> join.cuh -> select.cuh, prefix.cuh).  No CPU fallback: every compute entry point needs
+// a CUDA device and fails with VLGB_ERR_CUDA otherwise.
+#include <algorithm>
+#include <cstdlib>
+#include <memory>
+#include <numeric>
+
+#include "common.cuh"
+#include "parse.hpp"
+#include "search.cuh"
+
+using namespace vlgb;
+
+// ---------------------------------------------------------------------------------------------
+// handles
+// ---------------------------------------------------------------------------------------------
+struct vlgb_index {
+    uint8_t* d_text = nullptr;  // n + PAD readable bytes
+    bool owns = false;
+    uint64_t n = 0, global_offset = 0, owned_len = 0, total_len = 0;
+};
+static constexpr uint64_t TEXT_PAD = 64;
+static constexpr uint64_t MAX_SHARD = 0xFFFFF000ull;  // positions are shard-local u32 on the device
+
+struct HostBlock {  // pinned result memory
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct vlgb_result {
+    uint32_t nq = 0;
+    uint32_t want = 0;
+    std::vector<int32_t> status;
+    std::vector<uint64_t> counts, exit_cursor, occ;
+    std::vector<const uint64_t*> starts, tuples;
+    std::vector<HostBlock> blocks;
+    uint64_t total = 0;
+};
+
+namespace {
+
+// pinned blocks are recycled across results (cudaHostAlloc is slow)
+struct PinnedPool {
+    std::vector<HostBlock> free_list;
+    HostBlock take(size_t bytes)
+    {
+        size_t best = SIZE_MAX;
+        for (size_t i = 0; i < free_list.size(); i++)
+            if (free_list[i].cap >= bytes && (best == SIZE_MAX || free_list[i].cap < free_list[best].cap)) best = i;
+        if (best != SIZE_MAX && free_list[best].cap <= 4 * bytes + (1u << 20)) {
+            HostBlock b = free_list[best];
+            free_list.erase(free_list.begin() + best);
+            return b;
+        }
+        HostBlock b;
+        b.cap = bytes + bytes / 4 + 4096;
+        if (cudaMallocHost(&b.p, b.cap) != cudaSuccess) throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
+        return b;
+    }
+    void give(HostBlock b)
+    {
+        if (free_list.size() >= 8) {
+            size_t small = 0;
+            for (size_t i = 1; i < free_list.size(); i++)
+                if (free_list[i].cap < free_list[small].cap) small = i;
+            if (free_list[small].cap < b.cap) std::swap(free_list[small], b);
+            cudaFreeHost(b.p);
+            return;
+        }
+        free_list.push_back(b);
+    }
+};
+PinnedPool& pinned_pool()
+{
+    static thread_local PinnedPool p;
+    return p;
+}
+
+int cuda_fail(const CudaError& e)
+{
+    cudaGetLastError();
+    int code = e.e == cudaErrorMemoryAllocation ? VLGB_ERR_NOMEM : VLGB_ERR_CUDA;
+    return fail(code, "CUDA error %d (%s) at %s:%d", (int)e.e, cudaGetErrorString(e.e), e.file, e.line);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// device / errors
+// ---------------------------------------------------------------------------------------------
+extern "C" int vlgb_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" int vlgb_init(int device)
+{
+    try {
+        Context& c = ctx();
+        if (c.ready && c.device == device) return VLGB_OK;
+        if (c.ready) return fail(VLGB_ERR_ARG, "vlgb_init: thread already bound to device %d", c.device);
+        c.device = device;
+        ensure_ready();
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        ctx().device = -1;
+        return cuda_fail(e);
+    }
+}
+
+extern "C" const char* vlgb_last_error(void) { return last_error().c_str(); }
+extern "C" const char* vlgb_version(void) { return "vlgb200 0.1 (sm_100a, abi 1)"; }
+extern "C" const char* vlgb_stage_name(uint32_t stage) { return stage_name(stage); }
+
+extern "C" int vlgb_last_stats(vlgb_stats* out)
+{
+    if (!out) return fail(VLGB_ERR_ARG, "vlgb_last_stats: null");
+    Context& c = ctx();
+    c.flush_timers();
+    *out = c.stats;
+    out->n_stages = ST_COUNT;
+    return VLGB_OK;
+}
+
+extern "C" void* vlgb_stream_handle(void) { return ctx().ready ? (void*)ctx().stream : nullptr; }
+
+extern "C" int vlgb_set_tuning(uint64_t segment_bytes, uint64_t join_budget_bytes)
+{
+    Context& c = ctx();
+    if (segment_bytes) c.segment_bytes = segment_bytes;
+    if (join_budget_bytes) c.join_budget = join_budget_bytes;
+    return VLGB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// parsing
+// ---------------------------------------------------------------------------------------------
+extern "C" int vlgb_parse_query(const char* str, size_t len, int syntax, vlgb_batch** out)
+{
+    if (!str || !out) return fail(VLGB_ERR_ARG, "vlgb_parse_query: null argument");
+    if (syntax != VLGB_SYNTAX_LIBRARY && syntax != VLGB_SYNTAX_BENCHMARK)
+        return fail(VLGB_ERR_ARG, "vlgb_parse_query: unknown syntax %d", syntax);
+    *out = nullptr;
+    ParsedQuery q;
+    int rc = parse_query(str, len, syntax, q);
+    if (rc == VLGB_ERR_LAZY) return fail(rc, "invalid gap description: expected '?' (lazy semantics)");
+    if (rc == VLGB_ERR_MINMAX) return fail(rc, "invalid gap description: min-gap > max-gap");
+    if (rc != VLGB_OK) return fail(rc, "invalid gap description: not a number");
+    OwnedBatch* b = new (std::nothrow) OwnedBatch();
+    if (!b) return fail(VLGB_ERR_NOMEM, "out of memory");
+    b->add(q);
+    b->seal();
+    *out = &b->pub;
+    return VLGB_OK;
+}
+
+extern "C" void vlgb_batch_free(vlgb_batch* b)
+{
+    if (b) delete reinterpret_cast<OwnedBatch*>(b);  // pub is the first member
+}
+
+// ---------------------------------------------------------------------------------------------
+// index: a text shard resident in HBM
+// ---------------------------------------------------------------------------------------------
+static int index_check(uint64_t n, uint64_t owned_len, const char* who)
+{
+    if (n > MAX_SHARD) return fail(VLGB_ERR_TOO_LARGE, "%s: shard of %llu bytes exceeds %llu (split the text into shards)", who,
+                                   (unsigned long long)n, (unsigned long long)MAX_SHARD);
+    if (owned_len > n) return fail(VLGB_ERR_ARG, "%s: owned_len > n", who);
+    return VLGB_OK;
+}
+
+extern "C" int vlgb_index_build(const uint8_t* text, uint64_t n, uint64_t global_offset, uint64_t owned_len,
+                                uint64_t total_len, vlgb_index** out)
+{
+    if (!out || (!text && n)) return fail(VLGB_ERR_ARG, "vlgb_index_build: null argument");
+    *out = nullptr;
+    int rc = index_check(n, owned_len, "vlgb_index_build");
+    if (rc) return rc;
+    if (n && memchr(text, 0, n))
+        return fail(VLGB_ERR_ZERO_SYMBOL, "Error: File \"<memory>\" contains zero symbol.");  // construct.hpp:35-45
+    try {
+        ensure_ready();
+        Context& c = ctx();
+        std::unique_ptr<vlgb_index> idx(new vlgb_index());
+        VLGB_CUDA(cudaMalloc(&idx->d_text, n + TEXT_PAD));
+        idx->owns = true;
+        VLGB_CUDA(cudaMemsetAsync(idx->d_text + n, 0, TEXT_PAD, c.stream));
+        if (n) VLGB_CUDA(cudaMemcpyAsync(idx->d_text, text, n, cudaMemcpyHostToDevice, c.stream));
+        VLGB_CUDA(cudaStreamSynchronize(c.stream));
+        idx->n = n;
+        idx->global_offset = global_offset;
+        idx->owned_len = owned_len;
+        idx->total_len = total_len;
+        *out = idx.release();
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+extern "C" int vlgb_index_build_device(const uint8_t* text_device, uint64_t n, uint64_t global_offset,
+                                       uint64_t owned_len, uint64_t total_len, vlgb_index** out)
+{
+    if (!out || !text_device) return fail(VLGB_ERR_ARG, "vlgb_index_build_device: null argument");
+    *out = nullptr;
+    int rc = index_check(n, owned_len, "vlgb_index_build_device");
+    if (rc) return rc;
+    try {
+        ensure_ready();
+        vlgb_index* idx = new vlgb_index();
+        idx->d_text = const_cast<uint8_t*>(text_device);
+        idx->owns = false;
+        idx->n = n;
+        idx->global_offset = global_offset;
+        idx->owned_len = owned_len;
+        idx->total_len = total_len;
+        *out = idx;
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+static int read_file(const char* path, std::vector<uint8_t>& buf, uint64_t skip)
+{
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(VLGB_ERR_IO, "cannot open %s", path);
+    fseek(f, 0, SEEK_END);
+    long long sz = ftell(f);
+    if (sz < (long long)skip) {
+        fclose(f);
+        return fail(VLGB_ERR_IO, "%s: truncated", path);
+    }
+    fseek(f, (long)skip, SEEK_SET);
+    buf.resize((size_t)(sz - skip));
+    size_t got = buf.empty() ? 0 : fread(buf.data(), 1, buf.size(), f);
+    fclose(f);
+    if (got != buf.size()) return fail(VLGB_ERR_IO, "%s: short read", path);
+    return VLGB_OK;
+}
+
+extern "C" int vlgb_index_build_file(const char* path, vlgb_index** out)
+{
+    if (!path || !out) return fail(VLGB_ERR_ARG, "vlgb_index_build_file: null argument");
+    std::vector<uint8_t> buf;
+    int rc = read_file(path, buf, 0);
+    if (rc) return rc;
+    rc = vlgb_index_build(buf.data(), buf.size(), 0, buf.size(), buf.size(), out);
+    if (rc == VLGB_ERR_ZERO_SYMBOL) fail(rc, "Error: File \"%s\" contains zero symbol.", path);
+    return rc;
+}
+
+// on-disk: magic, n, global_offset, owned_len, total_len, text bytes (vlg_index::serialize writes
+// text then wt, vlg_index.hpp:183-191; there is no wavelet tree here)
+static const char INDEX_MAGIC[8] = {'V', 'L', 'G', 'B', '2', '0', '0', '\1'};
+
+extern "C" int vlgb_index_save(const vlgb_index* idx, const char* path)
+{
+    if (!idx || !path) return fail(VLGB_ERR_ARG, "vlgb_index_save: null argument");
+    try {
+        ensure_ready();
+        std::vector<uint8_t> buf(idx->n);
+        if (idx->n) VLGB_CUDA(cudaMemcpy(buf.data(), idx->d_text, idx->n, cudaMemcpyDeviceToHost));
+        FILE* f = fopen(path, "wb");
+        if (!f) return fail(VLGB_ERR_IO, "cannot create %s", path);
+        uint64_t hdr[4] = {idx->n, idx->global_offset, idx->owned_len, idx->total_len};
+        bool ok = fwrite(INDEX_MAGIC, 1, 8, f) == 8 && fwrite(hdr, 8, 4, f) == 4 &&
+                  (idx->n == 0 || fwrite(buf.data(), 1, idx->n, f) == idx->n);
+        ok = (fclose(f) == 0) && ok;
+        return ok ? VLGB_OK : fail(VLGB_ERR_IO, "write to %s failed", path);
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+extern "C" int vlgb_index_load(const char* path, vlgb_index** out)
+{
+    if (!path || !out) return fail(VLGB_ERR_ARG, "vlgb_index_load: null argument");
+    *out = nullptr;
+    std::vector<uint8_t> buf;
+    int rc = read_file(path, buf, 0);
+    if (rc) return rc;
+    if (buf.size() < 40 || memcmp(buf.data(), INDEX_MAGIC, 8) != 0) return fail(VLGB_ERR_IO, "%s: not a vlgb200 index", path);
+    uint64_t hdr[4];
+    memcpy(hdr, buf.data() + 8, 32);
+    if (buf.size() - 40 != hdr[0]) return fail(VLGB_ERR_IO, "%s: size mismatch", path);
+    return vlgb_index_build(buf.data() + 40, hdr[0], hdr[1], hdr[2], hdr[3], out);
+}
+
+extern "C" uint64_t vlgb_index_size(const vlgb_index* idx) { return idx ? idx->n : 0; }
+
+extern "C" int vlgb_index_extract(const vlgb_index* idx, uint64_t pos, uint64_t len, uint8_t* out)
+{
+    if (!idx || (!out && len)) return fail(VLGB_ERR_ARG, "vlgb_index_extract: null argument");
+    if (pos > idx->n || len > idx->n - pos) return fail(VLGB_ERR_ARG, "vlgb_index_extract: range outside the shard");
+    try {
+        ensure_ready();
+        if (len) VLGB_CUDA(cudaMemcpy(out, idx->d_text + pos, len, cudaMemcpyDeviceToHost));
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+extern "C" void vlgb_index_free(vlgb_index* idx)
+{
+    if (!idx) return;
+    if (idx->owns && idx->d_text) cudaFree(idx->d_text);
+    delete idx;
+}
+
+// ---------------------------------------------------------------------------------------------
+// search
+// ---------------------------------------------------------------------------------------------
+struct vlgb_result_ext {  // what vlgb_result_fixup needs to re-enter the shard
+    const vlgb_index* idx = nullptr;
+    OwnedBatch batch;
+    std::vector<uint64_t> entry, first_start;
+};
+
+
+namespace {
+
+struct ResultImpl : vlgb_result {
+    vlgb_result_ext ext;
+};
+
+const uint64_t EMPTY_LIST[1] = {0};
+
+void copy_batch(const vlgb_batch* b, OwnedBatch& o)
+{
+    uint32_t nq = b->n_queries;
+    uint32_t ns = b->sub_off[nq];
+    o.sub_off.assign(b->sub_off, b->sub_off + nq + 1);
+    o.pat_off.assign(b->pat_off, b->pat_off + ns + 1);
+    o.bytes.assign(b->pat_bytes, b->pat_bytes + b->pat_off[ns]);
+    o.gmin.assign(b->gap_min, b->gap_min + ns);
+    o.gmax.assign(b->gap_max, b->gap_max + ns);
+    o.seal();
+}
+
+int batch_check(const vlgb_batch* b)
+{
+    if (!b) return fail(VLGB_ERR_ARG, "vlgb_search_batch: null batch");
+    if (b->n_queries && (!b->sub_off || !b->pat_off || !b->gap_min || !b->gap_max))
+        return fail(VLGB_ERR_ARG, "vlgb_search_batch: null array inside the batch");
+    if (b->n_queries && b->sub_off[0] != 0) return fail(VLGB_ERR_ARG, "vlgb_search_batch: sub_off[0] != 0");
+    for (uint32_t q = 0; q < b->n_queries; q++)
+        if (b->sub_off[q + 1] < b->sub_off[q]) return fail(VLGB_ERR_ARG, "vlgb_search_batch: sub_off not ascending");
+    uint32_t ns = b->n_queries ? b->sub_off[b->n_queries] : 0;
+    for (uint32_t s = 0; s < ns; s++)
+        if (b->pat_off[s + 1] < b->pat_off[s]) return fail(VLGB_ERR_ARG, "vlgb_search_batch: pat_off not ascending");
+    if (ns && b->pat_off[ns] && !b->pat_bytes) return fail(VLGB_ERR_ARG, "vlgb_search_batch: null pat_bytes");
+    return VLGB_OK;
+}
+
+void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const uint64_t* entry_cursor, uint32_t want,
+               ResultImpl& R)
+{
+    const uint32_t nq = batch->n_queries;
+    const uint32_t ns = nq ? batch->sub_off[nq] : 0;
+    R.nq = nq;
+    R.want = want;
+    R.status.assign(nq, VLGB_OK);
+    R.counts.assign(nq, 0);
+    R.occ.assign(nq, 0);
+    R.exit_cursor.assign(nq, 0);
+    R.starts.assign(nq, nullptr);
+    R.tuples.assign(nq, nullptr);
+    R.total = 0;
+    R.ext.idx = idx;
+    R.ext.entry.assign(nq, 0);
+    R.ext.first_start.assign(nq, ~uint64_t(0));
+    const bool want_starts = (want & 3u) >= VLGB_WANT_STARTS, want_tuples = (want & 3u) >= VLGB_WANT_TUPLES;
+    const bool keep_device = (want & VLGB_KEEP_ON_DEVICE) != 0;
+    for (uint32_t q = 0; q < nq; q++) {
+        R.ext.entry[q] = entry_cursor ? entry_cursor[q] : 0;
+        R.exit_cursor[q] = R.ext.entry[q];
+        if (want_starts && !keep_device) R.starts[q] = EMPTY_LIST;
+        if (want_tuples && !keep_device) R.tuples[q] = EMPTY_LIST;
+    }
+
+    // ---- classify queries, collect the distinct subpatterns
+    const uint64_t halo = idx->n - idx->owned_len;
+    const bool halo_truncated_by_shard = idx->global_offset + idx->n < idx->total_len;
+    PatternDict dict;
+    std::vector<uint32_t> sub_pid(ns, NONE32);
+    std::vector<PlanQuery> plan;
+    for (uint32_t q = 0; q < nq; q++) {
+        uint32_t s0 = batch->sub_off[q], s1 = batch->sub_off[q + 1], k = s1 - s0;
+        if (k == 0) { R.status[q] = VLGB_ERR_ARG; continue; }
+        if (k > (uint32_t)MAX_K) { R.status[q] = VLGB_ERR_TOO_LARGE; continue; }
+        bool empty_sub = false;
+        uint64_t span = 0;
+        for (uint32_t s = s0; s < s1; s++) {
+            uint64_t len = batch->pat_off[s + 1] - batch->pat_off[s];
+            if (len == 0) empty_sub = true;
+            span = sat_add64(span, len);
+            if (s + 1 < s1) span = sat_add64(span, batch->gap_max[s]);
+        }
+        if (empty_sub) { R.status[q] = VLGB_ERR_EMPTY_SUB; continue; }  // SURVEY A.4 fence
+        // a match that starts in the owned part must end inside owned + halo
+        if (halo_truncated_by_shard && span > halo + 1) { R.status[q] = VLGB_ERR_TOO_LARGE; continue; }
+        bool impossible = false;
+        for (uint32_t s = s0; s < s1; s++) {
+            uint64_t len = batch->pat_off[s + 1] - batch->pat_off[s];
+            if (len > idx->n) { impossible = true; continue; }  // longer than the shard: cannot occur
+            sub_pid[s] = dict.add(batch->pat_bytes + batch->pat_off[s], len);
+        }
+        if (impossible) continue;
+        plan.push_back({q, k, s0, R.ext.entry[q]});
+    }
+
+    // ---- scan: one sorted occurrence list per distinct subpattern
+    ScanOut so;
+    run_scan(c, idx->d_text, idx->n, idx->owned_len, dict, so);
+    BatchView view{batch, &sub_pid, &so, idx->global_offset};
+
+    // queries with an empty list have no match (vlg_index.hpp:316)
+    std::vector<PlanQuery> live;
+    for (const PlanQuery& pq : plan) {
+        uint64_t occ = 0;
+        bool any_empty = false;
+        for (uint32_t i = 0; i < pq.k; i++) {
+            uint64_t l = list_len(view, pq.s0 + i, false);
+            occ += l;
+            if (list_len(view, pq.s0 + i, i == 0) == 0) any_empty = true;
+        }
+        R.occ[pq.q] = occ;
+        if (!any_empty) live.push_back(pq);
+    }
+    std::stable_sort(live.begin(), live.end(), [](const PlanQuery& a, const PlanQuery& b) { return a.k > b.k; });
+
+    // ---- join + select, chunked by device memory
+    const uint64_t budget = c.join_budget ? c.join_budget : (uint64_t)24 << 30;
+    size_t i0 = 0;
+    while (i0 < live.size()) {
+        std::vector<uint64_t> depth_slots(live[i0].k + 1, 0);
+        uint64_t bytes = 0, sel_slots = 0;
+        size_t i1 = i0;
+        while (i1 < live.size()) {
+            const PlanQuery& pq = live[i1];
+            uint64_t qb = query_state_bytes(view, pq);
+            bool fits = (i1 == i0) || bytes + qb <= budget;
+            uint64_t sel = (list_len(view, pq.s0, true) + SEL_TILE - 1) / SEL_TILE * SEL_TILE;
+            if (sel_slots + sel >= 0xF0000000ull) fits = (i1 == i0);
+            for (uint32_t d = 1; d < pq.k && fits; d++)
+                if (depth_slots[d] + list_len(view, pq.s0 + pq.k - 1 - d, pq.k - 1 - d == 0) >= 0xF0000000ull) fits = (i1 == i0);
+            if (!fits) break;
+            for (uint32_t d = 1; d < pq.k; d++) depth_slots[d] += list_len(view, pq.s0 + pq.k - 1 - d, pq.k - 1 - d == 0);
+            sel_slots += sel;
+            bytes += qb;
+            i1++;
+        }
+        std::vector<PlanQuery> chunk(live.begin() + i0, live.begin() + i1);
+        ChunkOut co;
+        run_chunk(c, view, chunk, want, keep_device,
+                  [&](size_t nbytes) {
+                      HostBlock hb = pinned_pool().take(nbytes ? nbytes : 8);
+                      R.blocks.push_back(hb);
+                      return hb.p;
+                  },
+                  co);
+        for (size_t s = 0; s < chunk.size(); s++) {
+            uint32_t q = chunk[s].q;
+            R.counts[q] = co.counts[s];
+            R.exit_cursor[q] = co.exit_cursor[s];
+            R.ext.first_start[q] = co.first_start[s];
+        }
+        uint64_t m = 0;
+        for (size_t s = 0; s < chunk.size(); s++) {
+            uint32_t q = chunk[s].q;
+            if (co.counts[s]) {
+                if (co.h_starts) R.starts[q] = co.h_starts + m;
+                if (co.h_tuples) R.tuples[q] = co.h_tuples + co.tuple_off[s];
+            }
+            m += co.counts[s];
+        }
+        R.total += co.matches;
+        c.stats.query_chunks++;
+        i0 = i1;
+    }
+    c.stats.segments = 1;
+}
+
+}  // namespace
+
+extern "C" int vlgb_search_batch(const vlgb_index* idx, const vlgb_batch* batch, const uint64_t* entry_cursor,
+                                 uint32_t want, vlgb_result** out)
+{
+    if (!idx || !out) return fail(VLGB_ERR_ARG, "vlgb_search_batch: null argument");
+    *out = nullptr;
+    int rc = batch_check(batch);
+    if (rc) return rc;
+    if ((want & 3u) > VLGB_WANT_TUPLES) return fail(VLGB_ERR_ARG, "vlgb_search_batch: bad `want`");
+    try {
+        ensure_ready();
+        Context& c = ctx();
+        c.flush_timers();
+        memset(&c.stats, 0, sizeof c.stats);
+        std::unique_ptr<ResultImpl> R(new ResultImpl());
+        try {
+            do_search(c, idx, batch, entry_cursor, want, *R);
+        } catch (...) {
+            for (auto& b : R->blocks) pinned_pool().give(b);
+            throw;
+        }
+        copy_batch(batch, R->ext.batch);
+        *out = R.release();
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    } catch (const std::bad_alloc&) {
+        return fail(VLGB_ERR_NOMEM, "out of host memory");
+    }
+}
+
+extern "C" uint32_t vlgb_result_queries(const vlgb_result* r) { return r ? r->nq : 0; }
+extern "C" int32_t vlgb_result_status(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->status[q] : VLGB_ERR_ARG; }
+extern "C" uint64_t vlgb_result_count(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->counts[q] : 0; }
+extern "C" uint64_t vlgb_result_total(const vlgb_result* r) { return r ? r->total : 0; }
+extern "C" const uint64_t* vlgb_result_counts(const vlgb_result* r) { return r ? r->counts.data() : nullptr; }
+extern "C" const uint64_t* vlgb_result_starts(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->starts[q] : nullptr; }
+extern "C" const uint64_t* vlgb_result_tuples(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->tuples[q] : nullptr; }
+extern "C" const uint64_t* vlgb_result_exit_cursors(const vlgb_result* r) { return r ? r->exit_cursor.data() : nullptr; }
+extern "C" const uint64_t* vlgb_result_first_starts(const vlgb_result* r)
+{
+    return r ? static_cast<const ResultImpl*>(r)->ext.first_start.data() : nullptr;
+}
+extern "C" uint64_t vlgb_result_occurrences(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->occ[q] : 0; }
+
+extern "C" void vlgb_result_free(vlgb_result* r)
+{
+    if (!r) return;
+    for (auto& b : r->blocks) pinned_pool().give(b);
+    delete static_cast<ResultImpl*>(r);
+}
+
+// Re-enter the shard with the true cursors.  A query is re-searched only when its reported set can
+// change: the orbit of succ() depends on the entry cursor only through its first element
+// (SURVEY A.3/A.5), so an entry that still lies at or before the first reported start (and not before
+// the entry the result was computed with) leaves every match in place.
+extern "C" int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, uint32_t* n_changed)
+{
+    if (!r || !entry_cursor) return fail(VLGB_ERR_ARG, "vlgb_result_fixup: null argument");
+    ResultImpl& R = *static_cast<ResultImpl*>(r);
+    if (n_changed) *n_changed = 0;
+    std::vector<uint32_t> redo;
+    for (uint32_t q = 0; q < R.nq; q++) {
+        if (R.status[q] != VLGB_OK) continue;
+        const uint64_t e_old = R.ext.entry[q], e_new = entry_cursor[q];
+        if (e_new == e_old) continue;
+        if (e_new > e_old && (R.counts[q] == 0 || e_new <= R.ext.first_start[q])) {
+            if (R.counts[q] == 0) R.exit_cursor[q] = e_new;
+            R.ext.entry[q] = e_new;
+            continue;
+        }
+        redo.push_back(q);
+    }
+    if (redo.empty()) return VLGB_OK;
+    OwnedBatch sub;
+    std::vector<uint64_t> sub_entry;
+    const vlgb_batch& B = R.ext.batch.pub;
+    sub.sub_off.push_back(0);
+    sub.pat_off.push_back(0);
+    for (uint32_t q : redo) {
+        for (uint32_t s = B.sub_off[q]; s < B.sub_off[q + 1]; s++) {
+            sub.bytes.insert(sub.bytes.end(), B.pat_bytes + B.pat_off[s], B.pat_bytes + B.pat_off[s + 1]);
+            sub.pat_off.push_back(sub.bytes.size());
+            sub.gmin.push_back(B.gap_min[s]);
+            sub.gmax.push_back(B.gap_max[s]);
+        }
+        sub.sub_off.push_back((uint32_t)(sub.pat_off.size() - 1));
+        sub_entry.push_back(entry_cursor[q]);
+    }
+    sub.seal();
+    vlgb_result* nr = nullptr;
+    vlgb_stats keep = ctx().stats;
+    int rc = vlgb_search_batch(R.ext.idx, &sub.pub, sub_entry.data(), R.want, &nr);
+    ctx().flush_timers();
+    ctx().stats = keep;
+    if (rc) return rc;
+    ResultImpl& N = *static_cast<ResultImpl*>(nr);
+    for (size_t i = 0; i < redo.size(); i++) {
+        uint32_t q = redo[i];
+        R.total = R.total - R.counts[q] + N.counts[i];
+        R.counts[q] = N.counts[i];
+        R.exit_cursor[q] = N.exit_cursor[i];
+        R.starts[q] = N.starts[i];
+        R.tuples[q] = N.tuples[i];
+        R.status[q] = N.status[i];
+        R.ext.entry[q] = entry_cursor[q];
+        R.ext.first_start[q] = N.ext.first_start[i];
+    }
+    for (auto& b : N.blocks) R.blocks.push_back(b);  // the spliced lists live in the new result's blocks
+    N.blocks.clear();
+    vlgb_result_free(nr);
+    if (n_changed) *n_changed = (uint32_t)redo.size();
+    return VLGB_OK;
+}

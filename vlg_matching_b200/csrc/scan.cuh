@@ -64,8 +64,9 @@ struct ScanArgs {
     const uint32_t* long_len;  // [s_act] full length (class 9 only)
     const uint32_t* long_off;  // [s_act] offset into long_blob
     const uint8_t* long_blob;
-    uint32_t* matrix;        // [rows][s_stride]: counts (pass 1 out) / write cursors (pass 2 in)
-    uint32_t* out;           // pass 2: positions (u32, segment-local)
+    uint32_t* matrix;        // [rows][s_stride]: counts (pass 1 out) / write cursors inside each list (pass 2 in)
+    const uint64_t* list_base;  // pass 2: [s_act] first word of every list inside `out`
+    uint32_t* out;           // pass 2: positions (u32, shard-local)
 };
 
 __device__ __forceinline__ uint64_t load_window(const uint8_t* p)
@@ -155,8 +156,11 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) scan_kernel(ScanArgs a)
                                         if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
                                 }
                             }
-                            if (ok) { pid = cand; break; }
-                            if (c < 9) break;
+                            // one candidate per round, hit or miss: lanes holding the same key walk the
+                            // same slot sequence, so each pattern is emitted in one round per step and
+                            // its list stays sorted
+                            if (ok) pid = cand;
+                            break;
                         }
                     }
                 }
@@ -173,7 +177,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32) scan_kernel(ScanArgs a)
                         cur[pid] = old + __popc(grp);
                     }
                     old = __shfl_sync(0xffffffffu, old, leader);
-                    if (pid != NONE32) a.out[old + rank] = p;
+                    if (pid != NONE32) a.out[__ldg(a.list_base + pid) + old + rank] = p;
                     __syncwarp();
                 }
             } while (c == 9 && __any_sync(0xffffffffu, more));
@@ -197,56 +201,28 @@ __global__ void scan_colsum_kernel(const uint32_t* matrix, uint32_t rows, uint32
     part[(size_t)blockIdx.y * stride + pid] = s;
 }
 
-// one block of `stride` (<= 1024) threads: part -> exclusive prefix over row-blocks (in place),
-// total[pid], base[pid] = exclusive prefix of totals over pid (list start inside the pass buffer)
-__global__ void scan_colbase_kernel(uint32_t* part, uint32_t nrb, uint32_t stride, uint32_t* total, uint32_t* base)
+// part -> exclusive prefix over row-blocks (in place), total[pid] = list length
+__global__ void scan_colbase_kernel(uint32_t* part, uint32_t nrb, uint32_t stride, uint32_t* total)
 {
-    __shared__ uint32_t warp_sums[32];
-    __shared__ uint32_t grand;
-    uint32_t pid = threadIdx.x;
+    uint32_t pid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pid >= stride) return;
     uint32_t run = 0;
-    if (pid < stride) {
-        for (uint32_t rb = 0; rb < nrb; rb++) {
-            uint32_t v = part[(size_t)rb * stride + pid];
-            part[(size_t)rb * stride + pid] = run;
-            run += v;
-        }
-        total[pid] = run;
+    for (uint32_t rb = 0; rb < nrb; rb++) {
+        uint32_t v = part[(size_t)rb * stride + pid];
+        part[(size_t)rb * stride + pid] = run;
+        run += v;
     }
-    // exclusive scan of `run` over the block
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t inc = run;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc += o;
-    }
-    if (lane == 31) warp_sums[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t wv = (lane < (int)(blockDim.x >> 5)) ? warp_sums[lane] : 0u;
-        uint32_t winc = wv;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t o = __shfl_up_sync(0xffffffffu, winc, d);
-            if (lane >= d) winc += o;
-        }
-        warp_sums[lane] = winc - wv;
-        if (lane == 31) grand = winc;
-    }
-    __syncthreads();
-    if (pid < stride) base[pid] = warp_sums[warp] + inc - run;
-    if (threadIdx.x == 0) base[stride] = grand;
+    total[pid] = run;
 }
 
-// matrix[r][pid] <- base[pid] + part[rb][pid] + (prefix of the counts inside the row-block)
-__global__ void scan_rowoff_kernel(uint32_t* matrix, uint32_t rows, uint32_t stride, const uint32_t* part,
-                                   const uint32_t* base)
+// matrix[r][pid] <- part[rb][pid] + (prefix of the counts inside the row-block) = write cursor of row r
+// inside list pid
+__global__ void scan_rowoff_kernel(uint32_t* matrix, uint32_t rows, uint32_t stride, const uint32_t* part)
 {
     uint32_t pid = blockIdx.x * blockDim.x + threadIdx.x;
     if (pid >= stride) return;
     uint32_t r0 = blockIdx.y * SCAN_RB, r1 = min(rows, r0 + SCAN_RB);
-    uint32_t run = base[pid] + part[(size_t)blockIdx.y * stride + pid];
+    uint32_t run = part[(size_t)blockIdx.y * stride + pid];
     for (uint32_t r = r0; r < r1; r++) {
         uint32_t c = matrix[(size_t)r * stride + pid];
         matrix[(size_t)r * stride + pid] = run;
@@ -255,7 +231,7 @@ __global__ void scan_rowoff_kernel(uint32_t* matrix, uint32_t rows, uint32_t str
 }
 
 // owned[pid] = number of positions < owned_len in list pid (lists are sorted)
-__global__ void scan_owned_kernel(const uint32_t* pos, const uint32_t* base, const uint32_t* total, uint32_t s_act,
+__global__ void scan_owned_kernel(const uint32_t* pos, const uint64_t* base, const uint32_t* total, uint32_t s_act,
                                   uint32_t owned_len, uint32_t* owned)
 {
     uint32_t pid = blockIdx.x * blockDim.x + threadIdx.x;

@@ -1,0 +1,557 @@
+// search.cuh — host orchestration of one vlgb_search_batch call:
+//   scan   (scan.cuh)    text shard -> one sorted occurrence list per distinct subpattern of the batch
+//   join   (join.cuh)    right-to-left viability + next pointers, one launch set per depth
+//   select (select.cuh)  greedy non-overlapping selection, prefix-sum compaction, tuple resolve
+// Replaces the per-query body of locate()/count() (include/sdsl/vlg_index.hpp:395-411) and
+// index_wcsearch3::search (benchmark/gapped-matching/include/index_wcsearch3.hpp:399-422) for a whole
+// batch.  Host work is bookkeeping only (sizes, offsets, pointers); every position is produced on the
+// device.  Two host<->device synchronisations per batch for the scan (list sizes) and one per query
+// chunk (match counts) are the only places where sizes travel to the host.
+#pragma once
+#include <algorithm>
+#include <memory>
+#include <numeric>
+
+#include "common.cuh"
+#include "prefix.cuh"
+#include "scan.cuh"
+#include "join.cuh"
+#include "select.cuh"
+
+namespace vlgb {
+
+// host blob that becomes one H2D copy; offsets are 256-byte aligned
+struct Packer {
+    std::vector<uint8_t> host;
+    template <class T>
+    size_t put(const T* src, size_t n)
+    {
+        size_t off = (host.size() + 255) & ~size_t(255);
+        host.resize(off + n * sizeof(T));
+        if (n) memcpy(host.data() + off, src, n * sizeof(T));
+        return off;
+    }
+    template <class T>
+    size_t put(const std::vector<T>& v)
+    {
+        return put(v.data(), v.size());
+    }
+    size_t size() const { return (host.size() + 255) & ~size_t(255); }
+};
+
+template <class T>
+inline T* dev_at(uint8_t* base, size_t off)
+{
+    return reinterpret_cast<T*>(base + off);
+}
+
+// ---------------------------------------------------------------------------------------------
+// scan stage
+// ---------------------------------------------------------------------------------------------
+struct ScanOut {
+    std::vector<uint32_t> tot;   // list length per distinct pattern
+    std::vector<uint32_t> own;   // entries < owned_len
+    std::vector<uint64_t> base;  // first word inside d_lists
+    uint32_t* d_lists = nullptr;
+    uint64_t total_words = 0;
+};
+
+inline uint32_t scan_chunk_for(uint64_t n)
+{
+    uint64_t c = (n / 8192 + 31) & ~uint64_t(31);
+    if (c < 1024) c = 1024;
+    if (c > 16384) c = 16384;
+    return (uint32_t)c;
+}
+
+inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t owned_len, const PatternDict& dict,
+                     ScanOut& so)
+{
+    const uint32_t P = (uint32_t)dict.pats.size();
+    so.tot.assign(P, 0);
+    so.own.assign(P, 0);
+    so.base.assign(P + 1, 0);
+    so.d_lists = nullptr;
+    so.total_words = 0;
+    if (P == 0 || n == 0) return;
+
+    const uint32_t npass = (P + SCAN_S - 1) / SCAN_S;
+    const uint32_t chunk = scan_chunk_for(n);
+    const uint32_t rows = (uint32_t)((n + chunk - 1) / chunk);
+    const uint32_t nrb = (rows + SCAN_RB - 1) / SCAN_RB;
+    const size_t smem = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_S * sizeof(uint32_t);
+    static thread_local bool attr_set = false;
+    if (!attr_set) {
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+
+    struct PassDev {
+        uint32_t s_act, stride;
+        size_t o_tables, o_len, o_off, o_blob, o_base;  // inside the control blob
+        uint32_t *matrix, *part, *total;
+    };
+    std::vector<PassDev> pd(npass);
+    Packer ctl;
+    std::unique_ptr<PassHost> ph(new PassHost());
+    size_t work_bytes = 0;
+    for (uint32_t p = 0; p < npass; p++) {
+        uint32_t first = p * SCAN_S, cnt = std::min<uint32_t>(SCAN_S, P - first);
+        build_pass(dict, first, cnt, *ph);
+        pd[p].s_act = cnt;
+        pd[p].stride = (cnt + 31) & ~31u;
+        pd[p].o_tables = ctl.put(&ph->tables, 1);
+        pd[p].o_len = ctl.put(ph->long_len);
+        pd[p].o_off = ctl.put(ph->long_off);
+        ph->long_blob.append(16, '\0');
+        pd[p].o_blob = ctl.put(ph->long_blob.data(), ph->long_blob.size());
+        std::vector<uint64_t> zero(cnt, 0);
+        pd[p].o_base = ctl.put(zero);
+        work_bytes += Arena::padded((size_t)rows * pd[p].stride, 4) + Arena::padded((size_t)nrb * pd[p].stride, 4) +
+                      Arena::padded(pd[p].stride, 4);
+    }
+    const size_t o_allbase = ctl.put(so.base);  // P+1 u64, filled later (owned kernel)
+    work_bytes += 2 * Arena::padded(P, 4);      // owned[], totals[]
+    c.scan_arena.reserve(ctl.size() + work_bytes + 4096);
+    uint8_t* d_ctl = c.scan_arena.take<uint8_t>(ctl.size());
+    VLGB_CUDA(cudaMemcpyAsync(d_ctl, ctl.host.data(), ctl.host.size(), cudaMemcpyHostToDevice, c.stream));
+    c.stats.h2d_bytes += ctl.host.size();
+    for (uint32_t p = 0; p < npass; p++) {
+        pd[p].matrix = c.scan_arena.take<uint32_t>((size_t)rows * pd[p].stride);
+        pd[p].part = c.scan_arena.take<uint32_t>((size_t)nrb * pd[p].stride);
+        pd[p].total = c.scan_arena.take<uint32_t>(pd[p].stride);
+    }
+    uint32_t* d_owned = c.scan_arena.take<uint32_t>(P);
+
+    auto args_for = [&](uint32_t p) {
+        ScanArgs a;
+        a.text = d_text;
+        a.valid_len = (uint32_t)n;
+        a.chunk = chunk;
+        a.rows = rows;
+        a.s_act = pd[p].s_act;
+        a.s_stride = pd[p].stride;
+        a.tables = dev_at<const ScanTables>(d_ctl, pd[p].o_tables);
+        a.long_len = dev_at<const uint32_t>(d_ctl, pd[p].o_len);
+        a.long_off = dev_at<const uint32_t>(d_ctl, pd[p].o_off);
+        a.long_blob = dev_at<const uint8_t>(d_ctl, pd[p].o_blob);
+        a.matrix = pd[p].matrix;
+        a.list_base = dev_at<const uint64_t>(d_ctl, pd[p].o_base);
+        a.out = nullptr;
+        return a;
+    };
+    const uint32_t grid = (rows + SCAN_WARPS - 1) / SCAN_WARPS;
+
+    // pass 1: counts, then per-row write cursors
+    for (uint32_t p = 0; p < npass; p++) {
+        ScanArgs a = args_for(p);
+        c.begin(ST_SCAN_COUNT);
+        scan_kernel<false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        c.end(ST_SCAN_COUNT, 1, n + (uint64_t)rows * pd[p].s_act * 4);
+        c.begin(ST_SCAN_OFFSETS);
+        dim3 g((pd[p].stride + 127) / 128, nrb);
+        scan_colsum_kernel<<<g, 128, 0, c.stream>>>(pd[p].matrix, rows, pd[p].stride, pd[p].part);
+        scan_colbase_kernel<<<(pd[p].stride + 127) / 128, 128, 0, c.stream>>>(pd[p].part, nrb, pd[p].stride, pd[p].total);
+        scan_rowoff_kernel<<<g, 128, 0, c.stream>>>(pd[p].matrix, rows, pd[p].stride, pd[p].part);
+        c.end(ST_SCAN_OFFSETS, 3, (uint64_t)rows * pd[p].stride * 12);
+        VLGB_CUDA(cudaMemcpyAsync(so.tot.data() + p * SCAN_S, pd[p].total, pd[p].s_act * 4, cudaMemcpyDeviceToHost,
+                                  c.stream));
+        c.stats.d2h_bytes += pd[p].s_act * 4;
+    }
+    VLGB_CUDA(cudaGetLastError());
+    VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync 1: list sizes
+
+    uint64_t words = 0;
+    for (uint32_t i = 0; i < P; i++) {
+        so.base[i] = words;
+        words += ((uint64_t)so.tot[i] + 3) & ~3ull;  // 16-byte aligned list starts
+    }
+    so.base[P] = words;
+    so.total_words = words;
+    c.list_arena.reserve(words * 4 + 4096);
+    so.d_lists = c.list_arena.take<uint32_t>(words + 16);
+    for (uint32_t p = 0; p < npass; p++)
+        VLGB_CUDA(cudaMemcpyAsync(d_ctl + pd[p].o_base, so.base.data() + p * SCAN_S, pd[p].s_act * 8,
+                                  cudaMemcpyHostToDevice, c.stream));
+    VLGB_CUDA(cudaMemcpyAsync(d_ctl + o_allbase, so.base.data(), (P + 1) * 8, cudaMemcpyHostToDevice, c.stream));
+    c.stats.h2d_bytes += (uint64_t)P * 16 + 8;
+
+    // pass 2: fill
+    uint64_t occ = 0;
+    for (uint32_t i = 0; i < P; i++) occ += so.tot[i];
+    c.stats.total_occurrences += occ;
+    for (uint32_t p = 0; p < npass; p++) {
+        uint64_t pocc = 0;
+        for (uint32_t i = 0; i < pd[p].s_act; i++) pocc += so.tot[p * SCAN_S + i];
+        ScanArgs a = args_for(p);
+        a.out = so.d_lists;
+        c.begin(ST_SCAN_FILL);
+        if (pocc) scan_kernel<true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        c.end(ST_SCAN_FILL, pocc ? 1 : 0, pocc ? n + (uint64_t)rows * pd[p].s_act * 4 + pocc * 4 : 0);
+    }
+    c.stats.scan_passes += npass;
+    c.stats.distinct_patterns += P;
+
+    if (owned_len >= n) {
+        so.own = so.tot;
+    } else {
+        // totals of all patterns, contiguous on the device for the owned-prefix search
+        uint32_t* d_tot = c.scan_arena.take<uint32_t>(P);
+        VLGB_CUDA(cudaMemcpyAsync(d_tot, so.tot.data(), (size_t)P * 4, cudaMemcpyHostToDevice, c.stream));
+        scan_owned_kernel<<<(P + 127) / 128, 128, 0, c.stream>>>(so.d_lists, dev_at<const uint64_t>(d_ctl, o_allbase), d_tot,
+                                                                 P, (uint32_t)owned_len, d_owned);
+        VLGB_CUDA(cudaMemcpyAsync(so.own.data(), d_owned, (size_t)P * 4, cudaMemcpyDeviceToHost, c.stream));
+        VLGB_CUDA(cudaGetLastError());
+        VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync 2 (sharded texts only)
+        c.stats.h2d_bytes += (uint64_t)P * 4;
+        c.stats.d2h_bytes += (uint64_t)P * 4;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// join + select stage for one chunk of queries
+// ---------------------------------------------------------------------------------------------
+struct PlanQuery {
+    uint32_t q;        // index in the batch
+    uint32_t k;
+    uint32_t s0;       // first subpattern (batch numbering)
+    uint64_t entry;    // whole-text entry cursor
+};
+
+struct ChunkOut {  // per query of the chunk, chunk order
+    std::vector<uint64_t> counts, exit_cursor, first_start;
+    uint64_t matches = 0, tuple_words = 0;
+    uint64_t* h_starts = nullptr;  // pinned (inside block)
+    uint64_t* h_tuples = nullptr;
+    std::vector<uint64_t> tuple_off;
+};
+
+struct BatchView {
+    const vlgb_batch* b;
+    const std::vector<uint32_t>* sub_pid;
+    const ScanOut* so;
+    uint64_t global_offset;
+};
+
+inline uint64_t list_len(const BatchView& v, uint32_t sub, bool level0)
+{
+    uint32_t pid = (*v.sub_pid)[sub];
+    return level0 ? v.so->own[pid] : v.so->tot[pid];
+}
+
+// bytes of device state a query needs in the join/select stage (upper bound, used for chunking)
+inline uint64_t query_state_bytes(const BatchView& v, const PlanQuery& pq)
+{
+    uint64_t slots = 0;
+    for (uint32_t i = 0; i + 1 < pq.k; i++) slots += list_len(v, pq.s0 + i, i == 0);
+    uint64_t sel = (list_len(v, pq.s0, true) + SEL_TILE - 1) / SEL_TILE * SEL_TILE;
+    return slots * 28 + sel * 14 + 1024;
+}
+
+// `qs` sorted by k descending.  Results land in `co`; starts/tuples (if wanted) in the pinned block
+// `hb` (grown by the caller-supplied allocator).
+template <class PinnedAlloc>
+inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuery>& qs, uint32_t want, bool keep_device,
+                      PinnedAlloc&& pinned_alloc, ChunkOut& co)
+{
+    const uint32_t nq = (uint32_t)qs.size();
+    const uint32_t kmax = qs[0].k;
+    const vlgb_batch& B = *v.b;
+    const ScanOut& so = *v.so;
+    auto list_ptr = [&](uint32_t sub) { return (const uint32_t*)(so.d_lists + so.base[(*v.sub_pid)[sub]]); };
+    auto plen = [&](uint32_t sub) { return B.pat_off[sub + 1] - B.pat_off[sub]; };
+
+    // ---- sizes per depth
+    struct DepthHost {
+        uint32_t nseg = 0;
+        std::vector<uint32_t> slot_off;
+        std::vector<const uint32_t*> left, right_list;
+        std::vector<uint32_t> right_len;
+        std::vector<uint64_t> lo, hi;
+        size_t o_slot_off, o_left, o_right_list, o_right_len, o_lo, o_hi;
+        uint32_t *vpos, *vnxt, *vlast, *vseg;
+    };
+    std::vector<DepthHost> dh(kmax);  // index 1 .. kmax-1
+    uint64_t max_slots = 0;
+    for (uint32_t d = 1; d < kmax; d++) {
+        DepthHost& h = dh[d];
+        uint32_t nseg = 0;
+        while (nseg < nq && qs[nseg].k > d) nseg++;
+        h.nseg = nseg;
+        h.slot_off.resize(nseg + 1);
+        h.left.resize(nseg);
+        h.lo.resize(nseg);
+        h.hi.resize(nseg);
+        if (d == 1) {
+            h.right_list.resize(nseg);
+            h.right_len.resize(nseg);
+        }
+        uint64_t run = 0;
+        for (uint32_t s = 0; s < nseg; s++) {
+            const PlanQuery& pq = qs[s];
+            uint32_t lvl = pq.k - 1 - d, sub = pq.s0 + lvl;
+            h.slot_off[s] = (uint32_t)run;
+            run += list_len(v, sub, lvl == 0);
+            h.left[s] = list_ptr(sub);
+            h.lo[s] = sat_add64(B.gap_min[sub], plen(sub));  // start-to-start bounds, vlg_index.hpp:95
+            h.hi[s] = sat_add64(B.gap_max[sub], plen(sub));
+            if (d == 1) {
+                h.right_list[s] = list_ptr(pq.s0 + pq.k - 1);
+                h.right_len[s] = (uint32_t)list_len(v, pq.s0 + pq.k - 1, false);
+            }
+        }
+        if (run >= 0xFFFF0000ull) throw CudaError{cudaErrorInvalidValue, __FILE__, __LINE__};  // chunking keeps this away
+        h.slot_off[nseg] = (uint32_t)run;
+        max_slots = std::max(max_slots, run);
+        c.stats.join_slots += run;
+    }
+
+    // ---- selection layout
+    std::vector<uint32_t> sel_off(nq + 1), kq(nq), last_len(nq), list0_len(nq);
+    std::vector<uint64_t> entry_local(nq), exit_init(nq), first_init(nq, ~uint64_t(0));
+    std::vector<const uint32_t*> list0(nq), last_list(nq);
+    uint64_t sel_run = 0;
+    for (uint32_t s = 0; s < nq; s++) {
+        const PlanQuery& pq = qs[s];
+        sel_off[s] = (uint32_t)sel_run;
+        uint64_t l0 = list_len(v, pq.s0, true);
+        sel_run += (l0 + SEL_TILE - 1) / SEL_TILE * SEL_TILE;
+        kq[s] = pq.k;
+        uint64_t ll = plen(pq.s0 + pq.k - 1);
+        last_len[s] = ll > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)ll;
+        entry_local[s] = pq.entry > v.global_offset ? pq.entry - v.global_offset : 0;
+        exit_init[s] = pq.entry;
+        list0[s] = list_ptr(pq.s0);
+        list0_len[s] = (uint32_t)l0;
+        last_list[s] = list_ptr(pq.s0 + pq.k - 1);
+    }
+    if (sel_run >= 0xFFFF0000ull) throw CudaError{cudaErrorInvalidValue, __FILE__, __LINE__};
+    sel_off[nq] = (uint32_t)sel_run;
+    const uint32_t sel_total = (uint32_t)sel_run;
+    const uint32_t ntiles = sel_total / SEL_TILE;
+
+    // ---- control blob
+    Packer ctl;
+    for (uint32_t d = 1; d < kmax; d++) {
+        DepthHost& h = dh[d];
+        h.o_slot_off = ctl.put(h.slot_off);
+        h.o_left = ctl.put(h.left);
+        h.o_lo = ctl.put(h.lo);
+        h.o_hi = ctl.put(h.hi);
+        if (d == 1) {
+            h.o_right_list = ctl.put(h.right_list);
+            h.o_right_len = ctl.put(h.right_len);
+        }
+    }
+    const size_t o_sel_off = ctl.put(sel_off), o_kq = ctl.put(kq), o_last_len = ctl.put(last_len),
+                 o_entry = ctl.put(entry_local), o_exit = ctl.put(exit_init), o_first = ctl.put(first_init), o_list0 = ctl.put(list0),
+                 o_list0_len = ctl.put(list0_len), o_last_list = ctl.put(last_list);
+    std::vector<const uint32_t*> tab(4 * MAX_K, nullptr);  // depth_vpos | depth_vnxt | depth_vlast | depth_vseg
+    const size_t o_tab = ctl.put(tab);                     // patched below once the arena addresses are known
+    std::vector<uint64_t> zeros64(nq, 0);
+    const size_t o_tuple_off = ctl.put(zeros64);
+
+    // ---- device memory
+    size_t need = ctl.size() + 4096;
+    need += Arena::padded(max_slots, 4) + Arena::padded(max_slots + 1, 4);  // raw, rank
+    for (uint32_t d = 1; d < kmax; d++)
+        need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
+    need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
+    need += 2 * Arena::padded(sel_total, 4) + Arena::padded(sel_total, 1);             // succ, exitp, flags
+    need += Arena::padded(ntiles + 1, 4) + Arena::padded((size_t)sel_total + 1, 4);    // entry, mrank
+    need += Arena::padded(nq, 8) + Arena::padded(kmax + 1, 4);                         // counts, viable totals
+    const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(max_slots, sel_total));
+    need += Arena::padded(scratch_words, 4);
+    c.join_arena.reserve(need);
+    Arena& A = c.join_arena;
+    uint8_t* d_ctl = A.take<uint8_t>(ctl.size());
+    uint32_t* raw = A.take<uint32_t>(max_slots);
+    uint32_t* rank = A.take<uint32_t>(max_slots + 1);
+    for (uint32_t d = 1; d < kmax; d++) {
+        size_t t = dh[d].slot_off[dh[d].nseg];
+        dh[d].vpos = A.take<uint32_t>(t);
+        dh[d].vnxt = A.take<uint32_t>(t);
+        dh[d].vlast = A.take<uint32_t>(t);
+        dh[d].vseg = A.take<uint32_t>(dh[d].nseg + 1);
+        tab[0 * MAX_K + d] = dh[d].vpos;
+        tab[1 * MAX_K + d] = dh[d].vnxt;
+        tab[2 * MAX_K + d] = dh[d].vlast;
+        tab[3 * MAX_K + d] = dh[d].vseg;
+    }
+    memcpy(ctl.host.data() + o_tab, tab.data(), tab.size() * sizeof(tab[0]));
+    const uint32_t** d_v0 = A.take<const uint32_t*>(nq);
+    const uint32_t** d_vlast = A.take<const uint32_t*>(nq);
+    uint32_t* d_v0_len = A.take<uint32_t>(nq);
+    uint32_t* d_t0 = A.take<uint32_t>(nq);
+    uint32_t* d_succ = A.take<uint32_t>(sel_total);
+    uint32_t* d_exitp = A.take<uint32_t>(sel_total);
+    uint8_t* d_flags = A.take<uint8_t>(sel_total);
+    uint32_t* d_entry = A.take<uint32_t>(ntiles + 1);
+    uint32_t* d_mrank = A.take<uint32_t>((size_t)sel_total + 1);
+    uint64_t* d_counts = A.take<uint64_t>(nq);
+    uint32_t* d_viable = A.take<uint32_t>(kmax + 1);
+    uint32_t* scratch = A.take<uint32_t>(scratch_words);
+
+    VLGB_CUDA(cudaMemcpyAsync(d_ctl, ctl.host.data(), ctl.host.size(), cudaMemcpyHostToDevice, c.stream));
+    c.stats.h2d_bytes += ctl.host.size();
+
+    // ---- join, depth by depth
+    for (uint32_t d = 1; d < kmax; d++) {
+        DepthHost& h = dh[d];
+        DepthDesc D;
+        D.nseg = h.nseg;
+        D.total_slots = h.slot_off[h.nseg];
+        D.slot_off = dev_at<const uint32_t>(d_ctl, h.o_slot_off);
+        D.left = dev_at<const uint32_t* const>(d_ctl, h.o_left);
+        D.right_list = d == 1 ? dev_at<const uint32_t* const>(d_ctl, h.o_right_list) : nullptr;
+        D.right_len = d == 1 ? dev_at<const uint32_t>(d_ctl, h.o_right_len) : nullptr;
+        D.prev_vpos = d > 1 ? dh[d - 1].vpos : nullptr;
+        D.prev_vlast = d > 1 ? dh[d - 1].vlast : nullptr;
+        D.prev_vseg = d > 1 ? dh[d - 1].vseg : nullptr;
+        D.lo = dev_at<const uint64_t>(d_ctl, h.o_lo);
+        D.hi = dev_at<const uint64_t>(d_ctl, h.o_hi);
+        D.raw = raw;
+        D.rank = rank;
+        D.vpos = h.vpos;
+        D.vnxt = h.vnxt;
+        D.vlast = h.vlast;
+        D.vseg = h.vseg;
+        const uint32_t T = D.total_slots;
+        if (T == 0) {
+            VLGB_CUDA(cudaMemsetAsync(h.vseg, 0, (h.nseg + 1) * 4, c.stream));
+            VLGB_CUDA(cudaMemsetAsync(d_viable + d, 0, 4, c.stream));
+            continue;
+        }
+        const uint32_t grid = (T + JOIN_THREADS - 1) / JOIN_THREADS;
+        c.begin(ST_JOIN_PROBE);
+        join_probe_kernel<<<grid, JOIN_THREADS, 0, c.stream>>>(D);
+        c.end(ST_JOIN_PROBE, 1, (uint64_t)T * 12);
+        c.begin(ST_JOIN_COMPACT);
+        uint32_t l = exclusive_scan(FlagNotNone{raw}, T, rank, scratch, c.stream);
+        join_compact_kernel<<<grid, JOIN_THREADS, 0, c.stream>>>(D);
+        join_vseg_kernel<<<(h.nseg + 1 + 127) / 128, 128, 0, c.stream>>>(D);
+        c.end(ST_JOIN_COMPACT, l + 2, (uint64_t)T * (8 + 4 + 8));
+        VLGB_CUDA(cudaMemcpyAsync(d_viable + d, rank + T, 4, cudaMemcpyDeviceToDevice, c.stream));
+    }
+
+    // ---- selection
+    SelDesc S;
+    S.nq = nq;
+    S.total_slots = sel_total;
+    S.sel_off = dev_at<const uint32_t>(d_ctl, o_sel_off);
+    S.kq = dev_at<const uint32_t>(d_ctl, o_kq);
+    S.last_len = dev_at<const uint32_t>(d_ctl, o_last_len);
+    S.entry_local = dev_at<const uint64_t>(d_ctl, o_entry);
+    S.list0 = dev_at<const uint32_t* const>(d_ctl, o_list0);
+    S.list0_len = dev_at<const uint32_t>(d_ctl, o_list0_len);
+    S.depth_vpos = dev_at<const uint32_t* const>(d_ctl, o_tab);
+    S.depth_vnxt = S.depth_vpos + MAX_K;
+    S.depth_vlast = S.depth_vpos + 2 * MAX_K;
+    S.depth_vseg = S.depth_vpos + 3 * MAX_K;
+    S.last_list = dev_at<const uint32_t* const>(d_ctl, o_last_list);
+    S.global_offset = v.global_offset;
+    S.v0 = d_v0;
+    S.vlast = d_vlast;
+    S.v0_len = d_v0_len;
+    S.t0 = d_t0;
+    S.succ = d_succ;
+    S.exitp = d_exitp;
+    S.flags = d_flags;
+    S.entry = d_entry;
+    S.mrank = d_mrank;
+    S.tuple_off = dev_at<const uint64_t>(d_ctl, o_tuple_off);
+    S.starts = nullptr;
+    S.tuples = nullptr;
+    S.exit_cursor = dev_at<uint64_t>(d_ctl, o_exit);
+    S.first_start = dev_at<uint64_t>(d_ctl, o_first);
+    S.counts = d_counts;
+
+    co.counts.assign(nq, 0);
+    co.exit_cursor = exit_init;
+    co.first_start = first_init;
+    co.tuple_off.assign(nq, 0);
+    co.matches = co.tuple_words = 0;
+    co.h_starts = co.h_tuples = nullptr;
+    std::vector<uint32_t> viable(kmax + 1, 0);
+
+    if (sel_total) {
+        c.begin(ST_SELECT_SUCC);
+        sel_resolve_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
+        sel_succ_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
+        c.end(ST_SELECT_SUCC, 2, (uint64_t)sel_total * 12);
+        c.begin(ST_SELECT_TILE);
+        sel_tile_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
+        c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 8);
+        c.begin(ST_SELECT_WALK);
+        VLGB_CUDA(cudaMemsetAsync(d_entry, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
+        VLGB_CUDA(cudaMemsetAsync(d_flags, 0, sel_total, c.stream));
+        sel_walk_kernel<<<(nq + 31) / 32, 32, 0, c.stream>>>(S);
+        sel_mark_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
+        c.end(ST_SELECT_WALK, 2, (uint64_t)sel_total * 5);
+        c.begin(ST_EMIT);
+        uint32_t l = exclusive_scan(FlagByte{d_flags}, sel_total, d_mrank, scratch, c.stream);
+        sel_counts_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
+        c.end(ST_EMIT, l + 1, (uint64_t)sel_total * 6);
+        VLGB_CUDA(cudaMemcpyAsync(co.counts.data(), d_counts, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+        if (kmax > 1)
+            VLGB_CUDA(cudaMemcpyAsync(viable.data(), d_viable, (size_t)(kmax + 1) * 4, cudaMemcpyDeviceToHost, c.stream));
+        VLGB_CUDA(cudaGetLastError());
+        VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: match counts
+        c.stats.d2h_bytes += (uint64_t)nq * 8 + (kmax + 1) * 4;
+        for (uint32_t d = 1; d < kmax; d++) c.stats.bytes[ST_JOIN_COMPACT] += (uint64_t)viable[d] * 12;
+
+        for (uint32_t s = 0; s < nq; s++) {
+            co.tuple_off[s] = co.tuple_words;
+            co.matches += co.counts[s];
+            co.tuple_words += co.counts[s] * qs[s].k;
+        }
+        const bool want_starts = (want & 3u) >= VLGB_WANT_STARTS;
+        const bool want_tuples = (want & 3u) >= VLGB_WANT_TUPLES;
+        uint64_t* d_starts = nullptr;
+        uint64_t* d_tuples = nullptr;
+        if (co.matches) {
+            size_t ob = 0;
+            if (want_starts) ob += Arena::padded(co.matches, 8);
+            if (want_tuples) ob += Arena::padded(co.tuple_words, 8);
+            uint8_t* o = (uint8_t*)c.out_buf.get(ob + 256);
+            if (want_starts) {
+                d_starts = (uint64_t*)o;
+                o += Arena::padded(co.matches, 8);
+            }
+            if (want_tuples) {
+                d_tuples = (uint64_t*)o;
+                VLGB_CUDA(cudaMemcpyAsync(d_ctl + o_tuple_off, co.tuple_off.data(), (size_t)nq * 8, cudaMemcpyHostToDevice,
+                                          c.stream));
+                c.stats.h2d_bytes += (uint64_t)nq * 8;
+            }
+            S.starts = d_starts;
+            S.tuples = d_tuples;
+            c.begin(ST_EMIT);
+            sel_emit_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
+            c.end(ST_EMIT, 1, co.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? co.tuple_words * 12 : 0));
+            VLGB_CUDA(cudaMemcpyAsync(co.exit_cursor.data(), S.exit_cursor, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+            VLGB_CUDA(cudaMemcpyAsync(co.first_start.data(), S.first_start, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+            c.stats.d2h_bytes += (uint64_t)nq * 16;
+            if (!keep_device && (want_starts || want_tuples)) {
+                size_t hb = (want_starts ? co.matches * 8 : 0) + (want_tuples ? co.tuple_words * 8 : 0);
+                uint8_t* h = (uint8_t*)pinned_alloc(hb);
+                if (want_starts) {
+                    co.h_starts = (uint64_t*)h;
+                    VLGB_CUDA(cudaMemcpyAsync(h, d_starts, co.matches * 8, cudaMemcpyDeviceToHost, c.stream));
+                    h += co.matches * 8;
+                    c.stats.d2h_bytes += co.matches * 8;
+                }
+                if (want_tuples) {
+                    co.h_tuples = (uint64_t*)h;
+                    VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, co.tuple_words * 8, cudaMemcpyDeviceToHost, c.stream));
+                    c.stats.d2h_bytes += co.tuple_words * 8;
+                }
+            }
+            VLGB_CUDA(cudaGetLastError());
+            VLGB_CUDA(cudaStreamSynchronize(c.stream));
+        }
+    }
+}
+
+}  // namespace vlgb

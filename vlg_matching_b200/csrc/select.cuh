@@ -1,0 +1,239 @@
+// select.cuh — greedy, non-overlapping selection of matches and result emission (north-star (4)).
+//
+// Replaces vlg_iterator::pull_forward()/operator++ (include/sdsl/vlg_index.hpp:253-264,349-356) in the
+// formulation of SURVEY.md A.3/A.5: with V_0 the ascending viable starts of a query and
+//   E(x) = last position of x's completed tuple + |P_k|        (the cursor pull_forward leaves)
+// the reported matches are the orbit of  t0 = lower_bound(V_0, entry cursor)  under
+//   succ(t) = lower_bound(V_0, E(V_0[t]))    (monotone, succ(t) > t).
+// k = 1 quirk (wt_helper.hpp:777-784): |P| = 1 and an even (whole-text) position p gives
+// E = p + 2.
+//
+// Slots: every query owns a TILE-aligned segment of upper-bound size (|L_0| owned part), so a tile
+// never straddles two queries.  Kernels:
+//   resolve : per query, where V_0 / last live (scan list for k = 1, else the deepest join level)
+//   succ    : succ[slot]                                                    (gallop from t+1)
+//   tile    : exitp[slot] = first orbit element of slot that lies outside its tile (pointer doubling
+//             in shared memory, log2(TILE) rounds)
+//   walk    : one thread per query hops tile to tile: entry[tile] = first selected element in it
+//   mark    : per entered tile, flags[slot] = 1 for the orbit of entry[tile] (doubling again)
+//   prefix  : mrank = exclusive scan of flags                               (prefix.cuh)
+//   emit    : starts / tuples / exit cursor
+#pragma once
+#include "join.cuh"
+
+namespace vlgb {
+
+constexpr int SEL_TILE = 1024;  // = threads per CTA of the tile kernels
+constexpr int SEL_LOG = 10;
+
+struct SelDesc {
+    uint32_t nq;                 // queries of the chunk
+    uint32_t total_slots;        // sel_off[nq], multiple of SEL_TILE
+    const uint32_t* sel_off;     // [nq+1], TILE-aligned prefix of upper-bound V_0 sizes
+    const uint32_t* kq;          // subpatterns of each query
+    const uint32_t* last_len;    // |P_k|
+    const uint64_t* entry_local; // entry cursor relative to the shard start (saturated at 0)
+    // k = 1: V_0 is the owned prefix of the scan list
+    const uint32_t* const* list0;
+    const uint32_t* list0_len;
+    // k >= 2: V_0 is the compacted level of depth k-1
+    const uint32_t* const* depth_vpos;   // [MAX_K] by depth
+    const uint32_t* const* depth_vnxt;
+    const uint32_t* const* depth_vlast;
+    const uint32_t* const* depth_vseg;
+    const uint32_t* const* last_list;    // scan list of the last subpattern (tuple resolve at depth 1)
+    uint64_t global_offset;
+    // resolved per query
+    const uint32_t** v0;
+    const uint32_t** vlast;      // nullptr entry for k = 1
+    uint32_t* v0_len;
+    uint32_t* t0;                // first selectable index
+    // per slot
+    uint32_t* succ;
+    uint32_t* exitp;
+    uint8_t* flags;
+    uint32_t* entry;             // [total_slots / SEL_TILE]
+    uint32_t* mrank;             // [total_slots + 1]
+    // emission
+    const uint64_t* tuple_off;   // [nq] first tuple word of each query (host prefix over count*k)
+    uint64_t* starts;            // [matches of the chunk]
+    uint64_t* tuples;            // nullable
+    uint64_t* exit_cursor;       // [nq] whole-text cursor, pre-set to the entry cursor
+    uint64_t* first_start;       // [nq] whole-text position of the first reported match, pre-set to ~0
+    uint64_t* counts;            // [nq]
+};
+
+__global__ void sel_resolve_kernel(SelDesc s)
+{
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= s.nq) return;
+    const uint32_t k = s.kq[q];
+    const uint32_t* v;
+    const uint32_t* vl = nullptr;
+    uint32_t len;
+    if (k == 1) {
+        v = s.list0[q];
+        len = s.list0_len[q];
+    } else {
+        const uint32_t d = k - 1;
+        const uint32_t* seg = s.depth_vseg[d];
+        v = s.depth_vpos[d] + seg[q];
+        vl = s.depth_vlast[d] + seg[q];
+        len = seg[q + 1] - seg[q];
+    }
+    s.v0[q] = v;
+    s.vlast[q] = vl;
+    s.v0_len[q] = len;
+    s.t0[q] = full_lower_bound(v, len, s.entry_local[q]);
+}
+
+__device__ __forceinline__ uint32_t sel_query_of_tile(const SelDesc& s, uint32_t slot0)
+{
+    return find_segment(s.sel_off, 0, s.nq - 1, slot0);
+}
+
+__global__ void __launch_bounds__(SEL_TILE) sel_succ_kernel(SelDesc s)
+{
+    __shared__ uint32_t s_q;
+    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
+    __syncthreads();
+    const uint32_t q = s_q;
+    const uint32_t t = slot0 - s.sel_off[q] + threadIdx.x;
+    const uint32_t len = s.v0_len[q];
+    if (t >= len) return;
+    const uint32_t* v = s.v0[q];
+    const uint32_t* vl = s.vlast[q];
+    const uint32_t x = __ldg(v + t);
+    const uint32_t ll = s.last_len[q];
+    uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
+    if (!vl && ll == 1 && (((uint64_t)x + s.global_offset) & 1ull) == 0) e = (uint64_t)x + 2;  // k = 1 sibling skip
+    s.succ[slot0 + threadIdx.x] = gallop_lower_bound(v, t + 1, len, e);
+}
+
+// Pointer doubling inside one tile.  ptr[i] (shared) holds a V_0 index; indices inside
+// [base, base + SEL_TILE) are followed, anything else is final.
+__device__ __forceinline__ uint32_t sel_hop(const uint32_t* ptr, uint32_t p, uint32_t base)
+{
+    uint32_t rel = p - base;
+    return rel < (uint32_t)SEL_TILE ? ptr[rel] : p;
+}
+
+__global__ void __launch_bounds__(SEL_TILE) sel_tile_kernel(SelDesc s)
+{
+    __shared__ uint32_t ptr[SEL_TILE];
+    __shared__ uint32_t s_q;
+    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
+    __syncthreads();
+    const uint32_t q = s_q;
+    const uint32_t base = slot0 - s.sel_off[q];  // V_0 index of the tile's first element
+    const uint32_t len = s.v0_len[q];
+    if (base >= len) return;                     // whole tile beyond the viable list (uniform)
+    const uint32_t t = base + threadIdx.x;
+    uint32_t p = t < len ? s.succ[slot0 + threadIdx.x] : 0xFFFFFFF0u;
+    ptr[threadIdx.x] = p;
+    __syncthreads();
+#pragma unroll 1
+    for (int r = 0; r < SEL_LOG; r++) {
+        uint32_t nx = sel_hop(ptr, p, base);
+        __syncthreads();
+        p = nx;
+        ptr[threadIdx.x] = p;
+        __syncthreads();
+    }
+    if (t < len) s.exitp[slot0 + threadIdx.x] = p;
+}
+
+__global__ void sel_walk_kernel(SelDesc s)
+{
+    // one thread per query; spread over warps so that long walks do not serialise 32 short ones
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= s.nq) return;
+    const uint32_t len = s.v0_len[q];
+    const uint32_t off = s.sel_off[q];
+    uint32_t cur = s.t0[q];
+    while (cur < len) {
+        s.entry[(off + cur) / SEL_TILE] = cur;
+        cur = s.exitp[off + cur];
+    }
+}
+
+__global__ void __launch_bounds__(SEL_TILE) sel_mark_kernel(SelDesc s)
+{
+    __shared__ uint32_t ptr[SEL_TILE];
+    __shared__ uint32_t mark[SEL_TILE];
+    __shared__ uint32_t s_q;
+    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    const uint32_t e = s.entry[blockIdx.x];
+    if (e == NONE32) return;  // tile not entered: flags stay 0 (uniform)
+    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
+    __syncthreads();
+    const uint32_t q = s_q;
+    const uint32_t base = slot0 - s.sel_off[q];
+    const uint32_t len = s.v0_len[q];
+    const uint32_t t = base + threadIdx.x;
+    uint32_t p = t < len ? s.succ[slot0 + threadIdx.x] : 0xFFFFFFF0u;
+    ptr[threadIdx.x] = p;
+    mark[threadIdx.x] = (t == e) ? 1u : 0u;
+    __syncthreads();
+#pragma unroll 1
+    for (int r = 0; r < SEL_LOG; r++) {
+        // marked elements mark their 2^r-th successor (benign race: only orbit elements get marked)
+        uint32_t rel = p - base;
+        if (mark[threadIdx.x] && rel < (uint32_t)SEL_TILE) mark[rel] = 1u;
+        uint32_t nx = sel_hop(ptr, p, base);
+        __syncthreads();
+        p = nx;
+        ptr[threadIdx.x] = p;
+        __syncthreads();
+    }
+    if (t < len) s.flags[slot0 + threadIdx.x] = (uint8_t)mark[threadIdx.x];
+}
+
+// counts[q] = mrank[sel_off[q+1]] - mrank[sel_off[q]]
+__global__ void sel_counts_kernel(SelDesc s)
+{
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < s.nq) s.counts[q] = (uint64_t)(s.mrank[s.sel_off[q + 1]] - s.mrank[s.sel_off[q]]);
+}
+
+__global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
+{
+    __shared__ uint32_t s_q;
+    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    if (s.entry[blockIdx.x] == NONE32) return;
+    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
+    __syncthreads();
+    const uint32_t q = s_q;
+    const uint32_t slot = slot0 + threadIdx.x;
+    const uint32_t t = slot - s.sel_off[q];
+    if (t >= s.v0_len[q] || !s.flags[slot]) return;
+    const uint32_t o = s.mrank[slot];
+    const uint32_t qfirst = s.mrank[s.sel_off[q]];
+    const uint32_t qend = s.mrank[s.sel_off[q + 1]];
+    const uint32_t k = s.kq[q];
+    const uint32_t x = __ldg(s.v0[q] + t);
+    const uint64_t g = s.global_offset;
+    if (s.starts) s.starts[o] = g + x;
+    if (o == qfirst) s.first_start[q] = g + x;
+    const uint32_t* vl = s.vlast[q];
+    if (o + 1 == qend) {  // last match of the query: the cursor it leaves behind
+        const uint32_t ll = s.last_len[q];
+        uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
+        if (!vl && ll == 1 && (((uint64_t)x + g) & 1ull) == 0) e = (uint64_t)x + 2;
+        s.exit_cursor[q] = g + e;
+    }
+    if (s.tuples) {
+        uint64_t* out = s.tuples + s.tuple_off[q] + (uint64_t)(o - qfirst) * k;
+        out[0] = g + x;
+        uint32_t idx = t;
+        for (uint32_t d = k - 1, i = 1; d >= 1; d--, i++) {
+            idx = __ldg(s.depth_vnxt[d] + s.depth_vseg[d][q] + idx);
+            uint32_t pos = d > 1 ? __ldg(s.depth_vpos[d - 1] + s.depth_vseg[d - 1][q] + idx) : __ldg(s.last_list[q] + idx);
+            out[i] = g + pos;
+        }
+    }
+}
+
+}  // namespace vlgb
