@@ -56,11 +56,18 @@ struct ScanOut {
     uint64_t total_words = 0;
 };
 
-inline uint32_t scan_chunk_for(uint64_t n)
+// Rows (= warps' chunks): a whole number of waves of resident warps when the shard is large, at least
+// one step per row when it is small, never more than the u16 row counters can hold.
+inline uint32_t scan_chunk_for(uint64_t n, int sm_count)
 {
-    uint64_t c = (n / 8192 + 31) & ~uint64_t(31);
+    const uint64_t resident = (uint64_t)sm_count * SCAN_WARPS;
+    uint64_t waves = (n + resident * SCAN_MAX_CHUNK - 1) / (resident * SCAN_MAX_CHUNK);
+    if (waves < 2 && n >= resident * 2 * 8192) waves = 2;
+    if (waves < 1) waves = 1;
+    uint64_t c = (n + resident * waves - 1) / (resident * waves);
+    c = (c + SCAN_STEP - 1) / SCAN_STEP * SCAN_STEP;
     if (c < 1024) c = 1024;
-    if (c > 16384) c = 16384;
+    if (c > SCAN_MAX_CHUNK) c = SCAN_MAX_CHUNK;
     return (uint32_t)c;
 }
 
@@ -76,19 +83,21 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     if (P == 0 || n == 0) return;
 
     const uint32_t npass = (P + SCAN_S - 1) / SCAN_S;
-    const uint32_t chunk = scan_chunk_for(n);
+    const uint32_t chunk = scan_chunk_for(n, c.sm_count);
     const uint32_t rows = (uint32_t)((n + chunk - 1) / chunk);
     const uint32_t nrb = (rows + SCAN_RB - 1) / SCAN_RB;
-    const size_t smem = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_S * sizeof(uint32_t);
+    const size_t smem = SCAN_SMEM;
     static thread_local bool attr_set = false;
     if (!attr_set) {
-        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
 
     struct PassDev {
-        uint32_t s_act, stride;
+        uint32_t s_act, stride, has_short;
         size_t o_tables, o_len, o_off, o_blob, o_base;  // inside the control blob
         uint32_t *matrix, *part, *total;
     };
@@ -101,6 +110,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         build_pass(dict, first, cnt, *ph);
         pd[p].s_act = cnt;
         pd[p].stride = (cnt + 31) & ~31u;
+        pd[p].has_short = ph->has_short;
         pd[p].o_tables = ctl.put(&ph->tables, 1);
         pd[p].o_len = ctl.put(ph->long_len);
         pd[p].o_off = ctl.put(ph->long_off);
@@ -132,6 +142,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.rows = rows;
         a.s_act = pd[p].s_act;
         a.s_stride = pd[p].stride;
+        a.has_short = pd[p].has_short;
         a.tables = dev_at<const ScanTables>(d_ctl, pd[p].o_tables);
         a.long_len = dev_at<const uint32_t>(d_ctl, pd[p].o_len);
         a.long_off = dev_at<const uint32_t>(d_ctl, pd[p].o_off);
@@ -147,7 +158,8 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     for (uint32_t p = 0; p < npass; p++) {
         ScanArgs a = args_for(p);
         c.begin(ST_SCAN_COUNT);
-        scan_kernel<false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        if (a.has_short) scan_kernel<false, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        else scan_kernel<false, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
         c.end(ST_SCAN_COUNT, 1, n + (uint64_t)rows * pd[p].s_act * 4);
         c.begin(ST_SCAN_OFFSETS);
         dim3 g((pd[p].stride + 127) / 128, nrb);
@@ -187,7 +199,8 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         ScanArgs a = args_for(p);
         a.out = so.d_lists;
         c.begin(ST_SCAN_FILL);
-        if (pocc) scan_kernel<true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        if (pocc && a.has_short) scan_kernel<true, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        else if (pocc) scan_kernel<true, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
         c.end(ST_SCAN_FILL, pocc ? 1 : 0, pocc ? n + (uint64_t)rows * pd[p].s_act * 4 + pocc * 4 : 0);
     }
     c.stats.scan_passes += npass;
