@@ -98,7 +98,7 @@ int vlgb_index_build(const uint8_t* text, uint64_t n, uint64_t global_offset, ui
 /* Same, from a raw byte file (the `construct(idx, file, 1)` call of examples/vlg_matching.cpp:34). */
 int vlgb_index_build_file(const char* path, vlgb_index** out);
 /* Same, the text is already in device memory (device pointer stays owned by the caller and must
- * outlive the index; >= n+64 bytes must be readable). */
+ * outlive the index; it must be 16-byte aligned and >= n+64 bytes must be readable). */
 int vlgb_index_build_device(const uint8_t* text_device, uint64_t n, uint64_t global_offset, uint64_t owned_len,
                             uint64_t total_len, vlgb_index** out);
 int vlgb_index_save(const vlgb_index* idx, const char* path);

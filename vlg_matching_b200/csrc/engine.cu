@@ -212,6 +212,8 @@ extern "C" int vlgb_index_build_device(const uint8_t* text_device, uint64_t n, u
     *out = nullptr;
     int rc = index_check(n, owned_len, "vlgb_index_build_device");
     if (rc) return rc;
+    if (reinterpret_cast<uintptr_t>(text_device) & 15u)
+        return fail(VLGB_ERR_ARG, "vlgb_index_build_device: the text must be 16-byte aligned");
     try {
         ensure_ready();
         vlgb_index* idx = new vlgb_index();

@@ -6,15 +6,18 @@
 //
 // Layout / algorithm
 //  * up to SCAN_S patterns per pass; patterns are keyed by (class, first min(len,8) bytes) where
-//    class = min(len, 9).  Class <= 8 keys are exact; class 9 entries are verified byte by byte.
+//    class = min(len, 8).  Class <= 7 keys are exact; class 8 entries (len >= 8) are verified byte by byte.
 //  * shared memory per CTA: open-addressing hash table of the pass (SoA, SCAN_H slots), the prefilter
-//    f3 (hashed first 3 bytes -> mask of the classes 3..9 that have a pattern with that prefix; f1/f2 for
-//    1- and 2-byte patterns), one u16 cursor row and one work queue per warp.
+//    f3 (hashed first 3 bytes -> byte with bit c-1 set for every class c = 3..8 that has a pattern with that
+//    prefix; f1/f2 bitmaps for 1- and 2-byte patterns), one u16 cursor row and one work queue per warp.
 //  * every warp owns one contiguous chunk of the shard ("row") and walks it 256 positions per step:
-//    lane l holds bytes [8l, 8l+16) of the step in registers (one coalesced 8-byte load + a shuffle), tests
-//    its 8 positions against the prefilter, and the hits are expanded into (position, class, window)
-//    work items that are compacted IN POSITION ORDER into the warp's queue.  The queue is then drained
-//    32 items at a time with all lanes busy: one hash probe per item.
+//    lane l holds bytes [8l, 8l+12) of the step in registers (one coalesced 8-byte load + a shuffle), looks
+//    up the class-mask byte of its 8 positions and packs them into 64 bits.  A warp prefix sum of the
+//    popcounts gives every lane its place in POSITION ORDER; one short loop over the set bits appends
+//    4-byte items (position in row | class << 16) to the warp's circular queue.
+//  * the queue is drained only in full rounds of 32 items (leftovers wait for the next step), all lanes
+//    busy: re-read the item's 8-byte window from the text (L1), mask it to the class length, one hash
+//    probe, then a warp-wide emit.
 //  * pass 1 counts occurrences per (row, pattern); the column-wise exclusive scan of that count matrix
 //    gives every row its write cursor per pattern; pass 2 repeats the walk and writes positions at
 //    cursor + rank (rank among equal patterns of the round by __match_any_sync), which makes every list
@@ -34,17 +37,17 @@ constexpr int SCAN_H = 4096;       // hash slots
 constexpr int SCAN_WARPS = 16;     // warps per CTA
 constexpr int SCAN_PPL = 8;        // positions per lane per step
 constexpr int SCAN_STEP = 32 * SCAN_PPL;
-constexpr int SCAN_F3 = 65536;     // 3-byte prefilter entries (u8: bit c-3 set = class c present)
+constexpr int SCAN_F3 = 65536;     // 3-byte prefilter entries (u8: bit c-1 set = class c present, c = 3..8)
 constexpr int SCAN_F2_WORDS = 64;  // 2048 bits
 constexpr int SCAN_F1_WORDS = 8;   // 256 bits
-constexpr int SCAN_QCAP = 128;     // work items per warp queue
+constexpr int SCAN_QCAP = 512;     // entries (u32) of a warp's circular work queue
 constexpr int SCAN_RB = 64;        // rows per row-block in the count-matrix scan
 constexpr uint32_t SCAN_MAX_CHUNK = 65280;  // u16 per-row counters
 
 struct ScanTables {  // one pass; same layout on host, in global memory and in shared memory
     uint32_t klo[SCAN_H];
     uint32_t khi[SCAN_H];
-    uint32_t meta[SCAN_H];  // 0 = empty, else 0x80000000 | class << 16 | local pid
+    uint32_t meta[SCAN_H];  // 0 = empty, else 0x80000000 | class << 16 | local pid; class = min(len, 8)
     uint8_t f3[SCAN_F3];
     uint32_t f2[SCAN_F2_WORDS];
     uint32_t f1[SCAN_F1_WORDS];
@@ -70,7 +73,7 @@ struct ScanArgs {
     uint32_t s_stride;       // row stride of the count matrix (multiple of 32)
     uint32_t has_short;      // the pass holds 1- or 2-byte patterns
     const ScanTables* tables;
-    const uint32_t* long_len;  // [s_act] full length (class 9 only)
+    const uint32_t* long_len;  // [s_act] full length (class 8 only: len >= 8)
     const uint32_t* long_off;  // [s_act] offset into long_blob
     const uint8_t* long_blob;
     uint32_t* matrix;        // [rows][s_stride]: counts (pass 1 out) / write cursors inside each list (pass 2 in)
@@ -79,7 +82,81 @@ struct ScanArgs {
 };
 
 constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S / 2) * sizeof(uint32_t) +
-                             (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint4);
+                             (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t);
+
+// One drain round: the first n (<= 32) queue entries starting at qhead, one per lane, all lanes converged.
+// Entry = (position - row start) | class << 16.  The 8-byte window of the item is re-read from the text
+// (L1-resident: the warp loaded that line moments ago), masked to the class length and looked up in the
+// hash table of the pass; hits are ranked among equal patterns of the round in lane (= position) order.
+template <bool FILL>
+__device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* cur, const uint32_t* q,
+                                                 uint32_t qhead, uint32_t n, uint32_t row_lo, const uint32_t* mrow,
+                                                 uint32_t lane, uint32_t lt_mask)
+{
+    const bool act = lane < n;
+    uint32_t p = 0, c = 0, klo = 0, khi = 0;
+    if (act) {
+        const uint32_t e = q[(qhead + lane) & (SCAN_QCAP - 1)];
+        p = row_lo + (e & 0xFFFFu);
+        c = e >> 16;
+        const uint32_t* t32 = reinterpret_cast<const uint32_t*>(a.text + (p & ~3u));
+        const uint32_t w0 = __ldg(t32), w1 = __ldg(t32 + 1), w2 = __ldg(t32 + 2);
+        const uint32_t sh = (p & 3u) * 8u;
+        klo = __funnelshift_r(w0, w1, sh);
+        khi = __funnelshift_r(w1, w2, sh);
+        const uint32_t mlo = c >= 4 ? 0xFFFFFFFFu : ((1u << (8 * c)) - 1u);
+        const uint32_t mhi = c >= 8 ? 0xFFFFFFFFu : (c > 4 ? ((1u << (8 * (c - 4))) - 1u) : 0u);
+        klo &= mlo;
+        khi &= mhi;
+    }
+    uint32_t slot = scan_hash(klo, khi, c);
+    const uint32_t want = 0x80000000u | (c << 16);
+    bool more = act;
+    do {
+        uint32_t pid = NONE32;
+        if (more) {
+            for (;;) {
+                const uint32_t meta = T->meta[slot];
+                if (meta == 0) { more = false; break; }
+                const bool eq = ((meta & 0xFFFF0000u) == want) && T->klo[slot] == klo && T->khi[slot] == khi;
+                slot = (slot + 1) & (SCAN_H - 1);
+                if (eq) {
+                    const uint32_t cand = meta & 0xFFFFu;
+                    bool ok;
+                    if (c < 8) {
+                        ok = (uint64_t)p + c <= a.valid_len;
+                        more = false;  // classes 1..7 have at most one entry per key
+                    } else {
+                        const uint32_t L = a.long_len[cand];
+                        ok = (uint64_t)p + L <= a.valid_len;
+                        if (ok) {
+                            const uint8_t* pat = a.long_blob + a.long_off[cand];
+                            const uint8_t* txt = a.text + p;
+                            for (uint32_t j = 8; j < L; j++)
+                                if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
+                        }
+                    }
+                    // one candidate per round, hit or miss: lanes holding the same key walk the same
+                    // slot sequence, so each pattern is emitted in one round and its list stays sorted
+                    if (ok) pid = cand;
+                    break;
+                }
+            }
+        }
+        // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
+        const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+        const int leader = __ffs(grp) - 1;
+        uint32_t old = 0;
+        if (pid != NONE32 && (int)lane == leader) {
+            const uint32_t sh = (pid & 1u) * 16;
+            old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+        }
+        if (FILL) {
+            old = __shfl_sync(0xffffffffu, old, leader);
+            if (pid != NONE32) a.out[__ldg(a.list_base + pid) + __ldg(mrow + pid) + old + __popc(grp & lt_mask)] = p;
+        }
+    } while (__any_sync(0xffffffffu, more && c == 8));
+}
 
 template <bool FILL, bool SHORT>
 __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
@@ -87,7 +164,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     extern __shared__ __align__(16) uint8_t smem_raw[];
     ScanTables* T = reinterpret_cast<ScanTables*>(smem_raw);
     uint32_t* cursors = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables));
-    uint4* queues = reinterpret_cast<uint4*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S / 2) * 4);
+    uint32_t* queues = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S / 2) * 4);
 
     {  // stage the pass tables
         const uint4* src = reinterpret_cast<const uint4*>(a.tables);
@@ -96,7 +173,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     }
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* cur = cursors + warp * (SCAN_S / 2);  // u16 counters, two per word
-    uint4* q = queues + warp * SCAN_QCAP;
+    uint32_t* q = queues + warp * SCAN_QCAP;        // circular queue of (position - row start) | class << 16
     for (uint32_t i = lane; i < SCAN_S / 2; i += 32) cur[i] = 0u;
     __syncthreads();
 
@@ -107,139 +184,92 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     const uint32_t lo = row * a.chunk;
     const uint32_t hi = min(lo + a.chunk, a.valid_len);
     const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t qhead = 0, qcount = 0;  // warp-uniform
 
     for (uint32_t base = lo; base < hi; base += SCAN_STEP) {
         // ---- 16 bytes per lane: own 8 + the next lane's 8
         const uint32_t off = base + 8 * lane;
         uint2 own = make_uint2(0u, 0u);
         if (off < a.valid_len) own = __ldg(reinterpret_cast<const uint2*>(a.text + off));
-        uint2 nxt;
-        nxt.x = __shfl_down_sync(0xffffffffu, own.x, 1);
-        nxt.y = __shfl_down_sync(0xffffffffu, own.y, 1);
+        uint32_t nx = __shfl_down_sync(0xffffffffu, own.x, 1);
         if (lane == 31) {
-            nxt = make_uint2(0u, 0u);
-            if (base + SCAN_STEP < a.valid_len) nxt = __ldg(reinterpret_cast<const uint2*>(a.text + base + SCAN_STEP));
+            nx = 0u;
+            if (base + SCAN_STEP < a.valid_len) nx = __ldg(reinterpret_cast<const uint32_t*>(a.text + base + SCAN_STEP));
         }
-        // ---- prefilter: class mask per position
+        // ---- prefilter: one class-mask byte per position (bit c-1 = a pattern of class c may start here)
         uint32_t wl[SCAN_PPL];  // low 32 bits of the window at position j
         wl[0] = own.x;
         wl[1] = __funnelshift_r(own.x, own.y, 8);
         wl[2] = __funnelshift_r(own.x, own.y, 16);
         wl[3] = __funnelshift_r(own.x, own.y, 24);
         wl[4] = own.y;
-        wl[5] = __funnelshift_r(own.y, nxt.x, 8);
-        wl[6] = __funnelshift_r(own.y, nxt.x, 16);
-        wl[7] = __funnelshift_r(own.y, nxt.x, 24);
-        uint32_t m[SCAN_PPL];
-        uint32_t cnt = 0;
+        wl[5] = __funnelshift_r(own.y, nx, 8);
+        wl[6] = __funnelshift_r(own.y, nx, 16);
+        wl[7] = __funnelshift_r(own.y, nx, 24);
+        uint32_t s0 = 0, s1 = 0;
 #pragma unroll
         for (int j = 0; j < SCAN_PPL; j++) {
-            uint32_t mj = (uint32_t)T->f3[scan_h3(wl[j])] << 3;
+            uint32_t mj = T->f3[scan_h3(wl[j])];
             if (SHORT) {
-                uint32_t b0 = wl[j] & 0xFFu;
-                mj |= ((T->f1[b0 >> 5] >> (b0 & 31)) & 1u) << 1;
-                uint32_t i2 = scan_h2(wl[j]);
-                mj |= ((T->f2[i2 >> 5] >> (i2 & 31)) & 1u) << 2;
+                const uint32_t b0 = wl[j] & 0xFFu;
+                mj |= (T->f1[b0 >> 5] >> (b0 & 31)) & 1u;
+                const uint32_t i2 = scan_h2(wl[j]);
+                mj |= ((T->f2[i2 >> 5] >> (i2 & 31)) & 1u) << 1;
             }
-            if (off + j >= hi) mj = 0;
-            m[j] = mj;
-            cnt += __popc(mj);
+            if (j < 4) s0 |= mj << (8 * j); else s1 |= mj << (8 * (j - 4));
         }
+        if (base + SCAN_STEP > hi) {  // last step of the row: positions >= hi belong to the next row (or nobody)
+            const uint32_t left = off < hi ? hi - off : 0u;  // my positions j < left are inside
+            if (left < 4) { s1 = 0u; s0 &= left ? (0xFFFFFFFFu >> (8 * (4 - left))) : 0u; }
+            else if (left < 8) s1 &= left > 4 ? (0xFFFFFFFFu >> (8 * (8 - left))) : 0u;
+        }
+        const uint32_t cnt = __popc(s0) + __popc(s1);
         // ---- position-ordered offsets of the lanes' work items
         uint32_t incl = cnt;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+            const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
             if (lane >= (uint32_t)d) incl += o;
         }
         const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+        if (total == 0) continue;
         const uint32_t first = incl - cnt;
+        const uint32_t rel0 = off - lo;
 
-        for (uint32_t done = 0; done < total; done += SCAN_QCAP) {
-            // ---- enqueue the items whose index falls into [done, done + QCAP)
-            if (cnt && first < done + SCAN_QCAP && first + cnt > done) {
-                uint32_t idx = first;
-#pragma unroll
-                for (int j = 0; j < SCAN_PPL; j++) {
-                    uint32_t mm = m[j];
-                    if (mm) {
-                        uint32_t whi;
-                        if (j < 4) whi = j == 0 ? own.y : __funnelshift_r(own.y, nxt.x, 8 * j);
-                        else whi = j == 4 ? nxt.x : __funnelshift_r(nxt.x, nxt.y, 8 * (j - 4));
-                        while (mm) {
-                            uint32_t c = __ffs(mm) - 1;
-                            mm &= mm - 1;
-                            uint32_t rel = idx - done;
-                            if (rel < (uint32_t)SCAN_QCAP) q[rel] = make_uint4(off + j, c, wl[j], whi);
-                            idx++;
-                        }
-                    }
+        uint32_t done = 0;
+        do {
+            const uint32_t take = min(total - done, (uint32_t)SCAN_QCAP - qcount);
+            // ---- enqueue the items whose index falls into [done, done + take): one loop over the set
+            // bits of the lane's packed masks (ascending position, then ascending class)
+            if (cnt && first < done + take && first + cnt > done) {
+                const uint32_t wbase = qhead + qcount - done;
+                uint32_t idx = first, t0 = s0, t1 = s1;
+                while (t0) {
+                    const uint32_t b = __ffs(t0) - 1;
+                    t0 &= t0 - 1;
+                    if (idx - done < take) q[(wbase + idx) & (SCAN_QCAP - 1)] = (rel0 + (b >> 3)) | (((b & 7u) + 1u) << 16);
+                    idx++;
+                }
+                while (t1) {
+                    const uint32_t b = __ffs(t1) - 1;
+                    t1 &= t1 - 1;
+                    if (idx - done < take) q[(wbase + idx) & (SCAN_QCAP - 1)] = (rel0 + 4u + (b >> 3)) | (((b & 7u) + 1u) << 16);
+                    idx++;
                 }
             }
+            qcount += take;
+            done += take;
             __syncwarp();
-            // ---- drain: one hash probe per item, 32 items per round
-            const uint32_t nitems = min((uint32_t)SCAN_QCAP, total - done);
-            for (uint32_t r0 = 0; r0 < nitems; r0 += 32) {
-                const bool act = r0 + lane < nitems;
-                uint4 it = make_uint4(0u, 0u, 0u, 0u);
-                if (act) it = q[r0 + lane];
-                const uint32_t p = it.x, c = it.y;
-                uint32_t klo = it.z, khi = it.w;
-                if (c < 4) { klo &= (1u << (8 * c)) - 1u; khi = 0; }  // c >= 1 for live items
-                else if (c < 8) khi &= (1u << (8 * (c - 4))) - 1u;
-                uint32_t slot = scan_hash(klo, khi, c);
-                const uint32_t want = 0x80000000u | (c << 16);
-                bool more = act;
-                do {
-                    uint32_t pid = NONE32;
-                    if (more) {
-                        for (;;) {
-                            const uint32_t meta = T->meta[slot];
-                            if (meta == 0) { more = false; break; }
-                            const bool eq = ((meta & 0xFFFF0000u) == want) && T->klo[slot] == klo && T->khi[slot] == khi;
-                            slot = (slot + 1) & (SCAN_H - 1);
-                            if (eq) {
-                                const uint32_t cand = meta & 0xFFFFu;
-                                bool ok;
-                                if (c < 9) {
-                                    ok = (uint64_t)p + c <= a.valid_len;
-                                    more = false;  // classes 1..8 have at most one entry per key
-                                } else {
-                                    const uint32_t L = a.long_len[cand];
-                                    ok = (uint64_t)p + L <= a.valid_len;
-                                    if (ok) {
-                                        const uint8_t* pat = a.long_blob + a.long_off[cand];
-                                        const uint8_t* txt = a.text + p;
-                                        for (uint32_t j = 8; j < L; j++)
-                                            if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
-                                    }
-                                }
-                                // one candidate per round, hit or miss: lanes holding the same key walk the
-                                // same slot sequence, so each pattern is emitted in one round per step and
-                                // its list stays sorted
-                                if (ok) pid = cand;
-                                break;
-                            }
-                        }
-                    }
-                    // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
-                    const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-                    const int leader = __ffs(grp) - 1;
-                    uint32_t old = 0;
-                    if (pid != NONE32 && (int)lane == leader) {
-                        const uint32_t sh = (pid & 1u) * 16;
-                        old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
-                    }
-                    if (FILL) {
-                        old = __shfl_sync(0xffffffffu, old, leader);
-                        if (pid != NONE32)
-                            a.out[__ldg(a.list_base + pid) + __ldg(mrow + pid) + old + __popc(grp & lt_mask)] = p;
-                    }
-                } while (__any_sync(0xffffffffu, more && c == 9));
+            // ---- drain full rounds; fewer than 32 leftovers wait for the next step
+            while (qcount >= 32) {
+                scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask);
+                qhead = (qhead + 32) & (SCAN_QCAP - 1);
+                qcount -= 32;
             }
             __syncwarp();
-        }
+        } while (done < total);
     }
+    if (qcount) scan_drain_round<FILL>(a, T, cur, q, qhead, qcount, lo, mrow, lane, lt_mask);
     if (!FILL) {
         __syncwarp();
         for (uint32_t i = lane; i < a.s_act; i += 32) mrow[i] = (cur[i >> 1] >> ((i & 1u) * 16)) & 0xFFFFu;
@@ -338,7 +368,7 @@ inline void build_pass(const PatternDict& d, uint32_t first, uint32_t count, Pas
     for (uint32_t i = 0; i < count; i++) {
         const std::string& s = d.pats[first + i];
         uint32_t len = (uint32_t)s.size();
-        uint32_t c = len < 9 ? len : 9;
+        uint32_t c = len < 8 ? len : 8;
         uint64_t key = 0;
         for (uint32_t j = 0; j < len && j < 8; j++) key |= (uint64_t)(uint8_t)s[j] << (8 * j);
         uint32_t klo = (uint32_t)key, khi = (uint32_t)(key >> 32);
@@ -355,9 +385,9 @@ inline void build_pass(const PatternDict& d, uint32_t first, uint32_t count, Pas
             uint32_t i2 = scan_h2(w32);
             ph.tables.f2[i2 >> 5] |= 1u << (i2 & 31);
         } else {
-            ph.tables.f3[scan_h3(w32)] |= (uint8_t)(1u << (c - 3));
+            ph.tables.f3[scan_h3(w32)] |= (uint8_t)(1u << (c - 1));
         }
-        if (c == 9) {
+        if (c == 8) {
             ph.long_len[i] = len;
             ph.long_off[i] = (uint32_t)ph.long_blob.size();
             ph.long_blob += s;
