@@ -33,7 +33,7 @@
 namespace vlgb {
 
 constexpr int SCAN_S = 2048;       // patterns per pass
-constexpr int SCAN_H = 4096;       // hash slots
+constexpr int SCAN_H = 8192;       // hash slots (4 B each; load factor <= 25%)
 constexpr int SCAN_WARPS = 16;     // warps per CTA
 constexpr int SCAN_PPL = 8;        // positions per lane per step
 constexpr int SCAN_STEP = 32 * SCAN_PPL;
@@ -44,22 +44,32 @@ constexpr int SCAN_QCAP = 512;     // entries (u32) of a warp's circular work qu
 constexpr int SCAN_RB = 64;        // rows per row-block in the count-matrix scan
 constexpr uint32_t SCAN_MAX_CHUNK = 65280;  // u16 per-row counters
 
+// Hash slot word: 0 = empty, else  1 << 31 | tag (17 bits) << 14 | (class - 1) << 11 | local pid (11 bits),
+// class = min(len, 8).  A probe reads ONE word per slot; the 8-byte key (by pid) is only compared on a tag hit.
+constexpr uint32_t SCAN_PID_MASK = 0x7FFu;
+static_assert(SCAN_S <= 2048, "pid field of the slot word is 11 bits");
+
 struct ScanTables {  // one pass; same layout on host, in global memory and in shared memory
-    uint32_t klo[SCAN_H];
-    uint32_t khi[SCAN_H];
-    uint32_t meta[SCAN_H];  // 0 = empty, else 0x80000000 | class << 16 | local pid; class = min(len, 8)
+    uint32_t slot[SCAN_H];
+    uint32_t klo[SCAN_S];   // first min(len, 8) bytes of pattern pid, zero padded
+    uint32_t khi[SCAN_S];
     uint8_t f3[SCAN_F3];
     uint32_t f2[SCAN_F2_WORDS];
     uint32_t f1[SCAN_F1_WORDS];
 };
 
-__host__ __device__ inline uint32_t scan_hash(uint32_t klo, uint32_t khi, uint32_t c)
+// 32-bit mix of (key, class): low 13 bits = home slot, next 17 bits = tag
+__host__ __device__ inline uint32_t scan_mix(uint32_t klo, uint32_t khi, uint32_t c)
 {
     uint32_t h = (klo * 0x9E3779B1u) ^ ((khi + c) * 0x85EBCA77u);
     h ^= h >> 15;
     h *= 0x2C1B3C6Du;
-    h ^= h >> 12;
-    return h & (SCAN_H - 1);
+    h ^= h >> 13;
+    return h;
+}
+__host__ __device__ inline uint32_t scan_slot_word(uint32_t h, uint32_t c)  // pid field left 0
+{
+    return 0x80000000u | (((h >> 13) & 0x1FFFFu) << 14) | ((c - 1u) << 11);
 }
 __host__ __device__ inline uint32_t scan_h3(uint32_t w) { return ((w & 0xFFFFFFu) * 0x9E3779B1u) >> 16; }
 __host__ __device__ inline uint32_t scan_h2(uint32_t w) { return ((w & 0xFFFFu) * 0x9E3779B1u) >> 21; }
@@ -85,77 +95,83 @@ constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S /
                              (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t);
 
 // One drain round: the first n (<= 32) queue entries starting at qhead, one per lane, all lanes converged.
-// Entry = (position - row start) | class << 16.  The 8-byte window of the item is re-read from the text
-// (L1-resident: the warp loaded that line moments ago), masked to the class length and looked up in the
-// hash table of the pass; hits are ranked among equal patterns of the round in lane (= position) order.
+// Entry = (position - row start) | class-mask byte << 16.  The 8-byte window of the position is re-read
+// from the text (L1-resident: the warp loaded that line moments ago).  The classes present in the round
+// are visited in ascending, warp-uniform order; in each visit the lanes that carry the class mask their
+// window to the class length and probe the hash table (one 4-byte slot word per probe; the key itself is
+// compared only on a tag hit).  Hits are ranked among equal patterns in lane (= position) order.  A
+// pattern belongs to exactly one class, so every list receives its positions in ascending order.
 template <bool FILL>
 __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* cur, const uint32_t* q,
                                                  uint32_t qhead, uint32_t n, uint32_t row_lo, const uint32_t* mrow,
                                                  uint32_t lane, uint32_t lt_mask)
 {
-    const bool act = lane < n;
-    uint32_t p = 0, c = 0, klo = 0, khi = 0;
-    if (act) {
+    uint32_t p = 0, cmask = 0, wlo = 0, whi = 0;
+    if (lane < n) {
         const uint32_t e = q[(qhead + lane) & (SCAN_QCAP - 1)];
         p = row_lo + (e & 0xFFFFu);
-        c = e >> 16;
+        cmask = e >> 16;
         const uint32_t* t32 = reinterpret_cast<const uint32_t*>(a.text + (p & ~3u));
         const uint32_t w0 = __ldg(t32), w1 = __ldg(t32 + 1), w2 = __ldg(t32 + 2);
         const uint32_t sh = (p & 3u) * 8u;
-        klo = __funnelshift_r(w0, w1, sh);
-        khi = __funnelshift_r(w1, w2, sh);
-        const uint32_t mlo = c >= 4 ? 0xFFFFFFFFu : ((1u << (8 * c)) - 1u);
-        const uint32_t mhi = c >= 8 ? 0xFFFFFFFFu : (c > 4 ? ((1u << (8 * (c - 4))) - 1u) : 0u);
-        klo &= mlo;
-        khi &= mhi;
+        wlo = __funnelshift_r(w0, w1, sh);
+        whi = __funnelshift_r(w1, w2, sh);
     }
-    uint32_t slot = scan_hash(klo, khi, c);
-    const uint32_t want = 0x80000000u | (c << 16);
-    bool more = act;
-    do {
-        uint32_t pid = NONE32;
-        if (more) {
-            for (;;) {
-                const uint32_t meta = T->meta[slot];
-                if (meta == 0) { more = false; break; }
-                const bool eq = ((meta & 0xFFFF0000u) == want) && T->klo[slot] == klo && T->khi[slot] == khi;
+    uint32_t classes = __reduce_or_sync(0xffffffffu, cmask);
+    while (classes) {
+        const uint32_t c = __ffs(classes);  // class 1..8, warp-uniform
+        classes &= classes - 1;
+        const uint32_t klo = c >= 4 ? wlo : (wlo & ((1u << (8 * c)) - 1u));
+        const uint32_t khi = c >= 8 ? whi : (c > 4 ? (whi & ((1u << (8 * (c - 4))) - 1u)) : 0u);
+        const uint32_t h = scan_mix(klo, khi, c);
+        const uint32_t want = scan_slot_word(h, c);
+        uint32_t slot = h & (SCAN_H - 1);
+        bool more = (cmask >> (c - 1)) & 1u;
+        do {
+            uint32_t pid = NONE32;
+            while (more) {
+                const uint32_t s = T->slot[slot];
                 slot = (slot + 1) & (SCAN_H - 1);
-                if (eq) {
-                    const uint32_t cand = meta & 0xFFFFu;
-                    bool ok;
-                    if (c < 8) {
-                        ok = (uint64_t)p + c <= a.valid_len;
-                        more = false;  // classes 1..7 have at most one entry per key
-                    } else {
-                        const uint32_t L = a.long_len[cand];
-                        ok = (uint64_t)p + L <= a.valid_len;
-                        if (ok) {
-                            const uint8_t* pat = a.long_blob + a.long_off[cand];
-                            const uint8_t* txt = a.text + p;
-                            for (uint32_t j = 8; j < L; j++)
-                                if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
-                        }
+                if (s == 0) { more = false; break; }
+                if ((s & ~SCAN_PID_MASK) != want) continue;
+                const uint32_t cand = s & SCAN_PID_MASK;
+                if (T->klo[cand] != klo || T->khi[cand] != khi) continue;
+                bool ok;
+                if (c < 8) {
+                    ok = (uint64_t)p + c <= a.valid_len;
+                    more = false;  // classes 1..7 have at most one entry per key
+                } else {
+                    const uint32_t L = a.long_len[cand];
+                    ok = (uint64_t)p + L <= a.valid_len;
+                    if (ok) {
+                        const uint8_t* pat = a.long_blob + a.long_off[cand];
+                        const uint8_t* txt = a.text + p;
+                        for (uint32_t j = 8; j < L; j++)
+                            if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
                     }
-                    // one candidate per round, hit or miss: lanes holding the same key walk the same
-                    // slot sequence, so each pattern is emitted in one round and its list stays sorted
-                    if (ok) pid = cand;
-                    break;
+                }
+                // class 8: one candidate per emit, hit or miss -- lanes holding the same key walk the same
+                // slot sequence, so a pattern is emitted by all its lanes together and its list stays sorted
+                if (ok) pid = cand;
+                break;
+            }
+            // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
+            if (__any_sync(0xffffffffu, pid != NONE32)) {
+                const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+                const int leader = __ffs(grp) - 1;
+                uint32_t old = 0;
+                if (pid != NONE32 && (int)lane == leader) {
+                    const uint32_t sh = (pid & 1u) * 16;
+                    old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+                }
+                if (FILL) {
+                    old = __shfl_sync(0xffffffffu, old, leader);
+                    if (pid != NONE32)
+                        a.out[__ldg(a.list_base + pid) + __ldg(mrow + pid) + old + __popc(grp & lt_mask)] = p;
                 }
             }
-        }
-        // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
-        const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-        const int leader = __ffs(grp) - 1;
-        uint32_t old = 0;
-        if (pid != NONE32 && (int)lane == leader) {
-            const uint32_t sh = (pid & 1u) * 16;
-            old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
-        }
-        if (FILL) {
-            old = __shfl_sync(0xffffffffu, old, leader);
-            if (pid != NONE32) a.out[__ldg(a.list_base + pid) + __ldg(mrow + pid) + old + __popc(grp & lt_mask)] = p;
-        }
-    } while (__any_sync(0xffffffffu, more && c == 8));
+        } while (c == 8 && __any_sync(0xffffffffu, more));
+    }
 }
 
 template <bool FILL, bool SHORT>
@@ -173,7 +189,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     }
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* cur = cursors + warp * (SCAN_S / 2);  // u16 counters, two per word
-    uint32_t* q = queues + warp * SCAN_QCAP;        // circular queue of (position - row start) | class << 16
+    uint32_t* q = queues + warp * SCAN_QCAP;        // circular queue of (position - row start) | class mask << 16
     for (uint32_t i = lane; i < SCAN_S / 2; i += 32) cur[i] = 0u;
     __syncthreads();
 
@@ -223,8 +239,12 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             if (left < 4) { s1 = 0u; s0 &= left ? (0xFFFFFFFFu >> (8 * (4 - left))) : 0u; }
             else if (left < 8) s1 &= left > 4 ? (0xFFFFFFFFu >> (8 * (8 - left))) : 0u;
         }
-        const uint32_t cnt = __popc(s0) + __popc(s1);
-        // ---- position-ordered offsets of the lanes' work items
+        // ---- candidate positions of the lane (non-zero mask bytes), then their place in position order
+        uint32_t nz0 = s0 | (s0 >> 4), nz1 = s1 | (s1 >> 4);
+        nz0 |= nz0 >> 2; nz1 |= nz1 >> 2;
+        nz0 = (nz0 | (nz0 >> 1)) & 0x01010101u;
+        nz1 = (nz1 | (nz1 >> 1)) & 0x01010101u;
+        const uint32_t cnt = __popc(nz0) + __popc(nz1);
         uint32_t incl = cnt;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -233,41 +253,29 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         }
         const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
         if (total == 0) continue;
-        const uint32_t first = incl - cnt;
-        const uint32_t rel0 = off - lo;
-
-        uint32_t done = 0;
-        do {
-            const uint32_t take = min(total - done, (uint32_t)SCAN_QCAP - qcount);
-            // ---- enqueue the items whose index falls into [done, done + take): one loop over the set
-            // bits of the lane's packed masks (ascending position, then ascending class)
-            if (cnt && first < done + take && first + cnt > done) {
-                const uint32_t wbase = qhead + qcount - done;
-                uint32_t idx = first, t0 = s0, t1 = s1;
-                while (t0) {
-                    const uint32_t b = __ffs(t0) - 1;
-                    t0 &= t0 - 1;
-                    if (idx - done < take) q[(wbase + idx) & (SCAN_QCAP - 1)] = (rel0 + (b >> 3)) | (((b & 7u) + 1u) << 16);
-                    idx++;
-                }
-                while (t1) {
-                    const uint32_t b = __ffs(t1) - 1;
-                    t1 &= t1 - 1;
-                    if (idx - done < take) q[(wbase + idx) & (SCAN_QCAP - 1)] = (rel0 + 4u + (b >> 3)) | (((b & 7u) + 1u) << 16);
+        // ---- enqueue (position in row | mask << 16); at most 256 new entries, the queue holds 512 and
+        // starts every step with fewer than 32
+        {
+            uint32_t idx = qhead + qcount + incl - cnt;
+            const uint32_t rel0 = off - lo;
+#pragma unroll
+            for (int j = 0; j < SCAN_PPL; j++) {
+                const uint32_t mj = ((j < 4 ? s0 : s1) >> (8 * (j & 3))) & 0xFFu;
+                if (mj) {
+                    q[idx & (SCAN_QCAP - 1)] = (rel0 + j) | (mj << 16);
                     idx++;
                 }
             }
-            qcount += take;
-            done += take;
-            __syncwarp();
-            // ---- drain full rounds; fewer than 32 leftovers wait for the next step
-            while (qcount >= 32) {
-                scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask);
-                qhead = (qhead + 32) & (SCAN_QCAP - 1);
-                qcount -= 32;
-            }
-            __syncwarp();
-        } while (done < total);
+        }
+        qcount += total;
+        __syncwarp();
+        // ---- drain full rounds; fewer than 32 leftovers wait for the next step
+        while (qcount >= 32) {
+            scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask);
+            qhead = (qhead + 32) & (SCAN_QCAP - 1);
+            qcount -= 32;
+        }
+        __syncwarp();
     }
     if (qcount) scan_drain_round<FILL>(a, T, cur, q, qhead, qcount, lo, mrow, lane, lt_mask);
     if (!FILL) {
@@ -372,11 +380,12 @@ inline void build_pass(const PatternDict& d, uint32_t first, uint32_t count, Pas
         uint64_t key = 0;
         for (uint32_t j = 0; j < len && j < 8; j++) key |= (uint64_t)(uint8_t)s[j] << (8 * j);
         uint32_t klo = (uint32_t)key, khi = (uint32_t)(key >> 32);
-        uint32_t slot = scan_hash(klo, khi, c);
-        while (ph.tables.meta[slot]) slot = (slot + 1) & (SCAN_H - 1);
-        ph.tables.klo[slot] = klo;
-        ph.tables.khi[slot] = khi;
-        ph.tables.meta[slot] = 0x80000000u | (c << 16) | i;
+        const uint32_t h = scan_mix(klo, khi, c);
+        uint32_t slot = h & (SCAN_H - 1);
+        while (ph.tables.slot[slot]) slot = (slot + 1) & (SCAN_H - 1);
+        ph.tables.slot[slot] = scan_slot_word(h, c) | i;
+        ph.tables.klo[i] = klo;
+        ph.tables.khi[i] = khi;
         uint32_t w32 = klo;
         if (c <= 2) ph.has_short = true;
         if (c == 1) {
