@@ -101,10 +101,24 @@ int vlgb_index_build_file(const char* path, vlgb_index** out);
  * outlive the index; it must be 16-byte aligned and >= n+64 bytes must be readable). */
 int vlgb_index_build_device(const uint8_t* text_device, uint64_t n, uint64_t global_offset, uint64_t owned_len,
                             uint64_t total_len, vlgb_index** out);
+/* Integer alphabet (vlg_index<int_alphabet_tag>, vlg_index.hpp:45,133; examples/vlg_matching.cpp:45-61).
+ * symbols[0 .. n) are non-zero integers; global_offset / owned_len / total_len count SYMBOLS.  The
+ * library stores every symbol as W = vlgb_index_symbol_width() bytes (1, 2, 4 or 8: the smallest width
+ * that holds the largest symbol), none of them zero, and runs the same kernels: occurrences are kept
+ * at multiples of W only and every reported position / cursor is a SYMBOL index.  Subpatterns of a
+ * batch searched on such an index must be encoded with vlgb_encode_symbols(W, ...) (pat_bytes then
+ * holds W bytes per symbol); gaps stay in symbols. */
+int vlgb_index_build_symbols(const uint64_t* symbols, uint64_t n, uint64_t global_offset, uint64_t owned_len,
+                             uint64_t total_len, vlgb_index** out);
+uint32_t vlgb_index_symbol_width(const vlgb_index* idx);   /* bytes per symbol: 1 for byte texts */
+/* out[0 .. n*width).  VLGB_ERR_TOO_LARGE if a symbol does not fit `width` bytes (such a subpattern
+ * cannot occur in the text), VLGB_ERR_ZERO_SYMBOL for a 0. */
+int vlgb_encode_symbols(uint32_t width, const uint64_t* symbols, uint64_t n, uint8_t* out);
 int vlgb_index_save(const vlgb_index* idx, const char* path);
 int vlgb_index_load(const char* path, vlgb_index** out);
-uint64_t vlgb_index_size(const vlgb_index* idx);          /* n (shard bytes incl. halo) */
-/* Copy text[pos .. pos+len) of the shard back to the host (vlg_index::text, vlg_index.hpp:141). */
+uint64_t vlgb_index_size(const vlgb_index* idx);          /* n (shard symbols incl. halo) */
+/* Copy text[pos .. pos+len) of the shard back to the host (vlg_index::text, vlg_index.hpp:141).  For a
+ * symbol index pos/len count ENCODED bytes (symbol i occupies bytes [i*W, (i+1)*W)). */
 int vlgb_index_extract(const vlgb_index* idx, uint64_t pos, uint64_t len, uint8_t* out);
 void vlgb_index_free(vlgb_index* idx);
 

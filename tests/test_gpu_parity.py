@@ -223,3 +223,43 @@ def test_full_size_properties_config2(V):
     idx.free()
     small = text[:1 << 20]
     assert compare_with_oracle(V, small, queries[:100]) >= 0
+
+
+def test_int_alphabet_example_block(V):
+    """examples/vlg_matching.cpp:45-61 — the int-alphabet block prints the same tuples as the byte block."""
+    sym = [97, 98, 114, 97, 99, 97, 100, 97, 98, 114, 97, 115, 105, 109, 115, 97, 108, 97, 98, 105, 109]
+    idx = V.construct(sym, 0)
+    assert idx.symbol_width() == 1 and idx.size() == 21
+    assert V.locate(idx, "97 99 .{2,5}? 97 .{4,8}? 98").tolist() == [[3, 10, 18]]
+    assert V.locate(idx, "97 .{0,10}? 97 .{0,10}? 97").tolist() == [[0, 3, 5], [7, 10, 15]]
+    assert V.count(idx, "1337 .{0,10}? 42") == 0          # 1337 cannot occur in a 1-byte-per-symbol index
+    with pytest.raises(ValueError, match="zero symbol"):
+        V.construct([5, 0, 7], 0)
+
+
+@pytest.mark.parametrize("scale,width", [(1, 1), (300, 2), (70000, 4), (1 << 40, 8)])
+def test_int_alphabet_wide_symbols_vs_oracle(V, scale, width):
+    """Symbols of 1/2/4/8 encoded bytes: matching depends on symbol equality only, so the oracle run on
+    the byte text (symbol = byte * scale + 7) must give the same tuples."""
+    from vlg_matching_b200 import capi, synth
+    rng = np.random.default_rng(5 + width)
+    text = rng.integers(1, 5, size=60000, dtype=np.uint8)
+    queries = synth.sample_queries(text, 40, 3, (1, 3), [(0, 5), (2, 40)], 77, False) + \
+        synth.sample_queries(text, 10, 1, (1, 2), [(0, 0)], 78, False)
+    sym = text.astype(np.uint64) * np.uint64(scale) + np.uint64(7)
+    idx = capi.Index.build_symbols(sym)
+    assert idx.symbol_width() == width and idx.size() == text.size
+    enc = [([idx.encode(np.frombuffer(s, dtype=np.uint8).astype(np.uint64) * np.uint64(scale) + np.uint64(7)) for s in subs], gaps)
+           for subs, gaps in queries]
+    r = idx.search(capi.PackedBatch(enc), capi.WANT_TUPLES)
+    ref = O.search(text, queries, want_tuples=True, threads=8)
+    total = 0
+    for q, (st, starts, tup) in enumerate(ref):
+        assert r.status(q) == 0
+        assert r.tuples(q).tolist() == tup.tolist(), (q, queries[q])
+        total += len(starts)
+    assert total > 100
+    # a subpattern that is not a whole number of symbols is an argument error for that query only
+    if width > 1:
+        bad = capi.PackedBatch([([b"\x01"], [])])
+        assert idx.search(bad, capi.WANT_COUNT).status(0) == capi.ERR_ARG

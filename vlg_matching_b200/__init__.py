@@ -34,10 +34,14 @@ class GappedPatternQuery:
 
 
 def construct(text, num_bytes: int = 1) -> Index:
-    """construct(idx, file, 1) / construct_im(idx, data, 1) for the byte alphabet."""
-    if num_bytes != 1:
-        raise NotImplementedError("int-alphabet index (SURVEY §8f row 1) is not built yet")
+    """construct(idx, file, 1) / construct_im(idx, data, 1) for the byte alphabet; num_bytes = 0 with a
+    sequence of non-zero integers builds the int-alphabet index (vlg_index<int_alphabet_tag>,
+    examples/vlg_matching.cpp:45-61)."""
+    if num_bytes not in (0, 1):
+        raise ValueError("num_bytes must be 1 (bytes) or 0 (integer symbols)")
     try:
+        if num_bytes == 0:
+            return Index.build_symbols(np.asarray(text, dtype=np.uint64))
         if isinstance(text, str):
             return Index.build_file(text)
         return Index.build(text)
@@ -53,10 +57,36 @@ def _query(q):
     return GappedPatternQuery(q)
 
 
+def _int_symbols(sub: bytes):
+    """Subpattern of the int alphabet: whitespace-separated decimals, read like `while (ss >> symbol)`
+    (vlg_index.hpp:63-69): stops at the first token that is not a number."""
+    out = []
+    for tok in sub.split():
+        if not tok.isdigit():
+            break
+        out.append(int(tok))
+    return out
+
+
+def _batch_for(idx: Index, q: GappedPatternQuery):
+    """-> PackedBatch, or None when a subpattern holds a symbol that cannot occur in an int-alphabet index."""
+    if idx.symbol_width() == 1 and not getattr(idx, "int_alphabet", False):
+        return PackedBatch([(q.subpatterns, q.raw_gaps)])
+    subs = []
+    for s in q.subpatterns:
+        e = idx.encode(_int_symbols(s))
+        if e is None:
+            return None
+        subs.append(e)
+    return PackedBatch([(subs, q.raw_gaps)])
+
+
 def locate(idx: Index, query) -> np.ndarray:
     """-> uint64 array [count, k]: row m holds it[0..k) of the m-th match (ascending start)."""
     q = _query(query)
-    b = PackedBatch([(q.subpatterns, q.raw_gaps)])
+    b = _batch_for(idx, q)
+    if b is None:
+        return np.zeros((0, len(q.subpatterns)), dtype=np.uint64)
     r = idx.search(b, WANT_TUPLES)
     st = r.status(0)
     if st != 0:
@@ -66,7 +96,10 @@ def locate(idx: Index, query) -> np.ndarray:
 
 def count(idx: Index, query) -> int:
     q = _query(query)
-    r = idx.search(PackedBatch([(q.subpatterns, q.raw_gaps)]), WANT_COUNT)
+    b = _batch_for(idx, q)
+    if b is None:
+        return 0
+    r = idx.search(b, WANT_COUNT)
     if r.status(0) != 0:
         raise ValueError(f"query rejected with status {r.status(0)}")
     return int(r.counts()[0])

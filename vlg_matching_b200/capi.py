@@ -29,7 +29,7 @@ SYMBOLS = [
     "vlgb_result_status", "vlgb_result_count", "vlgb_result_total", "vlgb_result_counts", "vlgb_result_starts",
     "vlgb_result_tuples", "vlgb_result_exit_cursors", "vlgb_result_first_starts", "vlgb_result_occurrences",
     "vlgb_result_fixup", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
-    "vlgb_stream_handle",
+    "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
 ]
 
 
@@ -96,6 +96,10 @@ lib.vlgb_stage_name.argtypes = [C.c_uint32]
 lib.vlgb_stage_name.restype = C.c_char_p
 lib.vlgb_set_tuning.argtypes = [C.c_uint64, C.c_uint64]
 lib.vlgb_stream_handle.restype = C.c_void_p
+lib.vlgb_index_build_symbols.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_P)]
+lib.vlgb_index_symbol_width.argtypes = [_P]
+lib.vlgb_index_symbol_width.restype = C.c_uint32
+lib.vlgb_encode_symbols.argtypes = [C.c_uint32, _P, C.c_uint64, _P]
 
 
 def check(rc):
@@ -244,6 +248,32 @@ class Index:
         check(lib.vlgb_index_build(text.ctypes.data if n else None, n, global_offset, n if owned_len is None else owned_len,
                                    (global_offset + n) if total_len is None else total_len, C.byref(h)))
         return cls(h)
+
+    @classmethod
+    def build_symbols(cls, symbols, global_offset=0, owned_len=None, total_len=None):
+        """Integer alphabet (vlg_index<int_alphabet_tag>): non-zero integers, positions count symbols."""
+        sym = np.ascontiguousarray(symbols, dtype=np.uint64)
+        n = sym.size
+        h = _P()
+        check(lib.vlgb_index_build_symbols(sym.ctypes.data if n else None, n, global_offset, n if owned_len is None else owned_len,
+                                           (global_offset + n) if total_len is None else total_len, C.byref(h)))
+        r = cls(h)
+        r.int_alphabet = True
+        return r
+
+    def symbol_width(self) -> int:
+        return lib.vlgb_index_symbol_width(self.h)
+
+    def encode(self, symbols):
+        """-> bytes of a subpattern given as integers, or None if a symbol cannot occur in this index."""
+        sym = np.ascontiguousarray(symbols, dtype=np.uint64)
+        w = self.symbol_width()
+        out = np.zeros(max(sym.size * w, 1), dtype=np.uint8)
+        rc = lib.vlgb_encode_symbols(w, sym.ctypes.data if sym.size else None, sym.size, out.ctypes.data)
+        if rc in (ERR_TOO_LARGE, ERR_ZERO_SYMBOL):
+            return None
+        check(rc)
+        return out[:sym.size * w].tobytes()
 
     @classmethod
     def build_device(cls, ptr: int, n: int, global_offset=0, owned_len=None, total_len=None):

@@ -226,6 +226,11 @@ __host__ __device__ inline uint64_t sat_add64(uint64_t a, uint64_t b)
     return a > ~uint64_t(0) - b ? ~uint64_t(0) : a + b;
 }
 
+__host__ __device__ inline uint64_t sat_shl64(uint64_t a, uint32_t sh)
+{
+    return sh && (a >> (64 - sh)) ? ~uint64_t(0) : a << sh;
+}
+
 constexpr uint32_t NONE32 = 0xFFFFFFFFu;
 
 }  // namespace vlgb

@@ -18,7 +18,8 @@ using namespace vlgb;
 struct vlgb_index {
     uint8_t* d_text = nullptr;  // n + PAD readable bytes
     bool owns = false;
-    uint64_t n = 0, global_offset = 0, owned_len = 0, total_len = 0;
+    uint64_t n = 0, global_offset = 0, owned_len = 0, total_len = 0;  // all in BYTES
+    uint32_t sym_shift = 0;  // log2(bytes per symbol): 0 = byte text, 1..3 = encoded integer alphabet
 };
 static constexpr uint64_t TEXT_PAD = 64;
 static constexpr uint64_t MAX_SHARD = 0xFFFFF000ull;  // positions are shard-local u32 on the device
@@ -259,9 +260,10 @@ extern "C" int vlgb_index_build_file(const char* path, vlgb_index** out)
     return rc;
 }
 
-// on-disk: magic, n, global_offset, owned_len, total_len, text bytes (vlg_index::serialize writes
-// text then wt, vlg_index.hpp:183-191; there is no wavelet tree here)
-static const char INDEX_MAGIC[8] = {'V', 'L', 'G', 'B', '2', '0', '0', '\1'};
+// on-disk: magic, {n, global_offset, owned_len, total_len (bytes), sym_shift}, text bytes (vlg_index::serialize
+// writes text then wt, vlg_index.hpp:183-191; there is no wavelet tree here)
+static const char INDEX_MAGIC[8] = {'V', 'L', 'G', 'B', '2', '0', '0', '\2'};
+static constexpr size_t INDEX_HDR = 8 + 5 * 8;
 
 extern "C" int vlgb_index_save(const vlgb_index* idx, const char* path)
 {
@@ -272,8 +274,8 @@ extern "C" int vlgb_index_save(const vlgb_index* idx, const char* path)
         if (idx->n) VLGB_CUDA(cudaMemcpy(buf.data(), idx->d_text, idx->n, cudaMemcpyDeviceToHost));
         FILE* f = fopen(path, "wb");
         if (!f) return fail(VLGB_ERR_IO, "cannot create %s", path);
-        uint64_t hdr[4] = {idx->n, idx->global_offset, idx->owned_len, idx->total_len};
-        bool ok = fwrite(INDEX_MAGIC, 1, 8, f) == 8 && fwrite(hdr, 8, 4, f) == 4 &&
+        uint64_t hdr[5] = {idx->n, idx->global_offset, idx->owned_len, idx->total_len, idx->sym_shift};
+        bool ok = fwrite(INDEX_MAGIC, 1, 8, f) == 8 && fwrite(hdr, 8, 5, f) == 5 &&
                   (idx->n == 0 || fwrite(buf.data(), 1, idx->n, f) == idx->n);
         ok = (fclose(f) == 0) && ok;
         return ok ? VLGB_OK : fail(VLGB_ERR_IO, "write to %s failed", path);
@@ -289,14 +291,66 @@ extern "C" int vlgb_index_load(const char* path, vlgb_index** out)
     std::vector<uint8_t> buf;
     int rc = read_file(path, buf, 0);
     if (rc) return rc;
-    if (buf.size() < 40 || memcmp(buf.data(), INDEX_MAGIC, 8) != 0) return fail(VLGB_ERR_IO, "%s: not a vlgb200 index", path);
-    uint64_t hdr[4];
-    memcpy(hdr, buf.data() + 8, 32);
-    if (buf.size() - 40 != hdr[0]) return fail(VLGB_ERR_IO, "%s: size mismatch", path);
-    return vlgb_index_build(buf.data() + 40, hdr[0], hdr[1], hdr[2], hdr[3], out);
+    if (buf.size() < INDEX_HDR || memcmp(buf.data(), INDEX_MAGIC, 8) != 0) return fail(VLGB_ERR_IO, "%s: not a vlgb200 index", path);
+    uint64_t hdr[5];
+    memcpy(hdr, buf.data() + 8, 40);
+    if (buf.size() - INDEX_HDR != hdr[0] || hdr[4] > 3) return fail(VLGB_ERR_IO, "%s: size mismatch", path);
+    rc = vlgb_index_build(buf.data() + INDEX_HDR, hdr[0], hdr[1], hdr[2], hdr[3], out);
+    if (rc == VLGB_OK) (*out)->sym_shift = (uint32_t)hdr[4];
+    return rc;
 }
 
-extern "C" uint64_t vlgb_index_size(const vlgb_index* idx) { return idx ? idx->n : 0; }
+// ---- integer alphabets (vlg_index<int_alphabet_tag>, vlg_index.hpp:45,133): every symbol becomes W bytes
+// (W = 1, 2, 4 or 8, the smallest that holds the largest symbol of the text), none of them 0, so the byte
+// kernels apply unchanged: occurrences are kept only at multiples of W and positions are divided by W.
+//   W = 1: the byte IS the symbol (1..255);  W > 1: big-endian base-255 digits, each stored + 1.
+static const uint64_t SYM_LIMIT[4] = {256ull, 255ull * 255ull, 255ull * 255ull * 255ull * 255ull,
+                                      17878103347812890625ull /* 255^8 */};
+
+extern "C" int vlgb_encode_symbols(uint32_t width, const uint64_t* symbols, uint64_t n, uint8_t* out)
+{
+    if ((width != 1 && width != 2 && width != 4 && width != 8) || (n && (!symbols || !out)))
+        return fail(VLGB_ERR_ARG, "vlgb_encode_symbols: bad argument");
+    const uint32_t sh = width == 1 ? 0 : width == 2 ? 1 : width == 4 ? 2 : 3;
+    for (uint64_t i = 0; i < n; i++) {
+        uint64_t v = symbols[i];
+        if (v == 0) return fail(VLGB_ERR_ZERO_SYMBOL, "Error: symbol sequence contains zero symbol.");
+        if (v >= SYM_LIMIT[sh]) return fail(VLGB_ERR_TOO_LARGE, "symbol %llu does not fit %u encoded bytes", (unsigned long long)v, width);
+        uint8_t* o = out + i * width;
+        if (width == 1) { o[0] = (uint8_t)v; continue; }
+        for (int d = (int)width - 1; d >= 0; d--) {
+            o[d] = (uint8_t)(v % 255 + 1);
+            v /= 255;
+        }
+    }
+    return VLGB_OK;
+}
+
+extern "C" int vlgb_index_build_symbols(const uint64_t* symbols, uint64_t n, uint64_t global_offset, uint64_t owned_len,
+                                        uint64_t total_len, vlgb_index** out)
+{
+    if (!out || (!symbols && n)) return fail(VLGB_ERR_ARG, "vlgb_index_build_symbols: null argument");
+    *out = nullptr;
+    uint64_t mx = 0;
+    for (uint64_t i = 0; i < n; i++) {
+        if (symbols[i] == 0) return fail(VLGB_ERR_ZERO_SYMBOL, "Error: File \"<memory>\" contains zero symbol.");
+        mx = std::max(mx, symbols[i]);
+    }
+    uint32_t sh = 0;
+    while (sh < 3 && mx >= SYM_LIMIT[sh]) sh++;
+    if (mx >= SYM_LIMIT[sh]) return fail(VLGB_ERR_TOO_LARGE, "symbol %llu is not representable", (unsigned long long)mx);
+    if (n > (MAX_SHARD >> sh)) return fail(VLGB_ERR_TOO_LARGE, "vlgb_index_build_symbols: shard too large (split the text into shards)");
+    std::vector<uint8_t> enc((size_t)n << sh);
+    int rc = vlgb_encode_symbols(1u << sh, symbols, n, enc.data());
+    if (rc) return rc;
+    rc = vlgb_index_build(enc.data(), n << sh, global_offset << sh, owned_len << sh, total_len << sh, out);
+    if (rc == VLGB_OK) (*out)->sym_shift = sh;
+    return rc;
+}
+
+extern "C" uint32_t vlgb_index_symbol_width(const vlgb_index* idx) { return idx ? 1u << idx->sym_shift : 0; }
+
+extern "C" uint64_t vlgb_index_size(const vlgb_index* idx) { return idx ? idx->n >> idx->sym_shift : 0; }
 
 extern "C" int vlgb_index_extract(const vlgb_index* idx, uint64_t pos, uint64_t len, uint8_t* out)
 {
@@ -399,15 +453,17 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
         uint32_t s0 = batch->sub_off[q], s1 = batch->sub_off[q + 1], k = s1 - s0;
         if (k == 0) { R.status[q] = VLGB_ERR_ARG; continue; }
         if (k > (uint32_t)MAX_K) { R.status[q] = VLGB_ERR_TOO_LARGE; continue; }
-        bool empty_sub = false;
+        bool empty_sub = false, bad_width = false;
         uint64_t span = 0;
         for (uint32_t s = s0; s < s1; s++) {
             uint64_t len = batch->pat_off[s + 1] - batch->pat_off[s];
             if (len == 0) empty_sub = true;
+            if (len & ((1u << idx->sym_shift) - 1u)) bad_width = true;
             span = sat_add64(span, len);
-            if (s + 1 < s1) span = sat_add64(span, batch->gap_max[s]);
+            if (s + 1 < s1) span = sat_add64(span, sat_shl64(batch->gap_max[s], idx->sym_shift));
         }
         if (empty_sub) { R.status[q] = VLGB_ERR_EMPTY_SUB; continue; }  // SURVEY A.4 fence
+        if (bad_width) { R.status[q] = VLGB_ERR_ARG; continue; }        // not a whole number of encoded symbols
         // a match that starts in the owned part must end inside owned + halo
         if (halo_truncated_by_shard && span > halo + 1) { R.status[q] = VLGB_ERR_TOO_LARGE; continue; }
         bool impossible = false;
@@ -422,8 +478,8 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
 
     // ---- scan: one sorted occurrence list per distinct subpattern
     ScanOut so;
-    run_scan(c, idx->d_text, idx->n, idx->owned_len, dict, so);
-    BatchView view{batch, &sub_pid, &so, idx->global_offset};
+    run_scan(c, idx->d_text, idx->n, idx->owned_len, idx->sym_shift, dict, so);
+    BatchView view{batch, &sub_pid, &so, idx->global_offset, idx->sym_shift};
 
     // queries with an empty list have no match (vlg_index.hpp:316)
     std::vector<PlanQuery> live;

@@ -82,6 +82,8 @@ struct ScanArgs {
     uint32_t s_act;          // patterns in this pass
     uint32_t s_stride;       // row stride of the count matrix (multiple of 32)
     uint32_t has_short;      // the pass holds 1- or 2-byte patterns
+    uint32_t align0, align1; // byte masks of the positions j = 0..3 / 4..7 of a lane that are symbol-aligned
+                             // (all ones for byte texts; W-byte symbols start at multiples of W)
     const ScanTables* tables;
     const uint32_t* long_len;  // [s_act] full length (class 8 only: len >= 8)
     const uint32_t* long_off;  // [s_act] offset into long_blob
@@ -234,6 +236,8 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             }
             if (j < 4) s0 |= mj << (8 * j); else s1 |= mj << (8 * (j - 4));
         }
+        s0 &= a.align0;
+        s1 &= a.align1;
         if (base + SCAN_STEP > hi) {  // last step of the row: positions >= hi belong to the next row (or nobody)
             const uint32_t left = off < hi ? hi - off : 0u;  // my positions j < left are inside
             if (left < 4) { s1 = 0u; s0 &= left ? (0xFFFFFFFFu >> (8 * (4 - left))) : 0u; }

@@ -71,8 +71,8 @@ inline uint32_t scan_chunk_for(uint64_t n, int sm_count)
     return (uint32_t)c;
 }
 
-inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t owned_len, const PatternDict& dict,
-                     ScanOut& so)
+inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t owned_len, uint32_t sym_shift,
+                     const PatternDict& dict, ScanOut& so)
 {
     const uint32_t P = (uint32_t)dict.pats.size();
     so.tot.assign(P, 0);
@@ -143,6 +143,10 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.s_act = pd[p].s_act;
         a.s_stride = pd[p].stride;
         a.has_short = pd[p].has_short;
+        static const uint32_t al0[4] = {0xFFFFFFFFu, 0x00FF00FFu, 0x000000FFu, 0x000000FFu};
+        static const uint32_t al1[4] = {0xFFFFFFFFu, 0x00FF00FFu, 0x000000FFu, 0u};
+        a.align0 = al0[sym_shift];
+        a.align1 = al1[sym_shift];
         a.tables = dev_at<const ScanTables>(d_ctl, pd[p].o_tables);
         a.long_len = dev_at<const uint32_t>(d_ctl, pd[p].o_len);
         a.long_off = dev_at<const uint32_t>(d_ctl, pd[p].o_off);
@@ -244,7 +248,8 @@ struct BatchView {
     const vlgb_batch* b;
     const std::vector<uint32_t>* sub_pid;
     const ScanOut* so;
-    uint64_t global_offset;
+    uint64_t global_offset;  // bytes
+    uint32_t sym_shift;      // log2(bytes per symbol)
 };
 
 inline uint64_t list_len(const BatchView& v, uint32_t sub, bool level0)
@@ -307,8 +312,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             h.slot_off[s] = (uint32_t)run;
             run += list_len(v, sub, lvl == 0);
             h.left[s] = list_ptr(sub);
-            h.lo[s] = sat_add64(B.gap_min[sub], plen(sub));  // start-to-start bounds, vlg_index.hpp:95
-            h.hi[s] = sat_add64(B.gap_max[sub], plen(sub));
+            // start-to-start bounds, vlg_index.hpp:95, in bytes (gaps are given in symbols)
+            h.lo[s] = sat_add64(sat_shl64(B.gap_min[sub], v.sym_shift), plen(sub));
+            h.hi[s] = sat_add64(sat_shl64(B.gap_max[sub], v.sym_shift), plen(sub));
             if (d == 1) {
                 h.right_list[s] = list_ptr(pq.s0 + pq.k - 1);
                 h.right_len[s] = (uint32_t)list_len(v, pq.s0 + pq.k - 1, false);
@@ -333,7 +339,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         kq[s] = pq.k;
         uint64_t ll = plen(pq.s0 + pq.k - 1);
         last_len[s] = ll > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)ll;
-        entry_local[s] = pq.entry > v.global_offset ? pq.entry - v.global_offset : 0;
+        const uint64_t entry_bytes = sat_shl64(pq.entry, v.sym_shift);
+        entry_local[s] = entry_bytes > v.global_offset ? entry_bytes - v.global_offset : 0;
         exit_init[s] = pq.entry;
         list0[s] = list_ptr(pq.s0);
         list0_len[s] = (uint32_t)l0;
@@ -464,6 +471,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.depth_vseg = S.depth_vpos + 3 * MAX_K;
     S.last_list = dev_at<const uint32_t* const>(d_ctl, o_last_list);
     S.global_offset = v.global_offset;
+    S.sym_shift = v.sym_shift;
     S.v0 = d_v0;
     S.vlast = d_vlast;
     S.v0_len = d_v0_len;

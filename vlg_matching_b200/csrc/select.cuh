@@ -42,7 +42,8 @@ struct SelDesc {
     const uint32_t* const* depth_vlast;
     const uint32_t* const* depth_vseg;
     const uint32_t* const* last_list;    // scan list of the last subpattern (tuple resolve at depth 1)
-    uint64_t global_offset;
+    uint64_t global_offset;      // of the shard, in BYTES (symbol offset << sym_shift)
+    uint32_t sym_shift;          // log2(bytes per symbol): 0 for byte texts; reported positions are >> sym_shift
     // resolved per query
     const uint32_t** v0;
     const uint32_t** vlast;      // nullptr entry for k = 1
@@ -107,7 +108,8 @@ __global__ void __launch_bounds__(SEL_TILE) sel_succ_kernel(SelDesc s)
     const uint32_t x = __ldg(v + t);
     const uint32_t ll = s.last_len[q];
     uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
-    if (!vl && ll == 1 && (((uint64_t)x + s.global_offset) & 1ull) == 0) e = (uint64_t)x + 2;  // k = 1 sibling skip
+    if (!vl && ll == (1u << s.sym_shift) && ((((uint64_t)x + s.global_offset) >> s.sym_shift) & 1ull) == 0)
+        e = (uint64_t)x + (2u << s.sym_shift);  // k = 1 sibling skip
     s.succ[slot0 + threadIdx.x] = gallop_lower_bound(v, t + 1, len, e);
 }
 
@@ -215,23 +217,24 @@ __global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
     const uint32_t k = s.kq[q];
     const uint32_t x = __ldg(s.v0[q] + t);
     const uint64_t g = s.global_offset;
-    if (s.starts) s.starts[o] = g + x;
-    if (o == qfirst) s.first_start[q] = g + x;
+    const uint32_t sh = s.sym_shift;
+    if (s.starts) s.starts[o] = (g + x) >> sh;
+    if (o == qfirst) s.first_start[q] = (g + x) >> sh;
     const uint32_t* vl = s.vlast[q];
     if (o + 1 == qend) {  // last match of the query: the cursor it leaves behind
         const uint32_t ll = s.last_len[q];
         uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
-        if (!vl && ll == 1 && (((uint64_t)x + g) & 1ull) == 0) e = (uint64_t)x + 2;
-        s.exit_cursor[q] = g + e;
+        if (!vl && ll == (1u << sh) && ((((uint64_t)x + g) >> sh) & 1ull) == 0) e = (uint64_t)x + (2u << sh);
+        s.exit_cursor[q] = (g + e) >> sh;
     }
     if (s.tuples) {
         uint64_t* out = s.tuples + s.tuple_off[q] + (uint64_t)(o - qfirst) * k;
-        out[0] = g + x;
+        out[0] = (g + x) >> sh;
         uint32_t idx = t;
         for (uint32_t d = k - 1, i = 1; d >= 1; d--, i++) {
             idx = __ldg(s.depth_vnxt[d] + s.depth_vseg[d][q] + idx);
             uint32_t pos = d > 1 ? __ldg(s.depth_vpos[d - 1] + s.depth_vseg[d - 1][q] + idx) : __ldg(s.last_list[q] + idx);
-            out[i] = g + pos;
+            out[i] = (g + pos) >> sh;
         }
     }
 }
