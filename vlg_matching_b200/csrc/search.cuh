@@ -350,6 +350,16 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     sel_off[nq] = (uint32_t)sel_run;
     const uint32_t sel_total = (uint32_t)sel_run;
     const uint32_t ntiles = sel_total / SEL_TILE;
+    std::vector<uint32_t> chunk_q, chunk_tile0, q_chunk0(nq);
+    for (uint32_t s = 0; s < nq; s++) {
+        q_chunk0[s] = (uint32_t)chunk_q.size();
+        const uint32_t t0 = sel_off[s] / SEL_TILE, t1 = sel_off[s + 1] / SEL_TILE;
+        for (uint32_t t = t0; t < t1; t += SEL_CHUNK_TILES) {
+            chunk_q.push_back(s);
+            chunk_tile0.push_back(t);
+        }
+    }
+    const uint32_t nchunks = (uint32_t)chunk_q.size();
 
     // ---- control blob
     Packer ctl;
@@ -366,7 +376,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     }
     const size_t o_sel_off = ctl.put(sel_off), o_kq = ctl.put(kq), o_last_len = ctl.put(last_len),
                  o_entry = ctl.put(entry_local), o_exit = ctl.put(exit_init), o_first = ctl.put(first_init), o_list0 = ctl.put(list0),
-                 o_list0_len = ctl.put(list0_len), o_last_list = ctl.put(last_list);
+                 o_list0_len = ctl.put(list0_len), o_last_list = ctl.put(last_list), o_chunk_q = ctl.put(chunk_q),
+                 o_chunk_tile0 = ctl.put(chunk_tile0), o_q_chunk0 = ctl.put(q_chunk0);
     std::vector<const uint32_t*> tab(4 * MAX_K, nullptr);  // depth_vpos | depth_vnxt | depth_vlast | depth_vseg
     const size_t o_tab = ctl.put(tab);                     // patched below once the arena addresses are known
     std::vector<uint64_t> zeros64(nq, 0);
@@ -379,7 +390,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
     need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
     need += 2 * Arena::padded(sel_total, 4) + Arena::padded(sel_total, 1);             // succ, exitp, flags
-    need += Arena::padded(ntiles + 1, 4) + Arena::padded((size_t)sel_total + 1, 4);    // entry, mrank
+    need += 2 * Arena::padded(ntiles + 1, 4) + Arena::padded((size_t)sel_total + 1, 4);  // entry, spec, mrank
+    need += 2 * Arena::padded(nchunks + 1, 4);                                         // spec_exit, coalesce
     need += Arena::padded(nq, 8) + Arena::padded(kmax + 1, 4);                         // counts, viable totals
     const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(max_slots, sel_total));
     need += Arena::padded(scratch_words, 4);
@@ -408,6 +420,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     uint32_t* d_exitp = A.take<uint32_t>(sel_total);
     uint8_t* d_flags = A.take<uint8_t>(sel_total);
     uint32_t* d_entry = A.take<uint32_t>(ntiles + 1);
+    uint32_t* d_spec = A.take<uint32_t>(ntiles + 1);
+    uint32_t* d_spec_exit = A.take<uint32_t>(nchunks + 1);
+    uint32_t* d_coalesce = A.take<uint32_t>(nchunks + 1);
     uint32_t* d_mrank = A.take<uint32_t>((size_t)sel_total + 1);
     uint64_t* d_counts = A.take<uint64_t>(nq);
     uint32_t* d_viable = A.take<uint32_t>(kmax + 1);
@@ -480,6 +495,13 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.exitp = d_exitp;
     S.flags = d_flags;
     S.entry = d_entry;
+    S.nchunks = nchunks;
+    S.chunk_q = dev_at<const uint32_t>(d_ctl, o_chunk_q);
+    S.chunk_tile0 = dev_at<const uint32_t>(d_ctl, o_chunk_tile0);
+    S.q_chunk0 = dev_at<const uint32_t>(d_ctl, o_q_chunk0);
+    S.spec = d_spec;
+    S.spec_exit = d_spec_exit;
+    S.coalesce = d_coalesce;
     S.mrank = d_mrank;
     S.tuple_off = dev_at<const uint64_t>(d_ctl, o_tuple_off);
     S.starts = nullptr;
@@ -506,10 +528,14 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 8);
         c.begin(ST_SELECT_WALK);
         VLGB_CUDA(cudaMemsetAsync(d_entry, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
+        VLGB_CUDA(cudaMemsetAsync(d_spec, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
+        VLGB_CUDA(cudaMemsetAsync(d_coalesce, 0xFF, (size_t)(nchunks + 1) * 4, c.stream));
         VLGB_CUDA(cudaMemsetAsync(d_flags, 0, sel_total, c.stream));
+        sel_spec_kernel<<<(nchunks + 31) / 32, 32, 0, c.stream>>>(S);
         sel_walk_kernel<<<(nq + 31) / 32, 32, 0, c.stream>>>(S);
+        sel_entry_kernel<<<(ntiles + 255) / 256, 256, 0, c.stream>>>(S);
         sel_mark_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
-        c.end(ST_SELECT_WALK, 2, (uint64_t)sel_total * 5);
+        c.end(ST_SELECT_WALK, 4, (uint64_t)sel_total * 5);
         c.begin(ST_EMIT);
         uint32_t l = exclusive_scan(FlagByte{d_flags}, sel_total, d_mrank, scratch, c.stream);
         sel_counts_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);

@@ -14,7 +14,12 @@
 //   succ    : succ[slot]                                                    (gallop from t+1)
 //   tile    : exitp[slot] = first orbit element of slot that lies outside its tile (pointer doubling
 //             in shared memory, log2(TILE) rounds)
-//   walk    : one thread per query hops tile to tile: entry[tile] = first selected element in it
+//   spec    : one thread per CHUNK of 64 tiles hops tile to tile from the chunk's first element (a guess)
+//   walk    : one thread per query hops from the true start; orbits of a monotone successor coalesce, so
+//             inside a chunk it soon lands on an element the speculative hop also visited and jumps to that
+//             chunk's recorded exit: ~chunks x (a few hops) dependent loads instead of one per tile
+//   entry   : entry[tile] = first selected element in the tile (true hops before the coalescing point,
+//             speculative ones after it)
 //   mark    : per entered tile, flags[slot] = 1 for the orbit of entry[tile] (doubling again)
 //   prefix  : mrank = exclusive scan of flags                               (prefix.cuh)
 //   emit    : starts / tuples / exit cursor
@@ -25,6 +30,7 @@ namespace vlgb {
 
 constexpr int SEL_TILE = 1024;  // = threads per CTA of the tile kernels
 constexpr int SEL_LOG = 10;
+constexpr int SEL_CHUNK_TILES = 64;  // tiles per speculative chunk
 
 struct SelDesc {
     uint32_t nq;                 // queries of the chunk
@@ -54,6 +60,14 @@ struct SelDesc {
     uint32_t* exitp;
     uint8_t* flags;
     uint32_t* entry;             // [total_slots / SEL_TILE]
+    // speculative chunks (SEL_CHUNK_TILES tiles of one query each)
+    uint32_t nchunks;
+    const uint32_t* chunk_q;     // [nchunks] query of the chunk
+    const uint32_t* chunk_tile0; // [nchunks] first tile (global tile index)
+    const uint32_t* q_chunk0;    // [nq] first chunk of the query
+    uint32_t* spec;              // [tiles] element the speculative hop entered the tile with (NONE32: not visited)
+    uint32_t* spec_exit;         // [nchunks] where the speculative hop left the chunk
+    uint32_t* coalesce;          // [nchunks] first tile from which the speculative entries are the true ones
     uint32_t* mrank;             // [total_slots + 1]
     // emission
     const uint64_t* tuple_off;   // [nq] first tuple word of each query (host prefix over count*k)
@@ -147,6 +161,23 @@ __global__ void __launch_bounds__(SEL_TILE) sel_tile_kernel(SelDesc s)
     if (t < len) s.exitp[slot0 + threadIdx.x] = p;
 }
 
+__global__ void sel_spec_kernel(SelDesc s)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= s.nchunks) return;
+    const uint32_t q = s.chunk_q[c];
+    const uint32_t off = s.sel_off[q];
+    const uint32_t len = s.v0_len[q];
+    const uint32_t first = s.chunk_tile0[c] * SEL_TILE - off;  // V_0 index of the chunk's first element
+    const uint32_t end = min(len, first + SEL_CHUNK_TILES * SEL_TILE);
+    uint32_t cur = max(first, s.t0[q]);  // the chunk that holds t0 starts on the true orbit
+    while (cur < end) {
+        s.spec[(off + cur) / SEL_TILE] = cur;
+        cur = s.exitp[off + cur];
+    }
+    s.spec_exit[c] = cur;
+}
+
 __global__ void sel_walk_kernel(SelDesc s)
 {
     // one thread per query; spread over warps so that long walks do not serialise 32 short ones
@@ -154,11 +185,29 @@ __global__ void sel_walk_kernel(SelDesc s)
     if (q >= s.nq) return;
     const uint32_t len = s.v0_len[q];
     const uint32_t off = s.sel_off[q];
+    const uint32_t tile_first = off / SEL_TILE, c0 = s.q_chunk0[q];
     uint32_t cur = s.t0[q];
     while (cur < len) {
-        s.entry[(off + cur) / SEL_TILE] = cur;
+        const uint32_t tile = (off + cur) / SEL_TILE;
+        const uint32_t c = c0 + (tile - tile_first) / SEL_CHUNK_TILES;
+        if (s.spec[tile] == cur) {  // from here on the speculative hops of this chunk are the true ones
+            s.coalesce[c] = tile;
+            cur = s.spec_exit[c];
+            continue;
+        }
+        s.entry[tile] = cur;
         cur = s.exitp[off + cur];
     }
+}
+
+__global__ void sel_entry_kernel(SelDesc s)
+{
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= s.total_slots / SEL_TILE) return;
+    const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);
+    const uint32_t c = s.q_chunk0[q] + (tile - s.sel_off[q] / SEL_TILE) / SEL_CHUNK_TILES;
+    const uint32_t from = s.coalesce[c];
+    if (from != NONE32 && tile >= from) s.entry[tile] = s.spec[tile];
 }
 
 __global__ void __launch_bounds__(SEL_TILE) sel_mark_kernel(SelDesc s)
