@@ -6,17 +6,21 @@
 // y >= x + lo_i exists and y <= x + hi_i   (lo_i = a_i + |P_i|, hi_i = b_i + |P_i|, vlg_index.hpp:95).
 //
 // One "depth" d = k-1-i is processed per launch for ALL queries of the chunk that have such a level.
-// The slots of a depth are the concatenation of the left lists (one segment per query):
-//   probe   : raw[slot]  = lower_bound(V_right, x + lo)  if V_right[.] <= x + hi   else NONE
-//   prefix  : rank[slot] = exclusive prefix of (raw != NONE)                       (prefix.cuh)
-//   compact : vpos / vnxt / vlast [rank[slot]] = x / raw / last position of the completed tuple
-// vseg[seg] = rank[slot_off[seg]] gives every query its segment inside the compacted arrays, so no size
-// ever has to travel to the host between depths.
+// The slots of a depth are the concatenation of the left lists (one segment per query), cut into tiles of
+// 4096 slots:
+//   probe   : raw[slot] = j = lower_bound(V_right, x + lo) if V_right[j] <= x + hi, else NONE; viable count per tile
+//   prefix  : exclusive scan of the tile counts (prefix.cuh; ~1 value per 4096 slots)
+//   compact : in-tile ranks by warp ballots; vpos / vnxt / vlast [rank] = x / j / last position of the tuple
+// (A single-pass variant with a decoupled look-back was measured slower: probe times per tile vary widely and
+// the look-back makes every wave wait for its slowest tile.)
+// vseg[seg] = rank of the segment's first slot gives every query its segment inside the compacted arrays, so
+// no size ever has to travel to the host between depths.
 //
-// Both lists are ascending and x + lo is monotone in x, so neighbouring lanes probe neighbouring
-// places of the right list: lane 0 of a warp does the full binary search, the other lanes gallop from
-// lane 0's answer (a warp-cooperative merge step; the loads of a warp fall into one or two sectors).
-// Algorithmic bytes per slot: probe 4 (x) + 4 (right) + 4 (raw); compact 4+4+4+4 read, 12 written.
+// Both lists are ascending and x + lo is monotone in x, so a tile of consecutive slots maps to one contiguous
+// window of the right list (a merge-path partition): the window is staged in shared memory when it is small,
+// else the lanes gallop from their neighbours' answers.
+// Algorithmic bytes per depth: 4 B per slot (x) + 4 B per right-list element + 8 B per slot (raw out / in) +
+// 16 B per viable slot (x again, vlast gather; 12 written... counted as 4 + 4 + 12).
 #pragma once
 #include "common.cuh"
 
@@ -41,8 +45,11 @@ struct DepthDesc {
     const uint64_t* lo;          // start-to-start lower bound of this level (saturated)
     const uint64_t* hi;
     // outputs
-    uint32_t* raw;               // [total_slots]
-    uint32_t* rank;              // [total_slots+1]
+    uint32_t* raw;               // [total_slots] index into the right list, NONE32 = not viable
+    uint32_t* tile_count;        // [tiles] viable slots per tile
+    const uint32_t* tile_prefix; // [tiles+1] exclusive scan of tile_count
+    const uint32_t* tile_seg;    // [tiles] segment of each tile's first slot (join_tileseg_kernel)
+    uint32_t* total_out;         // number of viable slots of the depth
     uint32_t* vpos;              // [total_slots] compacted
     uint32_t* vnxt;
     uint32_t* vlast;
@@ -91,81 +98,222 @@ __device__ __forceinline__ uint32_t full_lower_bound(const uint32_t* __restrict_
     return lo;
 }
 
-__global__ void __launch_bounds__(JOIN_THREADS) join_probe_kernel(DepthDesc d)
+// lower_bound by a whole warp: 32 probes per step cut the range 33-fold (5 dependent loads for 2^24 elements
+// instead of 24).  All lanes must call it with the same arguments; every lane returns the answer.
+__device__ __forceinline__ uint32_t warp_lower_bound(const uint32_t* __restrict__ R, uint32_t len, uint64_t need, uint32_t lane)
 {
-    __shared__ uint32_t s_seg[2];
-    const uint32_t slot0 = blockIdx.x * JOIN_THREADS;
-    if (threadIdx.x < 2) {
-        uint32_t s = threadIdx.x == 0 ? slot0 : min(slot0 + JOIN_THREADS - 1, d.total_slots - 1);
-        s_seg[threadIdx.x] = find_segment(d.slot_off, 0, d.nseg - 1, s);
+    uint32_t lo = 0, hi = len;  // the answer lies in [lo, hi]
+    while (hi - lo > 32) {
+        const uint32_t step = (hi - lo + 32) / 33;
+        const uint32_t idx = lo + (lane + 1) * step - 1;
+        const bool ge = idx >= hi || (uint64_t)__ldg(R + idx) >= need;
+        const uint32_t b = __ballot_sync(0xffffffffu, ge);
+        const uint32_t f = b ? (uint32_t)__ffs(b) - 1u : 32u;  // first probe that is >= need
+        const uint32_t nlo = lo + f * step;
+        if (f < 32) hi = min(hi, lo + (f + 1) * step - 1);
+        lo = nlo;
     }
-    __syncthreads();
-    const uint32_t slot = slot0 + threadIdx.x;
-    const bool live = slot < d.total_slots;
-    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t idx = lo + lane;
+    const bool ge = idx >= hi || (uint64_t)__ldg(R + idx) >= need;
+    const uint32_t b = __ballot_sync(0xffffffffu, ge);
+    return b ? min(hi, lo + (uint32_t)__ffs(b) - 1u) : hi;
+}
 
-    uint32_t seg = 0, rlen = 0;
-    const uint32_t* R = nullptr;
-    uint64_t need = 0, limit = 0;
-    if (live) {
-        seg = find_segment(d.slot_off, s_seg[0], s_seg[1], slot);
-        const uint32_t x = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
-        need = sat_add64(x, d.lo[seg]);
-        limit = sat_add64(x, d.hi[seg]);
+constexpr int JF_THREADS = 1024;
+constexpr int JF_ITEMS = 4;                          // slots per thread
+constexpr int JF_TILE = JF_THREADS * JF_ITEMS;       // slots per tile: large tiles keep the look-back short
+constexpr int JF_WIN = 8192;                         // right-list window staged in shared memory (elements)
+constexpr int JF_WARPS = JF_THREADS / 32;
+
+// A tile = JF_TILE consecutive slots.  Inside a tile of one segment the part of the right list that can be
+// hit, R[lb(need of first slot) .. lb(need of last slot)], is staged in shared memory when it is at most
+// JF_WIN elements (left and right lists of similar density) and searched there; otherwise lane 0 of every
+// warp gallops from the tile's first answer and the other lanes gallop from lane 0's.
+// tile_seg[t] = segment that holds slot t * JF_TILE
+__global__ void join_tileseg_kernel(const uint32_t* slot_off, uint32_t nseg, uint32_t ntiles, uint32_t* tile_seg)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < ntiles) tile_seg[t] = find_segment(slot_off, 0, nseg - 1, t * (uint32_t)JF_TILE);
+}
+
+__global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
+{
+    __shared__ uint32_t s_win[JF_WIN];
+    __shared__ uint32_t s_j[2], s_count;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_count = 0;
+    const uint32_t tile = blockIdx.x;
+    const uint32_t slot0 = tile * JF_TILE;
+    const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot0);
+    const uint32_t seg_lo = __ldg(d.tile_seg + tile);  // segment of the tile's first slot (join_tileseg_kernel)
+    // upper bound for the segment searches of this tile's slots: the segment of the next tile's first slot
+    const uint32_t seg_hi = slot0 + nslots == d.total_slots ? d.nseg - 1 : __ldg(d.tile_seg + tile + 1);
+    const bool single = __ldg(d.slot_off + seg_lo + 1) >= slot0 + nslots;  // segment seg_lo covers the whole tile
+
+    // ---- single-segment tile: bracket the reachable part of the right list
+    const uint32_t* R1 = nullptr;
+    uint32_t rlen1 = 0, vbase1 = 0;
+    if (single) {
         if (d.right_list) {
-            R = d.right_list[seg];
-            rlen = d.right_len[seg];
+            R1 = d.right_list[seg_lo];
+            rlen1 = d.right_len[seg_lo];
         } else {
-            uint32_t b = __ldg(d.prev_vseg + seg);
-            R = d.prev_vpos + b;
-            rlen = __ldg(d.prev_vseg + seg + 1) - b;
+            vbase1 = __ldg(d.prev_vseg + seg_lo);
+            R1 = d.prev_vpos + vbase1;
+            rlen1 = __ldg(d.prev_vseg + seg_lo + 1) - vbase1;
+        }
+        if (warp < 2) {  // two warps bracket the window in parallel
+            const uint32_t s = warp == 0 ? slot0 : slot0 + nslots - 1;
+            const uint32_t x = __ldg(d.left[seg_lo] + (s - __ldg(d.slot_off + seg_lo)));
+            const uint32_t j = warp_lower_bound(R1, rlen1, sat_add64(x, d.lo[seg_lo]), lane);
+            if (lane == 0) s_j[warp] = j;
         }
     }
-    // warp-cooperative narrowing: when the whole warp works on one segment, lane 0 searches the full
-    // list and everybody else gallops from its answer.
-    const uint32_t act = __ballot_sync(0xffffffffu, live);
-    const uint32_t seg0 = __shfl_sync(0xffffffffu, seg, 0);
-    const bool uniform = __all_sync(0xffffffffu, !live || seg == seg0) && (act & 1u);
-    uint32_t j = 0;
-    if (uniform) {
-        uint32_t j0 = 0;
-        if (lane == 0) j0 = full_lower_bound(R, rlen, need);
-        j0 = __shfl_sync(0xffffffffu, j0, 0);
-        if (live) j = lane == 0 ? j0 : gallop_lower_bound(R, j0, rlen, need);
-    } else if (live) {
-        j = full_lower_bound(R, rlen, need);
+    __syncthreads();
+    const uint32_t j_first = single ? s_j[0] : 0;
+    const uint32_t wlen = single ? min(rlen1, s_j[1] + 1) - j_first : 0;
+    const bool use_win = single && wlen <= (uint32_t)JF_WIN;
+    if (use_win) {
+        for (uint32_t i = tid; i < wlen; i += JF_THREADS) s_win[i] = __ldg(R1 + j_first + i);
+        __syncthreads();
     }
-    if (live) {
-        bool ok = j < rlen && (uint64_t)__ldg(R + j) <= limit;
-        d.raw[slot] = ok ? j : NONE32;
+
+    // ---- probe: JF_ITEMS rounds of JOIN_THREADS consecutive slots
+    uint32_t viable = 0;
+#pragma unroll
+    for (int it = 0; it < JF_ITEMS; it++) {
+        const uint32_t slot = slot0 + it * JF_THREADS + tid;
+        const bool live = slot < slot0 + nslots;
+        uint32_t seg = seg_lo, x = 0, j = 0, last = 0;
+        bool ok = false;
+        if (use_win) {
+            if (live) {
+                x = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
+                const uint64_t need = sat_add64(x, d.lo[seg]), limit = sat_add64(x, d.hi[seg]);
+                uint32_t lo = 0, hi = wlen;
+                while (lo < hi) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if ((uint64_t)s_win[mid] < need) lo = mid + 1; else hi = mid;
+                }
+                j = j_first + lo;
+                if (lo < wlen) {
+                    last = s_win[lo];
+                    ok = (uint64_t)last <= limit;
+                }
+            }
+        } else {
+            const uint32_t* R = R1;
+            uint32_t rlen = rlen1;
+            uint64_t need = 0, limit = 0;
+            if (live) {
+                if (!single) {
+                    seg = find_segment(d.slot_off, seg_lo, seg_hi, slot);
+                    if (d.right_list) {
+                        R = d.right_list[seg];
+                        rlen = d.right_len[seg];
+                    } else {
+                        const uint32_t b = __ldg(d.prev_vseg + seg);
+                        R = d.prev_vpos + b;
+                        rlen = __ldg(d.prev_vseg + seg + 1) - b;
+                    }
+                }
+                x = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
+                need = sat_add64(x, d.lo[seg]);
+                limit = sat_add64(x, d.hi[seg]);
+            }
+            if (single) {  // warp-uniform branch: lane 0 gallops from the tile's first answer, the rest from lane 0's
+                uint32_t j0 = 0;
+                if (lane == 0 && live) j0 = gallop_lower_bound(R, j_first, rlen, need);
+                j0 = __shfl_sync(0xffffffffu, j0, 0);
+                if (live) j = lane == 0 ? j0 : gallop_lower_bound(R, j0, rlen, need);
+            } else if (live) {
+                j = full_lower_bound(R, rlen, need);
+            }
+            if (live && j < rlen) {
+                last = __ldg(R + j);
+                ok = (uint64_t)last <= limit;
+            }
+        }
+        if (live) d.raw[slot] = ok ? j : NONE32;
+        viable += __popc(__ballot_sync(0xffffffffu, ok));
     }
+    if (lane == 0 && viable) atomicAdd(&s_count, viable);
+    __syncthreads();
+    if (tid == 0) d.tile_count[tile] = s_count;
 }
 
-__global__ void __launch_bounds__(JOIN_THREADS) join_compact_kernel(DepthDesc d)
+// Compaction of the viable slots of a tile; tile_prefix = exclusive scan of tile_count (prefix.cuh).
+__global__ void __launch_bounds__(JF_THREADS) join_compact_kernel(DepthDesc d)
 {
-    __shared__ uint32_t s_seg[2];
-    const uint32_t slot0 = blockIdx.x * JOIN_THREADS;
-    if (threadIdx.x < 2) {
-        uint32_t s = threadIdx.x == 0 ? slot0 : min(slot0 + JOIN_THREADS - 1, d.total_slots - 1);
-        s_seg[threadIdx.x] = find_segment(d.slot_off, 0, d.nseg - 1, s);
+    __shared__ uint32_t s_cnt[JF_ITEMS * JF_WARPS];  // flags per (round, warp), then their exclusive prefix
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tile = blockIdx.x;
+    const uint32_t slot0 = tile * JF_TILE;
+    const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot0);
+    const uint32_t seg_lo = __ldg(d.tile_seg + tile);
+    const uint32_t seg_hi = slot0 + nslots == d.total_slots ? d.nseg - 1 : __ldg(d.tile_seg + tile + 1);
+    const bool single = __ldg(d.slot_off + seg_lo + 1) >= slot0 + nslots;
+    uint32_t jv[JF_ITEMS], fl[JF_ITEMS];
+#pragma unroll
+    for (int it = 0; it < JF_ITEMS; it++) {
+        const uint32_t slot = slot0 + it * JF_THREADS + tid;
+        jv[it] = slot < slot0 + nslots ? d.raw[slot] : NONE32;
+        fl[it] = __ballot_sync(0xffffffffu, jv[it] != NONE32);
+        if (lane == 0) s_cnt[it * JF_WARPS + warp] = __popc(fl[it]);
     }
     __syncthreads();
-    const uint32_t slot = slot0 + threadIdx.x;
-    if (slot >= d.total_slots) return;
-    const uint32_t j = d.raw[slot];
-    if (j == NONE32) return;
-    const uint32_t seg = find_segment(d.slot_off, s_seg[0], s_seg[1], slot);
-    const uint32_t o = d.rank[slot];
-    d.vpos[o] = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
-    d.vnxt[o] = j;
-    d.vlast[o] = d.right_list ? __ldg(d.right_list[seg] + j) : __ldg(d.prev_vlast + __ldg(d.prev_vseg + seg) + j);
-}
-
-// vseg[s] = rank[slot_off[s]] for s = 0 .. nseg
-__global__ void join_vseg_kernel(DepthDesc d)
-{
-    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s <= d.nseg) d.vseg[s] = d.rank[d.slot_off[s]];
+    if (warp == 0) {
+        constexpr int PER = JF_ITEMS * JF_WARPS / 32;  // counts per lane, consecutive
+        uint32_t c[PER], v = 0;
+#pragma unroll
+        for (int i = 0; i < PER; i++) {
+            c[i] = s_cnt[lane * PER + i];
+            v += c[i];
+        }
+        uint32_t inc = v;
+#pragma unroll
+        for (int dd = 1; dd < 32; dd <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, inc, dd);
+            if (lane >= (uint32_t)dd) inc += o;
+        }
+        uint32_t run = inc - v;
+#pragma unroll
+        for (int i = 0; i < PER; i++) {
+            s_cnt[lane * PER + i] = run;
+            run += c[i];
+        }
+    }
+    __syncthreads();
+    const uint32_t prefix = __ldg(d.tile_prefix + tile);
+#pragma unroll
+    for (int it = 0; it < JF_ITEMS; it++) {
+        const uint32_t slot = slot0 + it * JF_THREADS + tid;
+        if (slot >= slot0 + nslots) break;
+        const uint32_t o = prefix + s_cnt[it * JF_WARPS + warp] + __popc(fl[it] & ((1u << lane) - 1u));
+        uint32_t sg = single ? seg_lo : find_segment(d.slot_off, seg_lo, seg_hi, slot);
+        const uint32_t so = __ldg(d.slot_off + sg);
+        if (jv[it] != NONE32) {
+            const uint32_t j = jv[it];
+            d.vpos[o] = __ldg(d.left[sg] + (slot - so));
+            d.vnxt[o] = j;
+            d.vlast[o] = d.right_list ? __ldg(d.right_list[sg] + j) : __ldg(d.prev_vlast + __ldg(d.prev_vseg + sg) + j);
+        }
+        if (slot == so) {  // segment start; also covers empty segments that start at the same slot
+            for (;;) {
+                d.vseg[sg] = o;
+                if (sg == 0 || __ldg(d.slot_off + sg - 1) != slot) break;
+                sg--;
+            }
+        }
+    }
+    if (slot0 + nslots == d.total_slots && tid == 0) {  // last tile: trailing empty segments and the grand total
+        const uint32_t all = __ldg(d.tile_prefix + tile + 1);
+        for (uint32_t sg = d.nseg;; sg--) {
+            d.vseg[sg] = all;
+            if (sg == 0 || __ldg(d.slot_off + sg - 1) != d.total_slots) break;
+        }
+        *d.total_out = all;
+    }
 }
 
 }  // namespace vlgb

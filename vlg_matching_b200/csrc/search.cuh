@@ -385,7 +385,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
 
     // ---- device memory
     size_t need = ctl.size() + 4096;
-    need += Arena::padded(max_slots, 4) + Arena::padded(max_slots + 1, 4);  // raw, rank
+    const size_t max_jtiles = (max_slots + JF_TILE - 1) / JF_TILE;
+    need += Arena::padded(max_slots, 4) + 3 * Arena::padded(max_jtiles + 4, 4);  // raw, tile counts / prefix / segments
     for (uint32_t d = 1; d < kmax; d++)
         need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
     need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
@@ -399,7 +400,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     Arena& A = c.join_arena;
     uint8_t* d_ctl = A.take<uint8_t>(ctl.size());
     uint32_t* raw = A.take<uint32_t>(max_slots);
-    uint32_t* rank = A.take<uint32_t>(max_slots + 1);
+    uint32_t* jtile_count = A.take<uint32_t>(max_jtiles + 4);
+    uint32_t* jtile_prefix = A.take<uint32_t>(max_jtiles + 4);
+    uint32_t* jtile_seg = A.take<uint32_t>(max_jtiles + 4);
     for (uint32_t d = 1; d < kmax; d++) {
         size_t t = dh[d].slot_off[dh[d].nseg];
         dh[d].vpos = A.take<uint32_t>(t);
@@ -447,7 +450,10 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         D.lo = dev_at<const uint64_t>(d_ctl, h.o_lo);
         D.hi = dev_at<const uint64_t>(d_ctl, h.o_hi);
         D.raw = raw;
-        D.rank = rank;
+        D.tile_count = jtile_count;
+        D.tile_prefix = jtile_prefix;
+        D.tile_seg = jtile_seg;
+        D.total_out = d_viable + d;
         D.vpos = h.vpos;
         D.vnxt = h.vnxt;
         D.vlast = h.vlast;
@@ -458,16 +464,18 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             VLGB_CUDA(cudaMemsetAsync(d_viable + d, 0, 4, c.stream));
             continue;
         }
-        const uint32_t grid = (T + JOIN_THREADS - 1) / JOIN_THREADS;
+        const uint32_t jtiles = (T + JF_TILE - 1) / JF_TILE;
+        uint64_t right_words = 0;
+        if (d == 1)
+            for (uint32_t s = 0; s < h.nseg; s++) right_words += h.right_len[s];
         c.begin(ST_JOIN_PROBE);
-        join_probe_kernel<<<grid, JOIN_THREADS, 0, c.stream>>>(D);
-        c.end(ST_JOIN_PROBE, 1, (uint64_t)T * 12);
+        join_tileseg_kernel<<<(jtiles + 255) / 256, 256, 0, c.stream>>>(D.slot_off, D.nseg, jtiles, jtile_seg);
+        join_probe_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
+        c.end(ST_JOIN_PROBE, 2, (uint64_t)T * 8 + right_words * 4);
         c.begin(ST_JOIN_COMPACT);
-        uint32_t l = exclusive_scan(FlagNotNone{raw}, T, rank, scratch, c.stream);
-        join_compact_kernel<<<grid, JOIN_THREADS, 0, c.stream>>>(D);
-        join_vseg_kernel<<<(h.nseg + 1 + 127) / 128, 128, 0, c.stream>>>(D);
-        c.end(ST_JOIN_COMPACT, l + 2, (uint64_t)T * (8 + 4 + 8));
-        VLGB_CUDA(cudaMemcpyAsync(d_viable + d, rank + T, 4, cudaMemcpyDeviceToDevice, c.stream));
+        const uint32_t l = exclusive_scan(ValueU32{jtile_count}, jtiles, jtile_prefix, scratch, c.stream);
+        join_compact_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
+        c.end(ST_JOIN_COMPACT, l + 1, (uint64_t)T * 4);
     }
 
     // ---- selection
@@ -546,7 +554,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         VLGB_CUDA(cudaGetLastError());
         VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: match counts
         c.stats.d2h_bytes += (uint64_t)nq * 8 + (kmax + 1) * 4;
-        for (uint32_t d = 1; d < kmax; d++) c.stats.bytes[ST_JOIN_COMPACT] += (uint64_t)viable[d] * 12;
+        for (uint32_t d = 1; d < kmax; d++)  // viable slots written; deeper levels read the previous viable list
+            c.stats.bytes[ST_JOIN_COMPACT] += (uint64_t)viable[d] * 20;
+        for (uint32_t d = 2; d < kmax; d++) c.stats.bytes[ST_JOIN_PROBE] += (uint64_t)viable[d - 1] * 4;
 
         for (uint32_t s = 0; s < nq; s++) {
             co.tuple_off[s] = co.tuple_words;
