@@ -178,8 +178,10 @@ const char* vlgb_stage_name(uint32_t stage);
 /* The CUDA stream (cudaStream_t) every kernel of the calling thread is launched on, for callers that
  * bracket calls with their own CUDA events.  NULL before the first device call. */
 void* vlgb_stream_handle(void);
-/* Tunables (0 = keep default): bytes per device segment, device memory budget for join state. */
-int vlgb_set_tuning(uint64_t segment_bytes, uint64_t join_budget_bytes);
+/* Tunables (0 = keep default): device memory the scan may use for its hit streams (pass 1 records the
+ * occurrences so that pass 2 need not read the text again; 1 = never, pass 2 always re-scans), and the device
+ * memory budget for join state. */
+int vlgb_set_tuning(uint64_t stream_budget_bytes, uint64_t join_budget_bytes);
 
 #ifdef __cplusplus
 }

@@ -263,3 +263,20 @@ def test_int_alphabet_wide_symbols_vs_oracle(V, scale, width):
     if width > 1:
         bad = capi.PackedBatch([([b"\x01"], [])])
         assert idx.search(bad, capi.WANT_COUNT).status(0) == capi.ERR_ARG
+
+
+def test_scan_hit_stream_paths(V):
+    """Pass 2 of the scan has three routes: scatter the hit stream recorded by pass 1 (default), re-scan rows
+    whose occurrences overflow the stream (> 2 per text position), re-scan everything (no stream budget)."""
+    from vlg_matching_b200 import capi, synth
+    text = synth.make_text(2, 1 << 19)
+    queries = synth.make_queries(2, text, 150)
+    dense = np.frombuffer(b"a" * 300000 + b"ab" * 50000, dtype=np.uint8)
+    dq = [([b"a"], []), ([b"aa", b"aaa"], [(0, 3)]), ([b"aaaa", b"a", b"ab"], [(1, 2), (0, 9)]), ([b"aaaaa", b"ba"], [(0, 100)])]
+    try:
+        for budget in (0, 1):
+            capi.check(capi.lib.vlgb_set_tuning(budget, 0))
+            compare_with_oracle(V, text, queries)
+            compare_with_oracle(V, dense, dq)     # 5 occurrences per position: every row overflows the stream
+    finally:
+        capi.check(capi.lib.vlgb_set_tuning(1 << 62, 0))  # back to "as much as the default rule allows"

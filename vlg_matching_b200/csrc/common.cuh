@@ -165,7 +165,7 @@ struct Context {
     std::vector<Span> spans;
     int ev_used = 0;
     vlgb_stats stats;
-    uint64_t segment_bytes = 0;  // 0 = default
+    uint64_t stream_budget = 0;  // 0 = default (a third of the free memory, <= 24 GiB); tiny = no hit stream
     uint64_t join_budget = 0;    // 0 = default
 
     void begin(uint32_t stage)

@@ -131,10 +131,10 @@ extern "C" int vlgb_last_stats(vlgb_stats* out)
 
 extern "C" void* vlgb_stream_handle(void) { return ctx().ready ? (void*)ctx().stream : nullptr; }
 
-extern "C" int vlgb_set_tuning(uint64_t segment_bytes, uint64_t join_budget_bytes)
+extern "C" int vlgb_set_tuning(uint64_t stream_budget_bytes, uint64_t join_budget_bytes)
 {
     Context& c = ctx();
-    if (segment_bytes) c.segment_bytes = segment_bytes;
+    if (stream_budget_bytes) c.stream_budget = stream_budget_bytes;
     if (join_budget_bytes) c.join_budget = join_budget_bytes;
     return VLGB_OK;
 }

@@ -91,6 +91,14 @@ struct ScanArgs {
     uint32_t* matrix;        // [rows][s_stride]: counts (pass 1 out) / write cursors inside each list (pass 2 in)
     const uint64_t* list_base;  // pass 2: [s_act] first word of every list inside `out`
     uint32_t* out;           // pass 2: positions (u32, shard-local)
+    // hit stream: pass 1 records every occurrence of a row as (position - row start) | pid << 16, in the order
+    // it was found (ascending per pattern), so that pass 2 only has to scatter it (scan_scatter_kernel).  A row
+    // with more than stream_cap occurrences is re-scanned by the FILL kernel instead.
+    uint32_t* stream;        // [rows][stream_cap] or nullptr
+    uint32_t stream_cap;
+    uint32_t* row_hits;      // [rows] occurrences found in the row (pass 1 out)
+    uint32_t* overflow;      // number of rows with row_hits > stream_cap (pass 1 out)
+    uint32_t only_overflow;  // FILL kernel: skip the rows the scatter kernel handles
 };
 
 constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S / 2) * sizeof(uint32_t) +
@@ -106,7 +114,7 @@ constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S /
 template <bool FILL>
 __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* cur, const uint32_t* q,
                                                  uint32_t qhead, uint32_t n, uint32_t row_lo, const uint32_t* mrow,
-                                                 uint32_t lane, uint32_t lt_mask)
+                                                 uint32_t lane, uint32_t lt_mask, uint32_t* stream_row, uint32_t& nh)
 {
     uint32_t p = 0, cmask = 0, wlo = 0, whi = 0;
     if (lane < n) {
@@ -158,7 +166,13 @@ __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTa
                 break;
             }
             // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
-            if (__any_sync(0xffffffffu, pid != NONE32)) {
+            const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
+            if (hits) {
+                if (!FILL && stream_row) {
+                    const uint32_t at = nh + __popc(hits & lt_mask);
+                    if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
+                    nh += __popc(hits);
+                }
                 const uint32_t grp = __match_any_sync(0xffffffffu, pid);
                 const int leader = __ffs(grp) - 1;
                 uint32_t old = 0;
@@ -203,6 +217,9 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     const uint32_t hi = min(lo + a.chunk, a.valid_len);
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint32_t qhead = 0, qcount = 0;  // warp-uniform
+    uint32_t nh = 0;                 // occurrences recorded in the row's hit stream (pass 1)
+    uint32_t* stream_row = (!FILL && a.stream) ? a.stream + (size_t)row * a.stream_cap : nullptr;
+    if (FILL && a.only_overflow && a.row_hits[row] <= a.stream_cap) return;  // scattered from the stream instead
 
     for (uint32_t base = lo; base < hi; base += SCAN_STEP) {
         // ---- 16 bytes per lane: own 8 + the next lane's 8
@@ -275,16 +292,62 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         __syncwarp();
         // ---- drain full rounds; fewer than 32 leftovers wait for the next step
         while (qcount >= 32) {
-            scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask);
+            scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
             qhead = (qhead + 32) & (SCAN_QCAP - 1);
             qcount -= 32;
         }
         __syncwarp();
     }
-    if (qcount) scan_drain_round<FILL>(a, T, cur, q, qhead, qcount, lo, mrow, lane, lt_mask);
+    if (qcount) scan_drain_round<FILL>(a, T, cur, q, qhead, qcount, lo, mrow, lane, lt_mask, stream_row, nh);
     if (!FILL) {
         __syncwarp();
         for (uint32_t i = lane; i < a.s_act; i += 32) mrow[i] = (cur[i >> 1] >> ((i & 1u) * 16)) & 0xFFFFu;
+        if (stream_row && lane == 0) {
+            a.row_hits[row] = nh;
+            if (nh > a.stream_cap) atomicAdd(a.overflow, 1u);
+        }
+    }
+}
+
+// Pass 2 for the rows whose occurrences fit the hit stream: no text, no tables -- read the row's stream
+// (coalesced), rank equal patterns of a round in lane order (= the order pass 1 found them = ascending
+// position) and write every position to its place:  list_base[pid] + row cursor[pid] + seen so far + rank.
+constexpr int SCAT_WARPS = 16;
+constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * (SCAN_S / 2) * sizeof(uint32_t);
+
+__global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
+{
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t* cur = reinterpret_cast<uint32_t*>(smem_raw) + warp * (SCAN_S / 2);  // u16 counters, two per word
+    const uint32_t row = blockIdx.x * SCAT_WARPS + warp;
+    if (row >= a.rows) return;
+    const uint32_t nh = a.row_hits[row];
+    if (nh == 0 || nh > a.stream_cap) return;
+    for (uint32_t i = lane; i < SCAN_S / 2; i += 32) cur[i] = 0u;
+    __syncwarp();
+    const uint32_t* st = a.stream + (size_t)row * a.stream_cap;
+    const uint32_t* mrow = a.matrix + (size_t)row * a.s_stride;
+    const uint32_t lo = row * a.chunk;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    for (uint32_t i = 0; i < nh; i += 32) {
+        uint32_t pid = NONE32, p = 0;
+        uint64_t dst = 0;
+        if (i + lane < nh) {
+            const uint32_t e = __ldg(st + i + lane);
+            pid = e >> 16;
+            p = lo + (e & 0xFFFFu);
+            dst = __ldg(a.list_base + pid) + __ldg(mrow + pid);
+        }
+        const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+        const int leader = __ffs(grp) - 1;
+        uint32_t old = 0;
+        if (pid != NONE32 && (int)lane == leader) {
+            const uint32_t sh = (pid & 1u) * 16;
+            old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        if (pid != NONE32) a.out[dst + old + __popc(grp & lt_mask)] = p;
     }
 }
 

@@ -93,6 +93,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
         attr_set = true;
     }
 
@@ -100,6 +101,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         uint32_t s_act, stride, has_short;
         size_t o_tables, o_len, o_off, o_blob, o_base;  // inside the control blob
         uint32_t *matrix, *part, *total;
+        uint32_t *stream = nullptr, *row_hits = nullptr, *overflow = nullptr;  // hit stream of pass 1 (if it fits)
     };
     std::vector<PassDev> pd(npass);
     Packer ctl;
@@ -123,6 +125,23 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     }
     const size_t o_allbase = ctl.put(so.base);  // P+1 u64, filled later (owned kernel)
     work_bytes += 2 * Arena::padded(P, 4);      // owned[], totals[]
+    // hit streams: stream_cap entries per row (2 per text position, else 1), for as many passes as the budget
+    // (a third of the free device memory, at most 24 GiB) allows; the other passes re-scan in pass 2
+    uint32_t stream_cap = 0, stream_passes = 0;
+    {
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        uint64_t budget = std::min<uint64_t>((uint64_t)24 << 30, (free_b + c.scan_arena.buf.cap) / 3);
+        if (c.stream_budget) budget = std::min(budget, c.stream_budget);
+        for (uint32_t per_pos = 2; per_pos >= 1 && !stream_passes; per_pos--) {
+            const uint64_t per_pass = (uint64_t)rows * chunk * per_pos * 4;
+            if (per_pass <= budget) {
+                stream_cap = chunk * per_pos;
+                stream_passes = (uint32_t)std::min<uint64_t>(npass, budget / per_pass);
+            }
+        }
+        work_bytes += stream_passes * (Arena::padded((size_t)rows * stream_cap, 4) + Arena::padded(rows, 4)) + Arena::padded(npass, 4);
+    }
     c.scan_arena.reserve(ctl.size() + work_bytes + 4096);
     uint8_t* d_ctl = c.scan_arena.take<uint8_t>(ctl.size());
     VLGB_CUDA(cudaMemcpyAsync(d_ctl, ctl.host.data(), ctl.host.size(), cudaMemcpyHostToDevice, c.stream));
@@ -133,6 +152,14 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         pd[p].total = c.scan_arena.take<uint32_t>(pd[p].stride);
     }
     uint32_t* d_owned = c.scan_arena.take<uint32_t>(P);
+    uint32_t* d_overflow = c.scan_arena.take<uint32_t>(npass);
+    VLGB_CUDA(cudaMemsetAsync(d_overflow, 0, (size_t)npass * 4, c.stream));
+    for (uint32_t p = 0; p < stream_passes; p++) {
+        pd[p].stream = c.scan_arena.take<uint32_t>((size_t)rows * stream_cap);
+        pd[p].row_hits = c.scan_arena.take<uint32_t>(rows);
+        pd[p].overflow = d_overflow + p;
+    }
+    std::vector<uint32_t> overflow(npass, 0);
 
     auto args_for = [&](uint32_t p) {
         ScanArgs a;
@@ -154,6 +181,11 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.matrix = pd[p].matrix;
         a.list_base = dev_at<const uint64_t>(d_ctl, pd[p].o_base);
         a.out = nullptr;
+        a.stream = pd[p].stream;
+        a.stream_cap = stream_cap;
+        a.row_hits = pd[p].row_hits;
+        a.overflow = pd[p].overflow;
+        a.only_overflow = 0;
         return a;
     };
     const uint32_t grid = (rows + SCAN_WARPS - 1) / SCAN_WARPS;
@@ -164,7 +196,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         c.begin(ST_SCAN_COUNT);
         if (a.has_short) scan_kernel<false, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
         else scan_kernel<false, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-        c.end(ST_SCAN_COUNT, 1, n + (uint64_t)rows * pd[p].s_act * 4);
+        c.end(ST_SCAN_COUNT, 1, n + (uint64_t)rows * pd[p].s_act * 4);  // + 4 B per occurrence streamed, added below
         c.begin(ST_SCAN_OFFSETS);
         dim3 g((pd[p].stride + 127) / 128, nrb);
         scan_colsum_kernel<<<g, 128, 0, c.stream>>>(pd[p].matrix, rows, pd[p].stride, pd[p].part);
@@ -175,6 +207,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
                                   c.stream));
         c.stats.d2h_bytes += pd[p].s_act * 4;
     }
+    VLGB_CUDA(cudaMemcpyAsync(overflow.data(), d_overflow, (size_t)npass * 4, cudaMemcpyDeviceToHost, c.stream));
     VLGB_CUDA(cudaGetLastError());
     VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync 1: list sizes
 
@@ -203,9 +236,23 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         ScanArgs a = args_for(p);
         a.out = so.d_lists;
         c.begin(ST_SCAN_FILL);
-        if (pocc && a.has_short) scan_kernel<true, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-        else if (pocc) scan_kernel<true, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-        c.end(ST_SCAN_FILL, pocc ? 1 : 0, pocc ? n + (uint64_t)rows * pd[p].s_act * 4 + pocc * 4 : 0);
+        uint32_t launches = 0;
+        uint64_t bytes = 0;
+        const bool streamed = pd[p].stream != nullptr;
+        if (pocc && streamed) {  // scatter the recorded occurrences; only overflowed rows are scanned again
+            scan_scatter_kernel<<<(rows + SCAT_WARPS - 1) / SCAT_WARPS, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
+            launches++;
+            bytes += pocc * 8 + (uint64_t)rows * pd[p].s_act * 4;
+            c.stats.bytes[ST_SCAN_COUNT] += pocc * 4;
+        }
+        if (pocc && (!streamed || overflow[p])) {
+            a.only_overflow = streamed ? 1u : 0u;
+            if (a.has_short) scan_kernel<true, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+            else scan_kernel<true, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+            launches++;
+            if (!streamed) bytes += n + (uint64_t)rows * pd[p].s_act * 4 + pocc * 4;
+        }
+        c.end(ST_SCAN_FILL, launches, bytes);
     }
     c.stats.scan_passes += npass;
     c.stats.distinct_patterns += P;
