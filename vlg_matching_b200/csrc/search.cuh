@@ -437,8 +437,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     for (uint32_t d = 1; d < kmax; d++)
         need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
     need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
-    need += 2 * Arena::padded(sel_total, 4) + Arena::padded(sel_total, 1);             // succ, exitp, flags
-    need += 2 * Arena::padded(ntiles + 1, 4) + Arena::padded((size_t)sel_total + 1, 4);  // entry, spec, mrank
+    need += 2 * Arena::padded(sel_total, 4) + Arena::padded((size_t)ntiles * 32, 4);   // succ, exitp, flag bits
+    need += 4 * Arena::padded(ntiles + 2, 4);                                          // entry, spec, tile count / prefix
     need += 2 * Arena::padded(nchunks + 1, 4);                                         // spec_exit, coalesce
     need += Arena::padded(nq, 8) + Arena::padded(kmax + 1, 4);                         // counts, viable totals
     const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(max_slots, sel_total));
@@ -468,12 +468,13 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     uint32_t* d_t0 = A.take<uint32_t>(nq);
     uint32_t* d_succ = A.take<uint32_t>(sel_total);
     uint32_t* d_exitp = A.take<uint32_t>(sel_total);
-    uint8_t* d_flags = A.take<uint8_t>(sel_total);
+    uint32_t* d_flagbits = A.take<uint32_t>((size_t)ntiles * 32);
+    uint32_t* d_tile_count = A.take<uint32_t>(ntiles + 2);
+    uint32_t* d_tile_prefix = A.take<uint32_t>(ntiles + 2);
     uint32_t* d_entry = A.take<uint32_t>(ntiles + 1);
     uint32_t* d_spec = A.take<uint32_t>(ntiles + 1);
     uint32_t* d_spec_exit = A.take<uint32_t>(nchunks + 1);
     uint32_t* d_coalesce = A.take<uint32_t>(nchunks + 1);
-    uint32_t* d_mrank = A.take<uint32_t>((size_t)sel_total + 1);
     uint64_t* d_counts = A.take<uint64_t>(nq);
     uint32_t* d_viable = A.take<uint32_t>(kmax + 1);
     uint32_t* scratch = A.take<uint32_t>(scratch_words);
@@ -548,7 +549,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.t0 = d_t0;
     S.succ = d_succ;
     S.exitp = d_exitp;
-    S.flags = d_flags;
+    S.flagbits = d_flagbits;
+    S.tile_count = d_tile_count;
+    S.tile_prefix = d_tile_prefix;
     S.entry = d_entry;
     S.nchunks = nchunks;
     S.chunk_q = dev_at<const uint32_t>(d_ctl, o_chunk_q);
@@ -557,7 +560,6 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.spec = d_spec;
     S.spec_exit = d_spec_exit;
     S.coalesce = d_coalesce;
-    S.mrank = d_mrank;
     S.tuple_off = dev_at<const uint64_t>(d_ctl, o_tuple_off);
     S.starts = nullptr;
     S.tuples = nullptr;
@@ -576,25 +578,23 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     if (sel_total) {
         c.begin(ST_SELECT_SUCC);
         sel_resolve_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
-        sel_succ_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
-        c.end(ST_SELECT_SUCC, 2, (uint64_t)sel_total * 12);
+        c.end(ST_SELECT_SUCC, 1, (uint64_t)nq * 32);
         c.begin(ST_SELECT_TILE);
         sel_tile_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
-        c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 8);
+        c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 16);
         c.begin(ST_SELECT_WALK);
         VLGB_CUDA(cudaMemsetAsync(d_entry, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
         VLGB_CUDA(cudaMemsetAsync(d_spec, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
         VLGB_CUDA(cudaMemsetAsync(d_coalesce, 0xFF, (size_t)(nchunks + 1) * 4, c.stream));
-        VLGB_CUDA(cudaMemsetAsync(d_flags, 0, sel_total, c.stream));
         sel_spec_kernel<<<(nchunks + 31) / 32, 32, 0, c.stream>>>(S);
         sel_walk_kernel<<<(nq + 31) / 32, 32, 0, c.stream>>>(S);
         sel_entry_kernel<<<(ntiles + 255) / 256, 256, 0, c.stream>>>(S);
         sel_mark_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
         c.end(ST_SELECT_WALK, 4, (uint64_t)sel_total * 5);
         c.begin(ST_EMIT);
-        uint32_t l = exclusive_scan(FlagByte{d_flags}, sel_total, d_mrank, scratch, c.stream);
+        uint32_t l = exclusive_scan(ValueU32{d_tile_count}, ntiles, d_tile_prefix, scratch, c.stream);
         sel_counts_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
-        c.end(ST_EMIT, l + 1, (uint64_t)sel_total * 6);
+        c.end(ST_EMIT, l + 1, (uint64_t)ntiles * 12);
         VLGB_CUDA(cudaMemcpyAsync(co.counts.data(), d_counts, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
         if (kmax > 1)
             VLGB_CUDA(cudaMemcpyAsync(viable.data(), d_viable, (size_t)(kmax + 1) * 4, cudaMemcpyDeviceToHost, c.stream));

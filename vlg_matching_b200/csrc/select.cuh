@@ -11,8 +11,7 @@
 // Slots: every query owns a TILE-aligned segment of upper-bound size (|L_0| owned part), so a tile
 // never straddles two queries.  Kernels:
 //   resolve : per query, where V_0 / last live (scan list for k = 1, else the deepest join level)
-//   succ    : succ[slot]                                                    (gallop from t+1)
-//   tile    : exitp[slot] = first orbit element of slot that lies outside its tile (pointer doubling
+//   tile    : succ[slot] (gallop from t+1), then exitp[slot] = first orbit element of slot that lies outside its tile (pointer doubling
 //             in shared memory, log2(TILE) rounds)
 //   spec    : one thread per CHUNK of 64 tiles hops tile to tile from the chunk's first element (a guess)
 //   walk    : one thread per query hops from the true start; orbits of a monotone successor coalesce, so
@@ -20,8 +19,8 @@
 //             chunk's recorded exit: ~chunks x (a few hops) dependent loads instead of one per tile
 //   entry   : entry[tile] = first selected element in the tile (true hops before the coalescing point,
 //             speculative ones after it)
-//   mark    : per entered tile, flags[slot] = 1 for the orbit of entry[tile] (doubling again)
-//   prefix  : mrank = exclusive scan of flags                               (prefix.cuh)
+//   mark    : per entered tile, one bit per slot for the orbit of entry[tile] (doubling again) + the tile's count
+//   prefix  : exclusive scan of the tile counts                             (prefix.cuh)
 //   emit    : starts / tuples / exit cursor
 #pragma once
 #include "join.cuh"
@@ -58,7 +57,9 @@ struct SelDesc {
     // per slot
     uint32_t* succ;
     uint32_t* exitp;
-    uint8_t* flags;
+    uint32_t* flagbits;          // [tiles * 32] selected-element bits of every warp of an entered tile
+    uint32_t* tile_count;        // [tiles] selected elements per tile (0 for tiles never entered)
+    const uint32_t* tile_prefix; // [tiles + 1] exclusive scan of tile_count
     uint32_t* entry;             // [total_slots / SEL_TILE]
     // speculative chunks (SEL_CHUNK_TILES tiles of one query each)
     uint32_t nchunks;
@@ -68,7 +69,6 @@ struct SelDesc {
     uint32_t* spec;              // [tiles] element the speculative hop entered the tile with (NONE32: not visited)
     uint32_t* spec_exit;         // [nchunks] where the speculative hop left the chunk
     uint32_t* coalesce;          // [nchunks] first tile from which the speculative entries are the true ones
-    uint32_t* mrank;             // [total_slots + 1]
     // emission
     const uint64_t* tuple_off;   // [nq] first tuple word of each query (host prefix over count*k)
     uint64_t* starts;            // [matches of the chunk]
@@ -107,26 +107,6 @@ __device__ __forceinline__ uint32_t sel_query_of_tile(const SelDesc& s, uint32_t
     return find_segment(s.sel_off, 0, s.nq - 1, slot0);
 }
 
-__global__ void __launch_bounds__(SEL_TILE) sel_succ_kernel(SelDesc s)
-{
-    __shared__ uint32_t s_q;
-    const uint32_t slot0 = blockIdx.x * SEL_TILE;
-    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
-    __syncthreads();
-    const uint32_t q = s_q;
-    const uint32_t t = slot0 - s.sel_off[q] + threadIdx.x;
-    const uint32_t len = s.v0_len[q];
-    if (t >= len) return;
-    const uint32_t* v = s.v0[q];
-    const uint32_t* vl = s.vlast[q];
-    const uint32_t x = __ldg(v + t);
-    const uint32_t ll = s.last_len[q];
-    uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
-    if (!vl && ll == (1u << s.sym_shift) && ((((uint64_t)x + s.global_offset) >> s.sym_shift) & 1ull) == 0)
-        e = (uint64_t)x + (2u << s.sym_shift);  // k = 1 sibling skip
-    s.succ[slot0 + threadIdx.x] = gallop_lower_bound(v, t + 1, len, e);
-}
-
 // Pointer doubling inside one tile.  ptr[i] (shared) holds a V_0 index; indices inside
 // [base, base + SEL_TILE) are followed, anything else is final.
 __device__ __forceinline__ uint32_t sel_hop(const uint32_t* ptr, uint32_t p, uint32_t base)
@@ -147,7 +127,18 @@ __global__ void __launch_bounds__(SEL_TILE) sel_tile_kernel(SelDesc s)
     const uint32_t len = s.v0_len[q];
     if (base >= len) return;                     // whole tile beyond the viable list (uniform)
     const uint32_t t = base + threadIdx.x;
-    uint32_t p = t < len ? s.succ[slot0 + threadIdx.x] : 0xFFFFFFF0u;
+    uint32_t p = 0xFFFFFFF0u;
+    if (t < len) {  // succ(t) = lower_bound(V_0, E(V_0[t]))
+        const uint32_t* v = s.v0[q];
+        const uint32_t* vl = s.vlast[q];
+        const uint32_t x = __ldg(v + t);
+        const uint32_t ll = s.last_len[q];
+        uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
+        if (!vl && ll == (1u << s.sym_shift) && ((((uint64_t)x + s.global_offset) >> s.sym_shift) & 1ull) == 0)
+            e = (uint64_t)x + (2u << s.sym_shift);  // k = 1 sibling skip
+        p = gallop_lower_bound(v, t + 1, len, e);
+        s.succ[slot0 + threadIdx.x] = p;
+    }
     ptr[threadIdx.x] = p;
     __syncthreads();
 #pragma unroll 1
@@ -217,7 +208,10 @@ __global__ void __launch_bounds__(SEL_TILE) sel_mark_kernel(SelDesc s)
     __shared__ uint32_t s_q;
     const uint32_t slot0 = blockIdx.x * SEL_TILE;
     const uint32_t e = s.entry[blockIdx.x];
-    if (e == NONE32) return;  // tile not entered: flags stay 0 (uniform)
+    if (e == NONE32) {  // tile not entered (uniform)
+        if (threadIdx.x == 0) s.tile_count[blockIdx.x] = 0;
+        return;
+    }
     if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
     __syncthreads();
     const uint32_t q = s_q;
@@ -239,14 +233,18 @@ __global__ void __launch_bounds__(SEL_TILE) sel_mark_kernel(SelDesc s)
         ptr[threadIdx.x] = p;
         __syncthreads();
     }
-    if (t < len) s.flags[slot0 + threadIdx.x] = (uint8_t)mark[threadIdx.x];
+    const bool sel = t < len && mark[threadIdx.x];
+    const uint32_t bits = __ballot_sync(0xffffffffu, sel);
+    if ((threadIdx.x & 31) == 0) s.flagbits[blockIdx.x * 32 + (threadIdx.x >> 5)] = bits;
+    const int total = __syncthreads_count(sel);
+    if (threadIdx.x == 0) s.tile_count[blockIdx.x] = (uint32_t)total;
 }
 
-// counts[q] = mrank[sel_off[q+1]] - mrank[sel_off[q]]
+// counts[q] = selected elements in the query's tiles
 __global__ void sel_counts_kernel(SelDesc s)
 {
     uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q < s.nq) s.counts[q] = (uint64_t)(s.mrank[s.sel_off[q + 1]] - s.mrank[s.sel_off[q]]);
+    if (q < s.nq) s.counts[q] = (uint64_t)(s.tile_prefix[s.sel_off[q + 1] / SEL_TILE] - s.tile_prefix[s.sel_off[q] / SEL_TILE]);
 }
 
 __global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
@@ -259,10 +257,21 @@ __global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
     const uint32_t q = s_q;
     const uint32_t slot = slot0 + threadIdx.x;
     const uint32_t t = slot - s.sel_off[q];
-    if (t >= s.v0_len[q] || !s.flags[slot]) return;
-    const uint32_t o = s.mrank[slot];
-    const uint32_t qfirst = s.mrank[s.sel_off[q]];
-    const uint32_t qend = s.mrank[s.sel_off[q + 1]];
+    // rank of the element = matches of earlier tiles + of earlier warps of this tile + of earlier lanes
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t wbits = s.flagbits[blockIdx.x * 32 + lane];  // lane l holds warp l's bits
+    uint32_t inc = __popc(wbits);
+#pragma unroll
+    for (int dd = 1; dd < 32; dd <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, dd);
+        if (lane >= (uint32_t)dd) inc += up;
+    }
+    const uint32_t before = __shfl_sync(0xffffffffu, inc - __popc(wbits), warp);
+    const uint32_t bits = __shfl_sync(0xffffffffu, wbits, warp);
+    if (!((bits >> lane) & 1u)) return;
+    const uint32_t o = s.tile_prefix[blockIdx.x] + before + __popc(bits & ((1u << lane) - 1u));
+    const uint32_t qfirst = s.tile_prefix[s.sel_off[q] / SEL_TILE];
+    const uint32_t qend = s.tile_prefix[s.sel_off[q + 1] / SEL_TILE];
     const uint32_t k = s.kq[q];
     const uint32_t x = __ldg(s.v0[q] + t);
     const uint64_t g = s.global_offset;
