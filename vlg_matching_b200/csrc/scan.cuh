@@ -13,11 +13,11 @@
 //  * every warp owns one contiguous chunk of the shard ("row") and walks it 256 positions per step:
 //    lane l holds bytes [8l, 8l+12) of the step in registers (one coalesced 8-byte load + a shuffle), looks
 //    up the class-mask byte of its 8 positions and packs them into 64 bits.  A warp prefix sum of the
-//    popcounts gives every lane its place in POSITION ORDER; one short loop over the set bits appends
-//    4-byte items (position in row | class << 16) to the warp's circular queue.
+//    popcounts gives every lane its place in (POSITION, CLASS) ORDER; one short loop over the set bits
+//    appends 4-byte items (position in row | (class - 1) << 16), one per probe, to the warp's circular queue.
 //  * the queue is drained only in full rounds of 32 items (leftovers wait for the next step), all lanes
-//    busy: re-read the item's 8-byte window from the text (L1), mask it to the class length, one hash
-//    probe, then a warp-wide emit.
+//    busy with one probe each: re-read the item's 8-byte window from the text (L1), mask it to the lane's
+//    class length, one hash probe, then a warp-wide emit.
 //  * pass 1 counts occurrences per (row, pattern); the column-wise exclusive scan of that count matrix
 //    gives every row its write cursor per pattern; pass 2 repeats the walk and writes positions at
 //    cursor + rank (rank among equal patterns of the round by __match_any_sync), which makes every list
@@ -105,88 +105,86 @@ constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S /
                              (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t);
 
 // One drain round: the first n (<= 32) queue entries starting at qhead, one per lane, all lanes converged.
-// Entry = (position - row start) | class-mask byte << 16.  The 8-byte window of the position is re-read
-// from the text (L1-resident: the warp loaded that line moments ago).  The classes present in the round
-// are visited in ascending, warp-uniform order; in each visit the lanes that carry the class mask their
-// window to the class length and probe the hash table (one 4-byte slot word per probe; the key itself is
-// compared only on a tag hit).  Hits are ranked among equal patterns in lane (= position) order.  A
-// pattern belongs to exactly one class, so every list receives its positions in ascending order.
+// Entry = (position - row start) | (class - 1) << 16: ONE probe, so a lane never idles while the warp visits a
+// class it does not carry.  The 8-byte window of the position is re-read from the text (L1-resident: the
+// warp loaded that line moments ago), masked to the lane's class length and looked up in the hash table (one
+// 4-byte slot word per probe; the key itself is compared only on a tag hit).  Hits are ranked among equal
+// patterns in lane order = (position, class) order.  A pattern belongs to exactly one class and the queue is
+// FIFO per class, so every list receives its positions in ascending order.
 template <bool FILL>
 __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* cur, const uint32_t* q,
                                                  uint32_t qhead, uint32_t n, uint32_t row_lo, const uint32_t* mrow,
                                                  uint32_t lane, uint32_t lt_mask, uint32_t* stream_row, uint32_t& nh)
 {
-    uint32_t p = 0, cmask = 0, wlo = 0, whi = 0;
-    if (lane < n) {
+    uint32_t p = 0, c = 1, klo = 0, khi = 0;
+    bool more = lane < n;
+    if (more) {
         const uint32_t e = q[(qhead + lane) & (SCAN_QCAP - 1)];
         p = row_lo + (e & 0xFFFFu);
-        cmask = e >> 16;
+        c = ((e >> 16) & 7u) + 1u;
         const uint32_t* t32 = reinterpret_cast<const uint32_t*>(a.text + (p & ~3u));
         const uint32_t w0 = __ldg(t32), w1 = __ldg(t32 + 1), w2 = __ldg(t32 + 2);
         const uint32_t sh = (p & 3u) * 8u;
-        wlo = __funnelshift_r(w0, w1, sh);
-        whi = __funnelshift_r(w1, w2, sh);
+        const uint32_t wlo = __funnelshift_r(w0, w1, sh), whi = __funnelshift_r(w1, w2, sh);
+        // bytes [0, c) of the window: 64-bit mask 2^(8c) - 1 split in two words (c = 8: all ones)
+        const uint32_t mlo = c >= 4 ? 0xFFFFFFFFu : ((1u << (8 * c)) - 1u);
+        const uint32_t mhi = c >= 8 ? 0xFFFFFFFFu : (c > 4 ? ((1u << (8 * (c - 4))) - 1u) : 0u);
+        klo = wlo & mlo;
+        khi = whi & mhi;
     }
-    uint32_t classes = __reduce_or_sync(0xffffffffu, cmask);
-    while (classes) {
-        const uint32_t c = __ffs(classes);  // class 1..8, warp-uniform
-        classes &= classes - 1;
-        const uint32_t klo = c >= 4 ? wlo : (wlo & ((1u << (8 * c)) - 1u));
-        const uint32_t khi = c >= 8 ? whi : (c > 4 ? (whi & ((1u << (8 * (c - 4))) - 1u)) : 0u);
-        const uint32_t h = scan_mix(klo, khi, c);
-        const uint32_t want = scan_slot_word(h, c);
-        uint32_t slot = h & (SCAN_H - 1);
-        bool more = (cmask >> (c - 1)) & 1u;
-        do {
-            uint32_t pid = NONE32;
-            while (more) {
-                const uint32_t s = T->slot[slot];
-                slot = (slot + 1) & (SCAN_H - 1);
-                if (s == 0) { more = false; break; }
-                if ((s & ~SCAN_PID_MASK) != want) continue;
-                const uint32_t cand = s & SCAN_PID_MASK;
-                if (T->klo[cand] != klo || T->khi[cand] != khi) continue;
-                bool ok;
-                if (c < 8) {
-                    ok = (uint64_t)p + c <= a.valid_len;
-                    more = false;  // classes 1..7 have at most one entry per key
-                } else {
-                    const uint32_t L = a.long_len[cand];
-                    ok = (uint64_t)p + L <= a.valid_len;
-                    if (ok) {
-                        const uint8_t* pat = a.long_blob + a.long_off[cand];
-                        const uint8_t* txt = a.text + p;
-                        for (uint32_t j = 8; j < L; j++)
-                            if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
-                    }
-                }
-                // class 8: one candidate per emit, hit or miss -- lanes holding the same key walk the same
-                // slot sequence, so a pattern is emitted by all its lanes together and its list stays sorted
-                if (ok) pid = cand;
-                break;
-            }
-            // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
-            const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
-            if (hits) {
-                if (!FILL && stream_row) {
-                    const uint32_t at = nh + __popc(hits & lt_mask);
-                    if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
-                    nh += __popc(hits);
-                }
-                const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-                const int leader = __ffs(grp) - 1;
-                uint32_t old = 0;
-                if (pid != NONE32 && (int)lane == leader) {
-                    const uint32_t sh = (pid & 1u) * 16;
-                    old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
-                }
-                if (FILL) {
-                    old = __shfl_sync(0xffffffffu, old, leader);
-                    if (pid != NONE32)
-                        a.out[__ldg(a.list_base + pid) + __ldg(mrow + pid) + old + __popc(grp & lt_mask)] = p;
+    const uint32_t h = scan_mix(klo, khi, c);
+    const uint32_t want = scan_slot_word(h, c);
+    uint32_t slot = h & (SCAN_H - 1);
+    for (;;) {
+        uint32_t pid = NONE32;
+        while (more) {
+            const uint32_t s = T->slot[slot];
+            slot = (slot + 1) & (SCAN_H - 1);
+            if (s == 0) { more = false; break; }
+            if ((s & ~SCAN_PID_MASK) != want) continue;
+            const uint32_t cand = s & SCAN_PID_MASK;
+            if (T->klo[cand] != klo || T->khi[cand] != khi) continue;
+            bool ok;
+            if (c < 8) {
+                ok = (uint64_t)p + c <= a.valid_len;
+                more = false;  // classes 1..7 have at most one entry per key
+            } else {
+                const uint32_t L = a.long_len[cand];
+                ok = (uint64_t)p + L <= a.valid_len;
+                if (ok) {
+                    const uint8_t* pat = a.long_blob + a.long_off[cand];
+                    const uint8_t* txt = a.text + p;
+                    for (uint32_t j = 8; j < L; j++)
+                        if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
                 }
             }
-        } while (c == 8 && __any_sync(0xffffffffu, more));
+            // class 8: one candidate per emit, hit or miss -- lanes holding the same key walk the same
+            // slot sequence, so a pattern is emitted by all its lanes together and its list stays sorted
+            if (ok) pid = cand;
+            break;
+        }
+        // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
+        const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
+        if (hits) {
+            if (!FILL && stream_row) {
+                const uint32_t at = nh + __popc(hits & lt_mask);
+                if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
+                nh += __popc(hits);
+            }
+            const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+            const int leader = __ffs(grp) - 1;
+            uint32_t old = 0;
+            if (pid != NONE32 && (int)lane == leader) {
+                const uint32_t sh = (pid & 1u) * 16;
+                old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+            }
+            if (FILL) {
+                old = __shfl_sync(0xffffffffu, old, leader);
+                if (pid != NONE32)
+                    a.out[__ldg(a.list_base + pid) + __ldg(mrow + pid) + old + __popc(grp & lt_mask)] = p;
+            }
+        }
+        if (!__any_sync(0xffffffffu, more)) break;  // only class-8 lanes can still have candidates
     }
 }
 
@@ -260,13 +258,14 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             if (left < 4) { s1 = 0u; s0 &= left ? (0xFFFFFFFFu >> (8 * (4 - left))) : 0u; }
             else if (left < 8) s1 &= left > 4 ? (0xFFFFFFFFu >> (8 * (8 - left))) : 0u;
         }
-        // ---- candidate positions of the lane (non-zero mask bytes), then their place in position order
-        uint32_t nz0 = s0 | (s0 >> 4), nz1 = s1 | (s1 >> 4);
-        nz0 |= nz0 >> 2; nz1 |= nz1 >> 2;
-        nz0 = (nz0 | (nz0 >> 1)) & 0x01010101u;
-        nz1 = (nz1 | (nz1 >> 1)) & 0x01010101u;
-        const uint32_t cnt = __popc(nz0) + __popc(nz1);
-        uint32_t incl = cnt;
+        // ---- one queue entry per set mask bit = one (position, class) probe, in (position, class) order.  The
+        // queue starts a step with fewer than 32 leftovers, so up to SCAN_QCAP - 32 new entries go in at once
+        // (the common case); a step with more probes (small alphabets: every position carries several
+        // classes) is enqueued class by class, at most 256 entries at a time.  Entries of one class stay in
+        // FIFO = position order either way.
+        const uint32_t rel0 = off - lo;
+        const uint32_t all = __popc(s0) + __popc(s1);
+        uint32_t incl = all;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
@@ -274,29 +273,51 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         }
         const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
         if (total == 0) continue;
-        // ---- enqueue (position in row | mask << 16); at most 256 new entries, the queue holds 512 and
-        // starts every step with fewer than 32
-        {
-            uint32_t idx = qhead + qcount + incl - cnt;
-            const uint32_t rel0 = off - lo;
+        if (total <= SCAN_QCAP - 32) {
+            uint32_t idx = qhead + qcount + incl - all;
+            for (uint32_t m = s0; m; m &= m - 1) {
+                const uint32_t b = __ffs(m) - 1;
+                q[idx++ & (SCAN_QCAP - 1)] = (rel0 + (b >> 3)) | ((b & 7u) << 16);
+            }
+            for (uint32_t m = s1; m; m &= m - 1) {
+                const uint32_t b = __ffs(m) - 1;
+                q[idx++ & (SCAN_QCAP - 1)] = (rel0 + 4 + (b >> 3)) | ((b & 7u) << 16);
+            }
+            qcount += total;
+            __syncwarp();
+            while (qcount >= 32) {  // drain full rounds; fewer than 32 leftovers wait for the next step
+                scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
+                qhead = (qhead + 32) & (SCAN_QCAP - 1);
+                qcount -= 32;
+            }
+            __syncwarp();
+        } else {
+            const uint32_t present = __reduce_or_sync(0xffffffffu, s0 | s1);
+            uint32_t classes = (present | (present >> 8) | (present >> 16) | (present >> 24)) & 0xFFu;
+            while (classes) {
+                const uint32_t cb = __ffs(classes) - 1;  // class - 1, warp-uniform
+                classes &= classes - 1;
+                const uint32_t t0 = (s0 >> cb) & 0x01010101u, t1 = (s1 >> cb) & 0x01010101u;
+                const uint32_t mine = __popc(t0) + __popc(t1);
+                uint32_t inc2 = mine;
 #pragma unroll
-            for (int j = 0; j < SCAN_PPL; j++) {
-                const uint32_t mj = ((j < 4 ? s0 : s1) >> (8 * (j & 3))) & 0xFFu;
-                if (mj) {
-                    q[idx & (SCAN_QCAP - 1)] = (rel0 + j) | (mj << 16);
-                    idx++;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xffffffffu, inc2, d);
+                    if (lane >= (uint32_t)d) inc2 += o;
                 }
+                uint32_t idx = qhead + qcount + inc2 - mine;
+                for (uint32_t m = t0; m; m &= m - 1) q[idx++ & (SCAN_QCAP - 1)] = (rel0 + ((__ffs(m) - 1) >> 3)) | (cb << 16);
+                for (uint32_t m = t1; m; m &= m - 1) q[idx++ & (SCAN_QCAP - 1)] = (rel0 + 4 + ((__ffs(m) - 1) >> 3)) | (cb << 16);
+                qcount += __shfl_sync(0xffffffffu, inc2, 31);
+                __syncwarp();
+                while (qcount >= 32) {
+                    scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
+                    qhead = (qhead + 32) & (SCAN_QCAP - 1);
+                    qcount -= 32;
+                }
+                __syncwarp();
             }
         }
-        qcount += total;
-        __syncwarp();
-        // ---- drain full rounds; fewer than 32 leftovers wait for the next step
-        while (qcount >= 32) {
-            scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
-            qhead = (qhead + 32) & (SCAN_QCAP - 1);
-            qcount -= 32;
-        }
-        __syncwarp();
     }
     if (qcount) scan_drain_round<FILL>(a, T, cur, q, qhead, qcount, lo, mrow, lane, lt_mask, stream_row, nh);
     if (!FILL) {

@@ -395,18 +395,11 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     }
     if (sel_run >= 0xFFFF0000ull) throw CudaError{cudaErrorInvalidValue, __FILE__, __LINE__};
     sel_off[nq] = (uint32_t)sel_run;
-    const uint32_t sel_total = (uint32_t)sel_run;
-    const uint32_t ntiles = sel_total / SEL_TILE;
+    // upper bounds (every occurrence of P_1 viable); the real layout follows the join, from the V_0 sizes
+    const uint32_t sel_total_ub = (uint32_t)sel_run;
+    const uint32_t ntiles_ub = sel_total_ub / SEL_TILE;
+    const uint32_t nchunks_ub = ntiles_ub / SEL_CHUNK_TILES + nq;
     std::vector<uint32_t> chunk_q, chunk_tile0, q_chunk0(nq);
-    for (uint32_t s = 0; s < nq; s++) {
-        q_chunk0[s] = (uint32_t)chunk_q.size();
-        const uint32_t t0 = sel_off[s] / SEL_TILE, t1 = sel_off[s + 1] / SEL_TILE;
-        for (uint32_t t = t0; t < t1; t += SEL_CHUNK_TILES) {
-            chunk_q.push_back(s);
-            chunk_tile0.push_back(t);
-        }
-    }
-    const uint32_t nchunks = (uint32_t)chunk_q.size();
 
     // ---- control blob
     Packer ctl;
@@ -421,10 +414,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             h.o_right_len = ctl.put(h.right_len);
         }
     }
-    const size_t o_sel_off = ctl.put(sel_off), o_kq = ctl.put(kq), o_last_len = ctl.put(last_len),
+    const size_t o_kq = ctl.put(kq), o_last_len = ctl.put(last_len),
                  o_entry = ctl.put(entry_local), o_exit = ctl.put(exit_init), o_first = ctl.put(first_init), o_list0 = ctl.put(list0),
-                 o_list0_len = ctl.put(list0_len), o_last_list = ctl.put(last_list), o_chunk_q = ctl.put(chunk_q),
-                 o_chunk_tile0 = ctl.put(chunk_tile0), o_q_chunk0 = ctl.put(q_chunk0);
+                 o_list0_len = ctl.put(list0_len), o_last_list = ctl.put(last_list);
     std::vector<const uint32_t*> tab(4 * MAX_K, nullptr);  // depth_vpos | depth_vnxt | depth_vlast | depth_vseg
     const size_t o_tab = ctl.put(tab);                     // patched below once the arena addresses are known
     std::vector<uint64_t> zeros64(nq, 0);
@@ -437,11 +429,13 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     for (uint32_t d = 1; d < kmax; d++)
         need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
     need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
-    need += 2 * Arena::padded(sel_total, 4) + Arena::padded((size_t)ntiles * 32, 4);   // succ, exitp, flag bits
-    need += 4 * Arena::padded(ntiles + 2, 4);                                          // entry, spec, tile count / prefix
-    need += 2 * Arena::padded(nchunks + 1, 4);                                         // spec_exit, coalesce
+    need += 2 * Arena::padded(sel_total_ub, 4) + Arena::padded((size_t)ntiles_ub * 32, 4);  // succ, exitp, flag bits
+    need += 4 * Arena::padded(ntiles_ub + 2, 4);                                       // entry, spec, tile count / prefix
+    need += 2 * Arena::padded(nchunks_ub + 1, 4);                                      // spec_exit, coalesce
+    const size_t ctl2_bytes = Arena::padded(nq + 1, 4) + Arena::padded(nq, 4) + 2 * Arena::padded(nchunks_ub, 4);
+    need += ctl2_bytes + 1024;                                                         // selection layout (second blob)
     need += Arena::padded(nq, 8) + Arena::padded(kmax + 1, 4);                         // counts, viable totals
-    const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(max_slots, sel_total));
+    const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(max_slots, sel_total_ub));
     need += Arena::padded(scratch_words, 4);
     c.join_arena.reserve(need);
     Arena& A = c.join_arena;
@@ -466,15 +460,16 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     const uint32_t** d_vlast = A.take<const uint32_t*>(nq);
     uint32_t* d_v0_len = A.take<uint32_t>(nq);
     uint32_t* d_t0 = A.take<uint32_t>(nq);
-    uint32_t* d_succ = A.take<uint32_t>(sel_total);
-    uint32_t* d_exitp = A.take<uint32_t>(sel_total);
-    uint32_t* d_flagbits = A.take<uint32_t>((size_t)ntiles * 32);
-    uint32_t* d_tile_count = A.take<uint32_t>(ntiles + 2);
-    uint32_t* d_tile_prefix = A.take<uint32_t>(ntiles + 2);
-    uint32_t* d_entry = A.take<uint32_t>(ntiles + 1);
-    uint32_t* d_spec = A.take<uint32_t>(ntiles + 1);
-    uint32_t* d_spec_exit = A.take<uint32_t>(nchunks + 1);
-    uint32_t* d_coalesce = A.take<uint32_t>(nchunks + 1);
+    uint32_t* d_succ = A.take<uint32_t>(sel_total_ub);
+    uint32_t* d_exitp = A.take<uint32_t>(sel_total_ub);
+    uint32_t* d_flagbits = A.take<uint32_t>((size_t)ntiles_ub * 32);
+    uint32_t* d_tile_count = A.take<uint32_t>(ntiles_ub + 2);
+    uint32_t* d_tile_prefix = A.take<uint32_t>(ntiles_ub + 2);
+    uint32_t* d_entry = A.take<uint32_t>(ntiles_ub + 1);
+    uint32_t* d_spec = A.take<uint32_t>(ntiles_ub + 1);
+    uint32_t* d_spec_exit = A.take<uint32_t>(nchunks_ub + 1);
+    uint32_t* d_coalesce = A.take<uint32_t>(nchunks_ub + 1);
+    uint8_t* d_ctl2 = A.take<uint8_t>(ctl2_bytes + 1024);
     uint64_t* d_counts = A.take<uint64_t>(nq);
     uint32_t* d_viable = A.take<uint32_t>(kmax + 1);
     uint32_t* scratch = A.take<uint32_t>(scratch_words);
@@ -529,8 +524,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     // ---- selection
     SelDesc S;
     S.nq = nq;
-    S.total_slots = sel_total;
-    S.sel_off = dev_at<const uint32_t>(d_ctl, o_sel_off);
+    S.total_slots = 0;     // layout fields are set once the V_0 sizes are known (below)
+    S.sel_off = nullptr;
     S.kq = dev_at<const uint32_t>(d_ctl, o_kq);
     S.last_len = dev_at<const uint32_t>(d_ctl, o_last_len);
     S.entry_local = dev_at<const uint64_t>(d_ctl, o_entry);
@@ -553,10 +548,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.tile_count = d_tile_count;
     S.tile_prefix = d_tile_prefix;
     S.entry = d_entry;
-    S.nchunks = nchunks;
-    S.chunk_q = dev_at<const uint32_t>(d_ctl, o_chunk_q);
-    S.chunk_tile0 = dev_at<const uint32_t>(d_ctl, o_chunk_tile0);
-    S.q_chunk0 = dev_at<const uint32_t>(d_ctl, o_q_chunk0);
+    S.nchunks = 0;
+    S.chunk_q = S.chunk_tile0 = S.q_chunk0 = nullptr;
     S.spec = d_spec;
     S.spec_exit = d_spec_exit;
     S.coalesce = d_coalesce;
@@ -575,10 +568,47 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     co.h_starts = co.h_tuples = nullptr;
     std::vector<uint32_t> viable(kmax + 1, 0);
 
-    if (sel_total) {
+    // ---- V_0 of every query (sizes travel to the host: selection tiles are laid out over the viable starts
+    // only -- on the configs of BASELINE.json fewer than a sixth of the occurrences of P_1 are viable)
+    std::vector<uint32_t> v0_len(nq, 0);
+    if (sel_total_ub) {
         c.begin(ST_SELECT_SUCC);
         sel_resolve_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
         c.end(ST_SELECT_SUCC, 1, (uint64_t)nq * 32);
+        VLGB_CUDA(cudaMemcpyAsync(v0_len.data(), d_v0_len, (size_t)nq * 4, cudaMemcpyDeviceToHost, c.stream));
+        VLGB_CUDA(cudaGetLastError());
+        VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: viable-start counts
+        c.stats.d2h_bytes += (uint64_t)nq * 4;
+    }
+    sel_run = 0;
+    for (uint32_t s = 0; s < nq; s++) {
+        sel_off[s] = (uint32_t)sel_run;
+        sel_run += ((uint64_t)v0_len[s] + SEL_TILE - 1) / SEL_TILE * SEL_TILE;
+    }
+    sel_off[nq] = (uint32_t)sel_run;
+    const uint32_t sel_total = (uint32_t)sel_run;
+    const uint32_t ntiles = sel_total / SEL_TILE;
+    for (uint32_t s = 0; s < nq; s++) {
+        q_chunk0[s] = (uint32_t)chunk_q.size();
+        const uint32_t t0 = sel_off[s] / SEL_TILE, t1 = sel_off[s + 1] / SEL_TILE;
+        for (uint32_t t = t0; t < t1; t += SEL_CHUNK_TILES) {
+            chunk_q.push_back(s);
+            chunk_tile0.push_back(t);
+        }
+    }
+    const uint32_t nchunks = (uint32_t)chunk_q.size();
+    if (sel_total) {
+        Packer ctl2;
+        const size_t o_sel_off = ctl2.put(sel_off), o_q_chunk0 = ctl2.put(q_chunk0), o_chunk_q = ctl2.put(chunk_q),
+                     o_chunk_tile0 = ctl2.put(chunk_tile0);
+        VLGB_CUDA(cudaMemcpyAsync(d_ctl2, ctl2.host.data(), ctl2.host.size(), cudaMemcpyHostToDevice, c.stream));
+        c.stats.h2d_bytes += ctl2.host.size();
+        S.total_slots = sel_total;
+        S.sel_off = dev_at<const uint32_t>(d_ctl2, o_sel_off);
+        S.nchunks = nchunks;
+        S.chunk_q = dev_at<const uint32_t>(d_ctl2, o_chunk_q);
+        S.chunk_tile0 = dev_at<const uint32_t>(d_ctl2, o_chunk_tile0);
+        S.q_chunk0 = dev_at<const uint32_t>(d_ctl2, o_q_chunk0);
         c.begin(ST_SELECT_TILE);
         sel_tile_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
         c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 16);
