@@ -9,7 +9,7 @@
 //    class = min(len, 8).  Class <= 7 keys are exact; class 8 entries (len >= 8) are verified byte by byte.
 //  * shared memory per CTA: open-addressing hash table of the pass (SoA, SCAN_H slots), the prefilter
 //    f3 (hashed first 3 bytes -> byte with bit c-1 set for every class c = 3..8 that has a pattern with that
-//    prefix; f1/f2 bitmaps for 1- and 2-byte patterns), one u16 cursor row and one work queue per warp.
+//    prefix; f1/f2 bitmaps for 1- and 2-byte patterns) and one work queue per warp.
 //  * every warp owns one contiguous chunk of the shard ("row") and walks it 256 positions per step:
 //    lane l holds bytes [8l, 8l+12) of the step in registers (one coalesced 8-byte load + a shuffle), looks
 //    up the class-mask byte of its 8 positions and packs them into 64 bits.  A warp prefix sum of the
@@ -18,10 +18,11 @@
 //  * the queue is drained only in full rounds of 32 items (leftovers wait for the next step), all lanes
 //    busy with one probe each: re-read the item's 8-byte window from the text (L1), mask it to the lane's
 //    class length, one hash probe, then a warp-wide emit.
-//  * pass 1 counts occurrences per (row, pattern); the column-wise exclusive scan of that count matrix
-//    gives every row its write cursor per pattern; pass 2 repeats the walk and writes positions at
-//    cursor + rank (rank among equal patterns of the round by __match_any_sync), which makes every list
-//    sorted and the result deterministic.
+//  * pass 1 counts occurrences per (row, pattern) with fire-and-forget reductions into the (L2-resident)
+//    count matrix and records every hit in the row's stream; the column-wise exclusive scan of the matrix
+//    gives every row its write cursor per pattern; pass 2 scatters the stream (scan_scatter_kernel) -- or, for
+//    rows whose stream overflowed, repeats the walk -- writing positions at cursor + rank (rank among equal
+//    patterns of the round by __match_any_sync), which makes every list sorted and the result deterministic.
 //  * algorithmic bytes per pass: 2 x shard bytes read + 4 B per occurrence written (+ count matrix).
 #pragma once
 #include <algorithm>
@@ -34,7 +35,7 @@ namespace vlgb {
 
 constexpr int SCAN_S = 2048;       // patterns per pass
 constexpr int SCAN_H = 8192;       // hash slots (4 B each; load factor <= 25%)
-constexpr int SCAN_WARPS = 16;     // warps per CTA
+constexpr int SCAN_WARPS = 32;     // warps per CTA (one CTA per SM: the pass tables take half its shared memory)
 constexpr int SCAN_PPL = 8;        // positions per lane per step
 constexpr int SCAN_STEP = 32 * SCAN_PPL;
 constexpr int SCAN_F3 = 65536;     // 3-byte prefilter entries (u8: bit c-1 set = class c present, c = 3..8)
@@ -88,7 +89,8 @@ struct ScanArgs {
     const uint32_t* long_len;  // [s_act] full length (class 8 only: len >= 8)
     const uint32_t* long_off;  // [s_act] offset into long_blob
     const uint8_t* long_blob;
-    uint32_t* matrix;        // [rows][s_stride]: counts (pass 1 out) / write cursors inside each list (pass 2 in)
+    uint32_t* matrix;        // [rows][s_stride]: counts (pass 1, zeroed by the host first) / write cursors inside
+                             // each list (pass 2; the re-scan advances them)
     const uint64_t* list_base;  // pass 2: [s_act] first word of every list inside `out`
     uint32_t* out;           // pass 2: positions (u32, shard-local)
     // hit stream: pass 1 records every occurrence of a row as (position - row start) | pid << 16, in the order
@@ -101,8 +103,7 @@ struct ScanArgs {
     uint32_t only_overflow;  // FILL kernel: skip the rows the scatter kernel handles
 };
 
-constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S / 2) * sizeof(uint32_t) +
-                             (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t);
+constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t);
 
 // One drain round: the first n (<= 32) queue entries starting at qhead, one per lane, all lanes converged.
 // Entry = (position - row start) | (class - 1) << 16: ONE probe, so a lane never idles while the warp visits a
@@ -112,8 +113,8 @@ constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S /
 // patterns in lane order = (position, class) order.  A pattern belongs to exactly one class and the queue is
 // FIFO per class, so every list receives its positions in ascending order.
 template <bool FILL>
-__device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* cur, const uint32_t* q,
-                                                 uint32_t qhead, uint32_t n, uint32_t row_lo, const uint32_t* mrow,
+__device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, const uint32_t* q,
+                                                 uint32_t qhead, uint32_t n, uint32_t row_lo, uint32_t* mrow,
                                                  uint32_t lane, uint32_t lt_mask, uint32_t* stream_row, uint32_t& nh)
 {
     uint32_t p = 0, c = 1, klo = 0, khi = 0;
@@ -163,25 +164,27 @@ __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTa
             if (ok) pid = cand;
             break;
         }
-        // ---- warp-wide emit (all 32 lanes take part): rank among equal patterns = position order
+        // ---- warp-wide emit (all 32 lanes take part)
         const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
         if (hits) {
-            if (!FILL && stream_row) {
-                const uint32_t at = nh + __popc(hits & lt_mask);
-                if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
-                nh += __popc(hits);
-            }
-            const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-            const int leader = __ffs(grp) - 1;
-            uint32_t old = 0;
-            if (pid != NONE32 && (int)lane == leader) {
-                const uint32_t sh = (pid & 1u) * 16;
-                old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
-            }
-            if (FILL) {
+            if (!FILL) {
+                // pass 1: bump the (row, pattern) count in the matrix (fire-and-forget L2 reduction) and append
+                // the hit to the row's stream at its place in lane = (position, class) order
+                if (pid != NONE32) atomicAdd(mrow + pid, 1u);
+                if (stream_row) {
+                    const uint32_t at = nh + __popc(hits & lt_mask);
+                    if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
+                    nh += __popc(hits);
+                }
+            } else {
+                // pass 2 (rows without a usable stream): the matrix entry is the row's write cursor inside the
+                // list; rank among equal patterns of the round = lane order = position order
+                const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+                const int leader = __ffs(grp) - 1;
+                uint32_t old = 0;
+                if (pid != NONE32 && (int)lane == leader) old = atomicAdd(mrow + pid, (uint32_t)__popc(grp));
                 old = __shfl_sync(0xffffffffu, old, leader);
-                if (pid != NONE32)
-                    a.out[__ldg(a.list_base + pid) + __ldg(mrow + pid) + old + __popc(grp & lt_mask)] = p;
+                if (pid != NONE32) a.out[__ldg(a.list_base + pid) + old + __popc(grp & lt_mask)] = p;
             }
         }
         if (!__any_sync(0xffffffffu, more)) break;  // only class-8 lanes can still have candidates
@@ -193,8 +196,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     ScanTables* T = reinterpret_cast<ScanTables*>(smem_raw);
-    uint32_t* cursors = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables));
-    uint32_t* queues = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * (SCAN_S / 2) * 4);
+    uint32_t* queues = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables));
 
     {  // stage the pass tables
         const uint4* src = reinterpret_cast<const uint4*>(a.tables);
@@ -202,9 +204,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         for (uint32_t i = threadIdx.x; i < sizeof(ScanTables) / 16; i += blockDim.x) dst[i] = __ldg(src + i);
     }
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* cur = cursors + warp * (SCAN_S / 2);  // u16 counters, two per word
-    uint32_t* q = queues + warp * SCAN_QCAP;        // circular queue of (position - row start) | class mask << 16
-    for (uint32_t i = lane; i < SCAN_S / 2; i += 32) cur[i] = 0u;
+    uint32_t* q = queues + warp * SCAN_QCAP;        // circular queue of (position - row start) | (class - 1) << 16
     __syncthreads();
 
     const uint32_t row = blockIdx.x * SCAN_WARPS + warp;
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             qcount += total;
             __syncwarp();
             while (qcount >= 32) {  // drain full rounds; fewer than 32 leftovers wait for the next step
-                scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
+                scan_drain_round<FILL>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
                 qhead = (qhead + 32) & (SCAN_QCAP - 1);
                 qcount -= 32;
             }
@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
                 qcount += __shfl_sync(0xffffffffu, inc2, 31);
                 __syncwarp();
                 while (qcount >= 32) {
-                    scan_drain_round<FILL>(a, T, cur, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
+                    scan_drain_round<FILL>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
                     qhead = (qhead + 32) & (SCAN_QCAP - 1);
                     qcount -= 32;
                 }
@@ -319,10 +319,8 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             }
         }
     }
-    if (qcount) scan_drain_round<FILL>(a, T, cur, q, qhead, qcount, lo, mrow, lane, lt_mask, stream_row, nh);
+    if (qcount) scan_drain_round<FILL>(a, T, q, qhead, qcount, lo, mrow, lane, lt_mask, stream_row, nh);
     if (!FILL) {
-        __syncwarp();
-        for (uint32_t i = lane; i < a.s_act; i += 32) mrow[i] = (cur[i >> 1] >> ((i & 1u) * 16)) & 0xFFFFu;
         if (stream_row && lane == 0) {
             a.row_hits[row] = nh;
             if (nh > a.stream_cap) atomicAdd(a.overflow, 1u);
@@ -380,6 +378,7 @@ __global__ void scan_colsum_kernel(const uint32_t* matrix, uint32_t rows, uint32
     if (pid >= stride) return;
     uint32_t r0 = blockIdx.y * SCAN_RB, r1 = min(rows, r0 + SCAN_RB);
     uint32_t s = 0;
+#pragma unroll 16
     for (uint32_t r = r0; r < r1; r++) s += matrix[(size_t)r * stride + pid];
     part[(size_t)blockIdx.y * stride + pid] = s;
 }
@@ -406,10 +405,15 @@ __global__ void scan_rowoff_kernel(uint32_t* matrix, uint32_t rows, uint32_t str
     if (pid >= stride) return;
     uint32_t r0 = blockIdx.y * SCAN_RB, r1 = min(rows, r0 + SCAN_RB);
     uint32_t run = part[(size_t)blockIdx.y * stride + pid];
-    for (uint32_t r = r0; r < r1; r++) {
-        uint32_t c = matrix[(size_t)r * stride + pid];
-        matrix[(size_t)r * stride + pid] = run;
-        run += c;
+    for (uint32_t r = r0; r < r1; r += 16) {  // 16 independent loads in flight, then the running sum
+        uint32_t c[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) c[i] = r + i < r1 ? matrix[(size_t)(r + i) * stride + pid] : 0u;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            if (r + i < r1) matrix[(size_t)(r + i) * stride + pid] = run;
+            run += c[i];
+        }
     }
 }
 

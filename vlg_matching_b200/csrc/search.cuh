@@ -62,7 +62,6 @@ inline uint32_t scan_chunk_for(uint64_t n, int sm_count)
 {
     const uint64_t resident = (uint64_t)sm_count * SCAN_WARPS;
     uint64_t waves = (n + resident * SCAN_MAX_CHUNK - 1) / (resident * SCAN_MAX_CHUNK);
-    if (waves < 2 && n >= resident * 2 * 8192) waves = 2;
     if (waves < 1) waves = 1;
     uint64_t c = (n + resident * waves - 1) / (resident * waves);
     c = (c + SCAN_STEP - 1) / SCAN_STEP * SCAN_STEP;
@@ -194,6 +193,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     for (uint32_t p = 0; p < npass; p++) {
         ScanArgs a = args_for(p);
         c.begin(ST_SCAN_COUNT);
+        VLGB_CUDA(cudaMemsetAsync(pd[p].matrix, 0, (size_t)rows * pd[p].stride * 4, c.stream));
         if (a.has_short) scan_kernel<false, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
         else scan_kernel<false, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
         c.end(ST_SCAN_COUNT, 1, n + (uint64_t)rows * pd[p].s_act * 4);  // + 4 B per occurrence streamed, added below
