@@ -328,45 +328,89 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     }
 }
 
-// Pass 2 for the rows whose occurrences fit the hit stream: no text, no tables -- read the row's stream
-// (coalesced), rank equal patterns of a round in lane order (= the order pass 1 found them = ascending
-// position) and write every position to its place:  list_base[pid] + row cursor[pid] + seen so far + rank.
+// Pass 2 for the rows whose occurrences fit the hit stream: no text, no tables -- every position of the row's
+// stream goes to  list_base[pid] + row cursor[pid] + (hits of pid earlier in the row).
+// A whole CTA works on ONE row at a time and CTAs take consecutive rows, so all writes into a 32-byte sector of
+// a list (the segments of neighbouring rows) happen within microseconds of each other and merge in L2.  (One
+// warp per row, 4736 rows in flight for the whole kernel, left every sector partially written for ~1 ms:
+// 4x the algorithmic DRAM traffic -- profiles/r01b.)  The row's stream is cut into one slice per warp:
+//   1. every warp histograms its slice by pattern (u16 counters, two per word),
+//   2. the counters become exclusive prefixes over the slices (packed adds, one word = two patterns),
+//   3. every warp scatters its slice: rank among equal patterns of a round in lane order (= the order pass 1
+//      found them = ascending position) on top of the running counter.
 constexpr int SCAT_WARPS = 16;
 constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * (SCAN_S / 2) * sizeof(uint32_t);
 
 __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);  // [SCAT_WARPS][SCAN_S / 2]
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* cur = reinterpret_cast<uint32_t*>(smem_raw) + warp * (SCAN_S / 2);  // u16 counters, two per word
-    const uint32_t row = blockIdx.x * SCAT_WARPS + warp;
-    if (row >= a.rows) return;
-    const uint32_t nh = a.row_hits[row];
-    if (nh == 0 || nh > a.stream_cap) return;
-    for (uint32_t i = lane; i < SCAN_S / 2; i += 32) cur[i] = 0u;
-    __syncwarp();
-    const uint32_t* st = a.stream + (size_t)row * a.stream_cap;
-    const uint32_t* mrow = a.matrix + (size_t)row * a.s_stride;
-    const uint32_t lo = row * a.chunk;
+    uint32_t* cur = hist + warp * (SCAN_S / 2);
     const uint32_t lt_mask = (1u << lane) - 1u;
-    for (uint32_t i = 0; i < nh; i += 32) {
-        uint32_t pid = NONE32, p = 0;
-        uint64_t dst = 0;
-        if (i + lane < nh) {
-            const uint32_t e = __ldg(st + i + lane);
-            pid = e >> 16;
-            p = lo + (e & 0xFFFFu);
-            dst = __ldg(a.list_base + pid) + __ldg(mrow + pid);
+    const uint32_t words = (a.s_act + 1) >> 1;  // counter words in use
+    for (uint32_t row = blockIdx.x; row < a.rows; row += gridDim.x) {
+        const uint32_t nh = a.row_hits[row];
+        if (nh == 0 || nh > a.stream_cap) continue;  // uniform: nothing to do / re-scanned by the FILL kernel
+        const uint32_t* st = a.stream + (size_t)row * a.stream_cap;
+        const uint32_t* mrow = a.matrix + (size_t)row * a.s_stride;
+        const uint32_t lo = row * a.chunk;
+        const uint32_t per = ((nh + SCAT_WARPS - 1) / SCAT_WARPS + 31) & ~31u;
+        const uint32_t i0 = min(nh, warp * per), i1 = min(nh, i0 + per);
+        __syncthreads();  // the previous row's counters are no longer in use
+        for (uint32_t w = 0; w < SCAT_WARPS; w++)
+            for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) hist[w * (SCAN_S / 2) + i] = 0u;
+        __syncthreads();
+        for (uint32_t i = i0 + lane; i < i1; i += 8 * 32) {  // 8 independent loads in flight per lane
+            uint32_t e[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) e[u] = i + u * 32 < i1 ? __ldg(st + i + u * 32) : NONE32;
+#pragma unroll
+            for (int u = 0; u < 8; u++)
+                if (e[u] != NONE32) atomicAdd(&cur[e[u] >> 17], 1u << ((e[u] >> 12) & 16u));
         }
-        const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-        const int leader = __ffs(grp) - 1;
-        uint32_t old = 0;
-        if (pid != NONE32 && (int)lane == leader) {
-            const uint32_t sh = (pid & 1u) * 16;
-            old = (atomicAdd(&cur[pid >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
+            uint32_t run = 0;  // both halves stay below 65536: a pattern occurs at most once per position of the row
+#pragma unroll
+            for (uint32_t w = 0; w < SCAT_WARPS; w++) {
+                const uint32_t v = hist[w * (SCAN_S / 2) + i];
+                hist[w * (SCAN_S / 2) + i] = run;
+                run += v;
+            }
         }
-        old = __shfl_sync(0xffffffffu, old, leader);
-        if (pid != NONE32) a.out[dst + old + __popc(grp & lt_mask)] = p;
+        __syncthreads();
+        for (uint32_t i = i0; i < i1; i += 4 * 32) {  // 4 rounds per trip: their loads and gathers overlap
+            uint32_t pid[4], p[4];
+            uint64_t dst[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                pid[u] = NONE32;
+                p[u] = 0;
+                dst[u] = 0;
+                if (i + u * 32 + lane < i1) {
+                    const uint32_t e = __ldg(st + i + u * 32 + lane);
+                    pid[u] = e >> 16;
+                    p[u] = lo + (e & 0xFFFFu);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                if (pid[u] != NONE32) dst[u] = __ldg(a.list_base + pid[u]) + __ldg(mrow + pid[u]);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (i + u * 32 >= i1) break;  // uniform
+                const uint32_t grp = __match_any_sync(0xffffffffu, pid[u]);
+                const int leader = __ffs(grp) - 1;
+                uint32_t old = 0;
+                if (pid[u] != NONE32 && (int)lane == leader) {
+                    const uint32_t sh = (pid[u] & 1u) * 16;
+                    old = (atomicAdd(&cur[pid[u] >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+                }
+                old = __shfl_sync(0xffffffffu, old, leader);
+                if (pid[u] != NONE32) a.out[dst[u] + old + __popc(grp & lt_mask)] = p[u];
+            }
+        }
     }
 }
 

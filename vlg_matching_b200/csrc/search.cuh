@@ -240,7 +240,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         uint64_t bytes = 0;
         const bool streamed = pd[p].stream != nullptr;
         if (pocc && streamed) {  // scatter the recorded occurrences; only overflowed rows are scanned again
-            scan_scatter_kernel<<<(rows + SCAT_WARPS - 1) / SCAT_WARPS, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
+            scan_scatter_kernel<<<std::min<uint32_t>(rows, 3u * (uint32_t)c.sm_count), SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
             launches++;
             bytes += pocc * 8 + (uint64_t)rows * pd[p].s_act * 4;
             c.stats.bytes[ST_SCAN_COUNT] += pocc * 4;
