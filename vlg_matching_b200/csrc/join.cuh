@@ -5,22 +5,23 @@
 // an occurrence x of P_i is VIABLE iff the smallest viable occurrence y of P_{i+1} with
 // y >= x + lo_i exists and y <= x + hi_i   (lo_i = a_i + |P_i|, hi_i = b_i + |P_i|, vlg_index.hpp:95).
 //
-// One "depth" d = k-1-i is processed per launch for ALL queries of the chunk that have such a level.
+// One "depth" d = k-1-i is processed per launch set for ALL queries of the chunk that have such a level.
 // The slots of a depth are the concatenation of the left lists (one segment per query), cut into tiles of
-// 4096 slots:
-//   probe   : raw[slot] = j = lower_bound(V_right, x + lo) if V_right[j] <= x + hi, else NONE; viable count per tile
+// 4096 slots, 4 consecutive slots per thread:
+//   probe   : j = lower_bound(V_right, x + lo); viable iff V_right[j] <= x + hi.  Viable slots are compacted
+//             inside the tile (order kept) into a staging area; viable count per tile
 //   prefix  : exclusive scan of the tile counts (prefix.cuh; ~1 value per 4096 slots)
-//   compact : in-tile ranks by warp ballots; vpos / vnxt / vlast [rank] = x / j / last position of the tuple
+//   vseg    : vseg[seg] = rank of the segment's first slot, so that every query finds its segment inside the
+//             compacted arrays and no size ever has to travel to the host between depths
+//   compact : vpos / vnxt / vlast [tile prefix + i] = staged x / j / last position of the tuple
 // (A single-pass variant with a decoupled look-back was measured slower: probe times per tile vary widely and
 // the look-back makes every wave wait for its slowest tile.)
-// vseg[seg] = rank of the segment's first slot gives every query its segment inside the compacted arrays, so
-// no size ever has to travel to the host between depths.
 //
 // Both lists are ascending and x + lo is monotone in x, so a tile of consecutive slots maps to one contiguous
 // window of the right list (a merge-path partition): the window is staged in shared memory when it is small,
 // else the lanes gallop from their neighbours' answers.
-// Algorithmic bytes per depth: 4 B per slot (x) + 4 B per right-list element + 8 B per slot (raw out / in) +
-// 16 B per viable slot (x again, vlast gather; 12 written... counted as 4 + 4 + 12).
+// Algorithmic bytes per depth: 4 B per slot (x) + 4 B per right-list element read; per VIABLE slot 12 B staged,
+// 12 B read back (+ 4 B gather of the tuple end at depth > 1) and 12 B written.
 #pragma once
 #include "common.cuh"
 
@@ -45,7 +46,10 @@ struct DepthDesc {
     const uint64_t* lo;          // start-to-start lower bound of this level (saturated)
     const uint64_t* hi;
     // outputs
-    uint32_t* raw;               // [total_slots] index into the right list, NONE32 = not viable
+    uint32_t* stage_x;           // [total_slots] viable slots of every tile, compacted inside the tile:
+    uint32_t* stage_j;           //   left position / index into the right list / partner position
+    uint32_t* stage_last;
+    uint32_t* seg_rank;          // [nseg+1] viable slots of the segment's first tile before the segment's first slot
     uint32_t* tile_count;        // [tiles] viable slots per tile
     const uint32_t* tile_prefix; // [tiles+1] exclusive scan of tile_count
     const uint32_t* tile_seg;    // [tiles] segment of each tile's first slot (join_tileseg_kernel)
@@ -120,15 +124,11 @@ __device__ __forceinline__ uint32_t warp_lower_bound(const uint32_t* __restrict_
 }
 
 constexpr int JF_THREADS = 1024;
-constexpr int JF_ITEMS = 4;                          // slots per thread
-constexpr int JF_TILE = JF_THREADS * JF_ITEMS;       // slots per tile: large tiles keep the look-back short
+constexpr int JF_ITEMS = 4;                          // CONSECUTIVE slots per thread
+constexpr int JF_TILE = JF_THREADS * JF_ITEMS;       // slots per tile
 constexpr int JF_WIN = 8192;                         // right-list window staged in shared memory (elements)
 constexpr int JF_WARPS = JF_THREADS / 32;
 
-// A tile = JF_TILE consecutive slots.  Inside a tile of one segment the part of the right list that can be
-// hit, R[lb(need of first slot) .. lb(need of last slot)], is staged in shared memory when it is at most
-// JF_WIN elements (left and right lists of similar density) and searched there; otherwise lane 0 of every
-// warp gallops from the tile's first answer and the other lanes gallop from lane 0's.
 // tile_seg[t] = segment that holds slot t * JF_TILE
 __global__ void join_tileseg_kernel(const uint32_t* slot_off, uint32_t nseg, uint32_t ntiles, uint32_t* tile_seg)
 {
@@ -136,12 +136,40 @@ __global__ void join_tileseg_kernel(const uint32_t* slot_off, uint32_t nseg, uin
     if (t < ntiles) tile_seg[t] = find_segment(slot_off, 0, nseg - 1, t * (uint32_t)JF_TILE);
 }
 
+// lower_bound in shared memory, galloping from `from` (answers of consecutive slots are a few elements apart)
+__device__ __forceinline__ uint32_t smem_gallop(const uint32_t* w, uint32_t from, uint32_t len, uint64_t need)
+{
+    if (from >= len || (uint64_t)w[from] >= need) return min(from, len);
+    uint32_t lo = from, step = 1, hi;  // w[lo] < need; answer in (lo, hi]
+    for (;;) {
+        const uint32_t nx = lo + step;
+        if (nx >= len) { hi = len; break; }
+        if ((uint64_t)w[nx] >= need) { hi = nx; break; }
+        lo = nx;
+        step <<= 1;
+    }
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if ((uint64_t)w[mid] >= need) hi = mid; else lo = mid;
+    }
+    return hi;
+}
+
+// A tile = JF_TILE consecutive slots, JF_ITEMS consecutive ones per thread.  Inside a tile of one segment the
+// part of the right list that can be hit, R[lb(need of first slot) .. lb(need of last slot)], is staged in
+// shared memory when it is at most JF_WIN elements (left and right lists of similar density): a thread
+// binary-searches its first slot there and gallops on for the next ones.  Otherwise (dense right list) lane 0
+// of every warp gallops from the tile's first answer, the other lanes from lane 0's, every thread's later
+// slots from its previous answer.
+// The viable slots are compacted INSIDE the tile (order kept) into stage_{x,j,last}[tile start + rank]: only
+// viable slots ever reach memory (a sixth of the slots on BASELINE config 2), join_compact_kernel then moves
+// tile_count[tile] records per tile to their final place.
 __global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
 {
     __shared__ uint32_t s_win[JF_WIN];
-    __shared__ uint32_t s_j[2], s_count;
+    __shared__ uint32_t s_j[2];
+    __shared__ uint32_t s_wsum[JF_WARPS];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_count = 0;
     const uint32_t tile = blockIdx.x;
     const uint32_t slot0 = tile * JF_TILE;
     const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot0);
@@ -152,13 +180,13 @@ __global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
 
     // ---- single-segment tile: bracket the reachable part of the right list
     const uint32_t* R1 = nullptr;
-    uint32_t rlen1 = 0, vbase1 = 0;
+    uint32_t rlen1 = 0;
     if (single) {
         if (d.right_list) {
             R1 = d.right_list[seg_lo];
             rlen1 = d.right_len[seg_lo];
         } else {
-            vbase1 = __ldg(d.prev_vseg + seg_lo);
+            const uint32_t vbase1 = __ldg(d.prev_vseg + seg_lo);
             R1 = d.prev_vpos + vbase1;
             rlen1 = __ldg(d.prev_vseg + seg_lo + 1) - vbase1;
         }
@@ -178,142 +206,181 @@ __global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
         __syncthreads();
     }
 
-    // ---- probe: JF_ITEMS rounds of JOIN_THREADS consecutive slots
-    uint32_t viable = 0;
+    // ---- probe
+    const uint32_t sbase = slot0 + tid * JF_ITEMS;
+    uint32_t xs[JF_ITEMS], js[JF_ITEMS], ls[JF_ITEMS], segs[JF_ITEMS];
+    uint32_t okbits = 0;
+    if (single) {
+        const uint32_t so = __ldg(d.slot_off + seg_lo);
+        const uint32_t* L = d.left[seg_lo] + (sbase - so);
+        const uint64_t glo = d.lo[seg_lo], ghi = d.hi[seg_lo];
+        const uint32_t live = sbase < slot0 + nslots ? min((uint32_t)JF_ITEMS, slot0 + nslots - sbase) : 0u;
 #pragma unroll
-    for (int it = 0; it < JF_ITEMS; it++) {
-        const uint32_t slot = slot0 + it * JF_THREADS + tid;
-        const bool live = slot < slot0 + nslots;
-        uint32_t seg = seg_lo, x = 0, j = 0, last = 0;
-        bool ok = false;
+        for (int i = 0; i < JF_ITEMS; i++) {
+            xs[i] = (uint32_t)i < live ? __ldg(L + i) : 0u;
+            segs[i] = seg_lo;
+        }
         if (use_win) {
-            if (live) {
-                x = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
-                const uint64_t need = sat_add64(x, d.lo[seg]), limit = sat_add64(x, d.hi[seg]);
-                uint32_t lo = 0, hi = wlen;
-                while (lo < hi) {
-                    const uint32_t mid = (lo + hi) >> 1;
-                    if ((uint64_t)s_win[mid] < need) lo = mid + 1; else hi = mid;
+            uint32_t at = 0;
+#pragma unroll
+            for (int i = 0; i < JF_ITEMS; i++) {
+                if ((uint32_t)i >= live) break;
+                const uint64_t need = sat_add64(xs[i], glo);
+                if (i == 0) {
+                    uint32_t lo = 0, hi = wlen;
+                    while (lo < hi) {
+                        const uint32_t mid = (lo + hi) >> 1;
+                        if ((uint64_t)s_win[mid] < need) lo = mid + 1; else hi = mid;
+                    }
+                    at = lo;
+                } else {
+                    at = smem_gallop(s_win, at, wlen, need);
                 }
-                j = j_first + lo;
-                if (lo < wlen) {
-                    last = s_win[lo];
-                    ok = (uint64_t)last <= limit;
+                js[i] = j_first + at;
+                if (at < wlen) {
+                    ls[i] = s_win[at];
+                    if ((uint64_t)ls[i] <= sat_add64(xs[i], ghi)) okbits |= 1u << i;
                 }
             }
         } else {
-            const uint32_t* R = R1;
-            uint32_t rlen = rlen1;
-            uint64_t need = 0, limit = 0;
-            if (live) {
-                if (!single) {
-                    seg = find_segment(d.slot_off, seg_lo, seg_hi, slot);
-                    if (d.right_list) {
-                        R = d.right_list[seg];
-                        rlen = d.right_len[seg];
-                    } else {
-                        const uint32_t b = __ldg(d.prev_vseg + seg);
-                        R = d.prev_vpos + b;
-                        rlen = __ldg(d.prev_vseg + seg + 1) - b;
-                    }
+            // warp-uniform branch: lane 0 gallops from the tile's first answer, the rest from lane 0's
+            uint32_t j0 = 0;
+            if (lane == 0 && live) j0 = gallop_lower_bound(R1, j_first, rlen1, sat_add64(xs[0], glo));
+            j0 = __shfl_sync(0xffffffffu, j0, 0);
+            uint32_t at = j0;
+#pragma unroll
+            for (int i = 0; i < JF_ITEMS; i++) {
+                if ((uint32_t)i >= live) break;
+                if (i > 0 || lane > 0) at = gallop_lower_bound(R1, at, rlen1, sat_add64(xs[i], glo));
+                js[i] = at;
+                if (at < rlen1) {
+                    ls[i] = __ldg(R1 + at);
+                    if ((uint64_t)ls[i] <= sat_add64(xs[i], ghi)) okbits |= 1u << i;
                 }
-                x = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
-                need = sat_add64(x, d.lo[seg]);
-                limit = sat_add64(x, d.hi[seg]);
-            }
-            if (single) {  // warp-uniform branch: lane 0 gallops from the tile's first answer, the rest from lane 0's
-                uint32_t j0 = 0;
-                if (lane == 0 && live) j0 = gallop_lower_bound(R, j_first, rlen, need);
-                j0 = __shfl_sync(0xffffffffu, j0, 0);
-                if (live) j = lane == 0 ? j0 : gallop_lower_bound(R, j0, rlen, need);
-            } else if (live) {
-                j = full_lower_bound(R, rlen, need);
-            }
-            if (live && j < rlen) {
-                last = __ldg(R + j);
-                ok = (uint64_t)last <= limit;
             }
         }
-        if (live) d.raw[slot] = ok ? j : NONE32;
-        viable += __popc(__ballot_sync(0xffffffffu, ok));
-    }
-    if (lane == 0 && viable) atomicAdd(&s_count, viable);
-    __syncthreads();
-    if (tid == 0) d.tile_count[tile] = s_count;
-}
-
-// Compaction of the viable slots of a tile; tile_prefix = exclusive scan of tile_count (prefix.cuh).
-__global__ void __launch_bounds__(JF_THREADS) join_compact_kernel(DepthDesc d)
-{
-    __shared__ uint32_t s_cnt[JF_ITEMS * JF_WARPS];  // flags per (round, warp), then their exclusive prefix
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tile = blockIdx.x;
-    const uint32_t slot0 = tile * JF_TILE;
-    const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot0);
-    const uint32_t seg_lo = __ldg(d.tile_seg + tile);
-    const uint32_t seg_hi = slot0 + nslots == d.total_slots ? d.nseg - 1 : __ldg(d.tile_seg + tile + 1);
-    const bool single = __ldg(d.slot_off + seg_lo + 1) >= slot0 + nslots;
-    uint32_t jv[JF_ITEMS], fl[JF_ITEMS];
+    } else {
 #pragma unroll
-    for (int it = 0; it < JF_ITEMS; it++) {
-        const uint32_t slot = slot0 + it * JF_THREADS + tid;
-        jv[it] = slot < slot0 + nslots ? d.raw[slot] : NONE32;
-        fl[it] = __ballot_sync(0xffffffffu, jv[it] != NONE32);
-        if (lane == 0) s_cnt[it * JF_WARPS + warp] = __popc(fl[it]);
+        for (int i = 0; i < JF_ITEMS; i++) {
+            const uint32_t slot = sbase + i;
+            segs[i] = seg_lo;
+            xs[i] = 0;
+            if (slot >= slot0 + nslots) continue;
+            const uint32_t seg = find_segment(d.slot_off, seg_lo, seg_hi, slot);
+            segs[i] = seg;
+            const uint32_t* R;
+            uint32_t rlen;
+            if (d.right_list) {
+                R = d.right_list[seg];
+                rlen = d.right_len[seg];
+            } else {
+                const uint32_t b = __ldg(d.prev_vseg + seg);
+                R = d.prev_vpos + b;
+                rlen = __ldg(d.prev_vseg + seg + 1) - b;
+            }
+            xs[i] = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
+            const uint32_t j = full_lower_bound(R, rlen, sat_add64(xs[i], d.lo[seg]));
+            js[i] = j;
+            if (j < rlen) {
+                ls[i] = __ldg(R + j);
+                if ((uint64_t)ls[i] <= sat_add64(xs[i], d.hi[seg])) okbits |= 1u << i;
+            }
+        }
     }
+
+    // ---- in-tile ranks (order kept), staged records, segment starts
+    const uint32_t mine = __popc(okbits);
+    uint32_t inc = mine;
+#pragma unroll
+    for (int dd = 1; dd < 32; dd <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, dd);
+        if (lane >= (uint32_t)dd) inc += o;
+    }
+    if (lane == 31) s_wsum[warp] = inc;
     __syncthreads();
     if (warp == 0) {
-        constexpr int PER = JF_ITEMS * JF_WARPS / 32;  // counts per lane, consecutive
-        uint32_t c[PER], v = 0;
-#pragma unroll
-        for (int i = 0; i < PER; i++) {
-            c[i] = s_cnt[lane * PER + i];
-            v += c[i];
-        }
-        uint32_t inc = v;
+        const uint32_t w = s_wsum[lane];
+        uint32_t winc = w;
 #pragma unroll
         for (int dd = 1; dd < 32; dd <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, inc, dd);
-            if (lane >= (uint32_t)dd) inc += o;
+            const uint32_t o = __shfl_up_sync(0xffffffffu, winc, dd);
+            if (lane >= (uint32_t)dd) winc += o;
         }
-        uint32_t run = inc - v;
-#pragma unroll
-        for (int i = 0; i < PER; i++) {
-            s_cnt[lane * PER + i] = run;
-            run += c[i];
-        }
+        s_wsum[lane] = winc - w;
+        if (lane == 31) d.tile_count[tile] = winc;
     }
     __syncthreads();
-    const uint32_t prefix = __ldg(d.tile_prefix + tile);
+    uint32_t rank = s_wsum[warp] + inc - mine;  // viable slots of the tile before this thread's first slot
 #pragma unroll
-    for (int it = 0; it < JF_ITEMS; it++) {
-        const uint32_t slot = slot0 + it * JF_THREADS + tid;
+    for (int i = 0; i < JF_ITEMS; i++) {
+        const uint32_t slot = sbase + i;
         if (slot >= slot0 + nslots) break;
-        const uint32_t o = prefix + s_cnt[it * JF_WARPS + warp] + __popc(fl[it] & ((1u << lane) - 1u));
-        uint32_t sg = single ? seg_lo : find_segment(d.slot_off, seg_lo, seg_hi, slot);
-        const uint32_t so = __ldg(d.slot_off + sg);
-        if (jv[it] != NONE32) {
-            const uint32_t j = jv[it];
-            d.vpos[o] = __ldg(d.left[sg] + (slot - so));
-            d.vnxt[o] = j;
-            d.vlast[o] = d.right_list ? __ldg(d.right_list[sg] + j) : __ldg(d.prev_vlast + __ldg(d.prev_vseg + sg) + j);
-        }
-        if (slot == so) {  // segment start; also covers empty segments that start at the same slot
-            for (;;) {
-                d.vseg[sg] = o;
-                if (sg == 0 || __ldg(d.slot_off + sg - 1) != slot) break;
-                sg--;
+        // segment starts: seg_rank[seg] = viable slots of this tile before the segment's first slot; also
+        // covers the empty segments that start at the same slot
+        if ((!single || (i == 0 && tid == 0)) ) {
+            uint32_t sg = segs[i];
+            if (slot == __ldg(d.slot_off + sg)) {
+                for (;;) {
+                    d.seg_rank[sg] = rank;
+                    if (sg == 0 || __ldg(d.slot_off + sg - 1) != slot) break;
+                    sg--;
+                }
             }
         }
-    }
-    if (slot0 + nslots == d.total_slots && tid == 0) {  // last tile: trailing empty segments and the grand total
-        const uint32_t all = __ldg(d.tile_prefix + tile + 1);
-        for (uint32_t sg = d.nseg;; sg--) {
-            d.vseg[sg] = all;
-            if (sg == 0 || __ldg(d.slot_off + sg - 1) != d.total_slots) break;
+        if ((okbits >> i) & 1u) {
+            d.stage_x[slot0 + rank] = xs[i];
+            d.stage_j[slot0 + rank] = js[i];
+            if (d.right_list) d.stage_last[slot0 + rank] = ls[i];  // deeper levels gather the tuple's end later
+            rank++;
         }
-        *d.total_out = all;
     }
+}
+
+// Moves the staged records of every tile to their final place; tile_prefix = exclusive scan of tile_count.
+//   vpos = x, vnxt = index of the partner in the right list, vlast = last position of the completed tuple
+constexpr int JC_THREADS = 256;
+__global__ void __launch_bounds__(JC_THREADS) join_compact_kernel(DepthDesc d)
+{
+    const uint32_t tile = blockIdx.x;
+    const uint32_t slot0 = tile * JF_TILE;
+    const uint32_t base = __ldg(d.tile_prefix + tile);
+    const uint32_t cnt = __ldg(d.tile_prefix + tile + 1) - base;
+    if (d.right_list) {  // depth 1: the partner's position IS the tuple's last position
+        for (uint32_t i = threadIdx.x; i < cnt; i += JC_THREADS) {
+            d.vpos[base + i] = d.stage_x[slot0 + i];
+            d.vnxt[base + i] = d.stage_j[slot0 + i];
+            d.vlast[base + i] = d.stage_last[slot0 + i];
+        }
+    } else {
+        // deeper levels: last position of the partner's tuple; the tile's records belong to the segments
+        // [seg_lo, seg_hi], found per record from the final vseg (join_vseg_kernel runs first)
+        const uint32_t seg_lo = __ldg(d.tile_seg + tile);
+        const uint32_t seg_hi = (uint64_t)slot0 + JF_TILE >= d.total_slots ? d.nseg - 1 : __ldg(d.tile_seg + tile + 1);
+        for (uint32_t i = threadIdx.x; i < cnt; i += JC_THREADS) {
+            const uint32_t o = base + i;
+            const uint32_t j = d.stage_j[slot0 + i];
+            // segment of record o: largest sg with vseg[sg] <= o among the non-empty ones -- vseg is ascending
+            uint32_t lo_s = seg_lo, hi_s = seg_hi;
+            while (lo_s < hi_s) {
+                const uint32_t mid = (lo_s + hi_s + 1) >> 1;
+                if (d.vseg[mid] <= o) lo_s = mid; else hi_s = mid - 1;
+            }
+            d.vpos[o] = d.stage_x[slot0 + i];
+            d.vnxt[o] = j;
+            d.vlast[o] = __ldg(d.prev_vlast + __ldg(d.prev_vseg + lo_s) + j);
+        }
+    }
+}
+
+// vseg[sg] = rank of the segment's first slot in the compacted arrays; vseg[nseg] = *total_out = viable slots
+__global__ void join_vseg_kernel(DepthDesc d, uint32_t ntiles)
+{
+    const uint32_t sg = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sg > d.nseg) return;
+    const uint32_t all = __ldg(d.tile_prefix + ntiles);
+    const uint32_t slot = sg < d.nseg ? __ldg(d.slot_off + sg) : d.total_slots;
+    d.vseg[sg] = slot >= d.total_slots ? all : __ldg(d.tile_prefix + slot / JF_TILE) + d.seg_rank[sg];
+    if (sg == d.nseg) *d.total_out = all;
 }
 
 }  // namespace vlgb

@@ -311,7 +311,7 @@ inline uint64_t query_state_bytes(const BatchView& v, const PlanQuery& pq)
     uint64_t slots = 0;
     for (uint32_t i = 0; i + 1 < pq.k; i++) slots += list_len(v, pq.s0 + i, i == 0);
     uint64_t sel = (list_len(v, pq.s0, true) + SEL_TILE - 1) / SEL_TILE * SEL_TILE;
-    return slots * 28 + sel * 14 + 1024;
+    return slots * 36 + sel * 14 + 1024;
 }
 
 // `qs` sorted by k descending.  Results land in `co`; starts/tuples (if wanted) in the pinned block
@@ -425,7 +425,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     // ---- device memory
     size_t need = ctl.size() + 4096;
     const size_t max_jtiles = (max_slots + JF_TILE - 1) / JF_TILE;
-    need += Arena::padded(max_slots, 4) + 3 * Arena::padded(max_jtiles + 4, 4);  // raw, tile counts / prefix / segments
+    need += 3 * Arena::padded(max_slots, 4) + 3 * Arena::padded(max_jtiles + 4, 4) + Arena::padded(nq + 2, 4);  // staging, tile counts / prefix / segments, seg_rank
     for (uint32_t d = 1; d < kmax; d++)
         need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
     need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
@@ -440,7 +440,10 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     c.join_arena.reserve(need);
     Arena& A = c.join_arena;
     uint8_t* d_ctl = A.take<uint8_t>(ctl.size());
-    uint32_t* raw = A.take<uint32_t>(max_slots);
+    uint32_t* stage_x = A.take<uint32_t>(max_slots);
+    uint32_t* stage_j = A.take<uint32_t>(max_slots);
+    uint32_t* stage_last = A.take<uint32_t>(max_slots);
+    uint32_t* seg_rank = A.take<uint32_t>(nq + 2);
     uint32_t* jtile_count = A.take<uint32_t>(max_jtiles + 4);
     uint32_t* jtile_prefix = A.take<uint32_t>(max_jtiles + 4);
     uint32_t* jtile_seg = A.take<uint32_t>(max_jtiles + 4);
@@ -492,7 +495,10 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         D.prev_vseg = d > 1 ? dh[d - 1].vseg : nullptr;
         D.lo = dev_at<const uint64_t>(d_ctl, h.o_lo);
         D.hi = dev_at<const uint64_t>(d_ctl, h.o_hi);
-        D.raw = raw;
+        D.stage_x = stage_x;
+        D.stage_j = stage_j;
+        D.stage_last = stage_last;
+        D.seg_rank = seg_rank;
         D.tile_count = jtile_count;
         D.tile_prefix = jtile_prefix;
         D.tile_seg = jtile_seg;
@@ -514,11 +520,12 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         c.begin(ST_JOIN_PROBE);
         join_tileseg_kernel<<<(jtiles + 255) / 256, 256, 0, c.stream>>>(D.slot_off, D.nseg, jtiles, jtile_seg);
         join_probe_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
-        c.end(ST_JOIN_PROBE, 2, (uint64_t)T * 8 + right_words * 4);
+        c.end(ST_JOIN_PROBE, 2, (uint64_t)T * 4 + right_words * 4);  // + 12 B per viable slot staged, added below
         c.begin(ST_JOIN_COMPACT);
         const uint32_t l = exclusive_scan(ValueU32{jtile_count}, jtiles, jtile_prefix, scratch, c.stream);
-        join_compact_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
-        c.end(ST_JOIN_COMPACT, l + 1, (uint64_t)T * 4);
+        join_vseg_kernel<<<(D.nseg + 1 + 255) / 256, 256, 0, c.stream>>>(D, jtiles);
+        join_compact_kernel<<<jtiles, JC_THREADS, 0, c.stream>>>(D);
+        c.end(ST_JOIN_COMPACT, l + 2, (uint64_t)jtiles * 12);  // + 24 B per viable slot, added below
     }
 
     // ---- selection
@@ -632,7 +639,10 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: match counts
         c.stats.d2h_bytes += (uint64_t)nq * 8 + (kmax + 1) * 4;
         for (uint32_t d = 1; d < kmax; d++)  // viable slots written; deeper levels read the previous viable list
-            c.stats.bytes[ST_JOIN_COMPACT] += (uint64_t)viable[d] * 20;
+        {
+            c.stats.bytes[ST_JOIN_PROBE] += (uint64_t)viable[d] * 12;
+            c.stats.bytes[ST_JOIN_COMPACT] += (uint64_t)viable[d] * 24 + (d > 1 ? (uint64_t)viable[d] * 4 : 0);
+        }
         for (uint32_t d = 2; d < kmax; d++) c.stats.bytes[ST_JOIN_PROBE] += (uint64_t)viable[d - 1] * 4;
 
         for (uint32_t s = 0; s < nq; s++) {
