@@ -14,7 +14,8 @@
 //   vseg    : vseg[seg] = rank of the segment's first slot, so that every query finds its segment inside the
 //             compacted arrays and no size ever has to travel to the host between depths
 //   compact : vpos / vnxt / vlast [tile prefix + i] = staged x / j / last position of the tuple
-// (A single-pass variant with a decoupled look-back was measured slower: probe times per tile vary widely and
+// (Streaming larger windows through shared memory chunk by chunk was measured slower than galloping in place;
+// a single-pass variant with a decoupled look-back was measured slower too: probe times per tile vary widely and
 // the look-back makes every wave wait for its slowest tile.)
 //
 // Both lists are ascending and x + lo is monotone in x, so a tile of consecutive slots maps to one contiguous
@@ -29,6 +30,20 @@ namespace vlgb {
 
 constexpr int JOIN_THREADS = 256;
 constexpr int MAX_K = 64;  // subpatterns per query (reference grid goes to 32, num_subpatterns.config:1-5)
+
+// Everything a probe CTA needs to know about its tile, in one 64-byte record (join_tileseg_kernel): the CTA
+// starts with two independent loads instead of a chain of five dependent ones.
+struct __align__(16) JoinTile {
+    const uint32_t* left;  // first slot of the tile inside its segment's left list (meaningful if single)
+    const uint32_t* R;     // right list of the segment of the tile's first slot
+    uint32_t rlen;
+    uint32_t j_first;      // lower_bound of the tile's first need in R
+    uint32_t seg;          // segment of the tile's first slot
+    uint32_t single;       // that segment covers the whole tile
+    uint64_t glo, ghi;     // start-to-start bounds of the segment, clamped to 2^33
+    uint64_t pad[2];
+};
+static_assert(sizeof(JoinTile) == 64, "JoinTile is one 64-byte record");
 
 // Per-depth description of the chunk (device arrays, nseg entries unless noted)
 struct DepthDesc {
@@ -52,7 +67,7 @@ struct DepthDesc {
     uint32_t* seg_rank;          // [nseg+1] viable slots of the segment's first tile before the segment's first slot
     uint32_t* tile_count;        // [tiles] viable slots per tile
     const uint32_t* tile_prefix; // [tiles+1] exclusive scan of tile_count
-    const uint32_t* tile_seg;    // [tiles] segment of each tile's first slot (join_tileseg_kernel)
+    JoinTile* tiles;             // [tiles+1] per-tile records (join_tileseg_kernel); the last one is a sentinel
     uint32_t* total_out;         // number of viable slots of the depth
     uint32_t* vpos;              // [total_slots] compacted
     uint32_t* vnxt;
@@ -123,17 +138,51 @@ __device__ __forceinline__ uint32_t warp_lower_bound(const uint32_t* __restrict_
     return b ? min(hi, lo + (uint32_t)__ffs(b) - 1u) : hi;
 }
 
-constexpr int JF_THREADS = 1024;
-constexpr int JF_ITEMS = 4;                          // CONSECUTIVE slots per thread
+constexpr int JF_THREADS = 512;
+constexpr int JF_ITEMS = 8;                          // CONSECUTIVE slots per thread
 constexpr int JF_TILE = JF_THREADS * JF_ITEMS;       // slots per tile
 constexpr int JF_WIN = 8192;                         // right-list window staged in shared memory (elements)
 constexpr int JF_WARPS = JF_THREADS / 32;
 
-// tile_seg[t] = segment that holds slot t * JF_TILE
-__global__ void join_tileseg_kernel(const uint32_t* slot_off, uint32_t nseg, uint32_t ntiles, uint32_t* tile_seg)
+// Per-tile records: segment of the tile's first slot, its lists and bounds, and the lower_bound of that slot's
+// need in the segment's right list -- the tile's window into the right list starts there and ends at the next
+// tile's value when that tile continues the same segment.  One thread per tile, all tiles in flight at once:
+// inside the probe kernel the same search would stall a whole CTA behind a chain of dependent loads.
+__global__ void join_tileseg_kernel(DepthDesc d, uint32_t ntiles)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t < ntiles) tile_seg[t] = find_segment(slot_off, 0, nseg - 1, t * (uint32_t)JF_TILE);
+    if (t > ntiles) return;
+    JoinTile jt;
+    jt.pad[0] = jt.pad[1] = 0;
+    if (t == ntiles) {  // sentinel: "the next tile starts another segment"
+        jt.left = jt.R = nullptr;
+        jt.rlen = jt.j_first = jt.single = 0;
+        jt.seg = d.nseg - 1;
+        jt.glo = jt.ghi = 0;
+        d.tiles[t] = jt;
+        return;
+    }
+    const uint32_t slot = t * (uint32_t)JF_TILE;
+    const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot);
+    const uint32_t seg = find_segment(d.slot_off, 0, d.nseg - 1, slot);
+    const uint32_t so = __ldg(d.slot_off + seg);
+    jt.seg = seg;
+    jt.single = __ldg(d.slot_off + seg + 1) >= slot + nslots;
+    if (d.right_list) {
+        jt.R = d.right_list[seg];
+        jt.rlen = d.right_len[seg];
+    } else {
+        const uint32_t b = __ldg(d.prev_vseg + seg);
+        jt.R = d.prev_vpos + b;
+        jt.rlen = __ldg(d.prev_vseg + seg + 1) - b;
+    }
+    jt.left = d.left[seg] + (slot - so);
+    // positions are < 2^32: bounds clamped to 2^33 compare the same and cannot overflow a 64-bit add
+    const uint64_t cap = 1ull << 33;
+    jt.glo = d.lo[seg] < cap ? d.lo[seg] : cap;
+    jt.ghi = d.hi[seg] < cap ? d.hi[seg] : cap;
+    jt.j_first = full_lower_bound(jt.R, jt.rlen, (uint64_t)__ldg(jt.left) + jt.glo);
+    d.tiles[t] = jt;
 }
 
 // lower_bound in shared memory, galloping from `from` (answers of consecutive slots are a few elements apart)
@@ -164,42 +213,30 @@ __device__ __forceinline__ uint32_t smem_gallop(const uint32_t* w, uint32_t from
 // The viable slots are compacted INSIDE the tile (order kept) into stage_{x,j,last}[tile start + rank]: only
 // viable slots ever reach memory (a sixth of the slots on BASELINE config 2), join_compact_kernel then moves
 // tile_count[tile] records per tile to their final place.
-__global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
+__global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
 {
     __shared__ uint32_t s_win[JF_WIN];
-    __shared__ uint32_t s_j[2];
-    __shared__ uint32_t s_wsum[JF_WARPS];
+    __shared__ uint32_t s_wsum[32];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t tile = blockIdx.x;
     const uint32_t slot0 = tile * JF_TILE;
     const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot0);
-    const uint32_t seg_lo = __ldg(d.tile_seg + tile);  // segment of the tile's first slot (join_tileseg_kernel)
+    const JoinTile jt = d.tiles[tile], jn = d.tiles[tile + 1];  // two independent 64-byte loads
+    const uint32_t seg_lo = jt.seg;  // segment of the tile's first slot
     // upper bound for the segment searches of this tile's slots: the segment of the next tile's first slot
-    const uint32_t seg_hi = slot0 + nslots == d.total_slots ? d.nseg - 1 : __ldg(d.tile_seg + tile + 1);
-    const bool single = __ldg(d.slot_off + seg_lo + 1) >= slot0 + nslots;  // segment seg_lo covers the whole tile
+    const uint32_t seg_hi = jn.seg;
+    const bool single = jt.single;   // segment seg_lo covers the whole tile
 
-    // ---- single-segment tile: bracket the reachable part of the right list
-    const uint32_t* R1 = nullptr;
-    uint32_t rlen1 = 0;
+    // ---- single-segment tile: the reachable part of the right list, R1[j_first, j_first + wlen)
+    const uint32_t* R1 = jt.R;
+    const uint32_t rlen1 = jt.rlen, j_first = jt.j_first;
+    uint32_t wlen = 0;
     if (single) {
-        if (d.right_list) {
-            R1 = d.right_list[seg_lo];
-            rlen1 = d.right_len[seg_lo];
-        } else {
-            const uint32_t vbase1 = __ldg(d.prev_vseg + seg_lo);
-            R1 = d.prev_vpos + vbase1;
-            rlen1 = __ldg(d.prev_vseg + seg_lo + 1) - vbase1;
-        }
-        if (warp < 2) {  // two warps bracket the window in parallel
-            const uint32_t s = warp == 0 ? slot0 : slot0 + nslots - 1;
-            const uint32_t x = __ldg(d.left[seg_lo] + (s - __ldg(d.slot_off + seg_lo)));
-            const uint32_t j = warp_lower_bound(R1, rlen1, sat_add64(x, d.lo[seg_lo]), lane);
-            if (lane == 0) s_j[warp] = j;
-        }
+        // the next tile's first need is >= every need of this tile, if it continues the segment
+        const bool cont = slot0 + nslots < d.total_slots && seg_hi == seg_lo;
+        const uint32_t j_end = cont ? min(rlen1, jn.j_first + 1) : rlen1;
+        wlen = j_end - j_first;
     }
-    __syncthreads();
-    const uint32_t j_first = single ? s_j[0] : 0;
-    const uint32_t wlen = single ? min(rlen1, s_j[1] + 1) - j_first : 0;
     const bool use_win = single && wlen <= (uint32_t)JF_WIN;
     if (use_win) {
         for (uint32_t i = tid; i < wlen; i += JF_THREADS) s_win[i] = __ldg(R1 + j_first + i);
@@ -211,9 +248,8 @@ __global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
     uint32_t xs[JF_ITEMS], js[JF_ITEMS], ls[JF_ITEMS], segs[JF_ITEMS];
     uint32_t okbits = 0;
     if (single) {
-        const uint32_t so = __ldg(d.slot_off + seg_lo);
-        const uint32_t* L = d.left[seg_lo] + (sbase - so);
-        const uint64_t glo = d.lo[seg_lo], ghi = d.hi[seg_lo];
+        const uint32_t* L = jt.left + tid * JF_ITEMS;
+        const uint64_t glo = jt.glo, ghi = jt.ghi;
         const uint32_t live = sbase < slot0 + nslots ? min((uint32_t)JF_ITEMS, slot0 + nslots - sbase) : 0u;
 #pragma unroll
         for (int i = 0; i < JF_ITEMS; i++) {
@@ -225,7 +261,7 @@ __global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
 #pragma unroll
             for (int i = 0; i < JF_ITEMS; i++) {
                 if ((uint32_t)i >= live) break;
-                const uint64_t need = sat_add64(xs[i], glo);
+                const uint64_t need = xs[i] + glo;
                 if (i == 0) {
                     uint32_t lo = 0, hi = wlen;
                     while (lo < hi) {
@@ -239,23 +275,23 @@ __global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
                 js[i] = j_first + at;
                 if (at < wlen) {
                     ls[i] = s_win[at];
-                    if ((uint64_t)ls[i] <= sat_add64(xs[i], ghi)) okbits |= 1u << i;
+                    if ((uint64_t)ls[i] <= xs[i] + ghi) okbits |= 1u << i;
                 }
             }
         } else {
             // warp-uniform branch: lane 0 gallops from the tile's first answer, the rest from lane 0's
             uint32_t j0 = 0;
-            if (lane == 0 && live) j0 = gallop_lower_bound(R1, j_first, rlen1, sat_add64(xs[0], glo));
+            if (lane == 0 && live) j0 = gallop_lower_bound(R1, j_first, rlen1, xs[0] + glo);
             j0 = __shfl_sync(0xffffffffu, j0, 0);
             uint32_t at = j0;
 #pragma unroll
             for (int i = 0; i < JF_ITEMS; i++) {
                 if ((uint32_t)i >= live) break;
-                if (i > 0 || lane > 0) at = gallop_lower_bound(R1, at, rlen1, sat_add64(xs[i], glo));
+                if (i > 0 || lane > 0) at = gallop_lower_bound(R1, at, rlen1, xs[i] + glo);
                 js[i] = at;
                 if (at < rlen1) {
                     ls[i] = __ldg(R1 + at);
-                    if ((uint64_t)ls[i] <= sat_add64(xs[i], ghi)) okbits |= 1u << i;
+                    if ((uint64_t)ls[i] <= xs[i] + ghi) okbits |= 1u << i;
                 }
             }
         }
@@ -299,7 +335,7 @@ __global__ void __launch_bounds__(JF_THREADS) join_probe_kernel(DepthDesc d)
     if (lane == 31) s_wsum[warp] = inc;
     __syncthreads();
     if (warp == 0) {
-        const uint32_t w = s_wsum[lane];
+        const uint32_t w = lane < (uint32_t)JF_WARPS ? s_wsum[lane] : 0u;
         uint32_t winc = w;
 #pragma unroll
         for (int dd = 1; dd < 32; dd <<= 1) {
@@ -354,8 +390,7 @@ __global__ void __launch_bounds__(JC_THREADS) join_compact_kernel(DepthDesc d)
     } else {
         // deeper levels: last position of the partner's tuple; the tile's records belong to the segments
         // [seg_lo, seg_hi], found per record from the final vseg (join_vseg_kernel runs first)
-        const uint32_t seg_lo = __ldg(d.tile_seg + tile);
-        const uint32_t seg_hi = (uint64_t)slot0 + JF_TILE >= d.total_slots ? d.nseg - 1 : __ldg(d.tile_seg + tile + 1);
+        const uint32_t seg_lo = d.tiles[tile].seg, seg_hi = d.tiles[tile + 1].seg;
         for (uint32_t i = threadIdx.x; i < cnt; i += JC_THREADS) {
             const uint32_t o = base + i;
             const uint32_t j = d.stage_j[slot0 + i];

@@ -425,7 +425,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     // ---- device memory
     size_t need = ctl.size() + 4096;
     const size_t max_jtiles = (max_slots + JF_TILE - 1) / JF_TILE;
-    need += 3 * Arena::padded(max_slots, 4) + 3 * Arena::padded(max_jtiles + 4, 4) + Arena::padded(nq + 2, 4);  // staging, tile counts / prefix / segments, seg_rank
+    need += 3 * Arena::padded(max_slots, 4) + 2 * Arena::padded(max_jtiles + 4, 4) + Arena::padded(max_jtiles + 2, sizeof(JoinTile)) + Arena::padded(nq + 2, 4);  // staging, tile counts / prefix / segments, seg_rank
     for (uint32_t d = 1; d < kmax; d++)
         need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
     need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
@@ -446,7 +446,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     uint32_t* seg_rank = A.take<uint32_t>(nq + 2);
     uint32_t* jtile_count = A.take<uint32_t>(max_jtiles + 4);
     uint32_t* jtile_prefix = A.take<uint32_t>(max_jtiles + 4);
-    uint32_t* jtile_seg = A.take<uint32_t>(max_jtiles + 4);
+    JoinTile* jtile_rec = A.take<JoinTile>(max_jtiles + 2);
     for (uint32_t d = 1; d < kmax; d++) {
         size_t t = dh[d].slot_off[dh[d].nseg];
         dh[d].vpos = A.take<uint32_t>(t);
@@ -501,7 +501,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         D.seg_rank = seg_rank;
         D.tile_count = jtile_count;
         D.tile_prefix = jtile_prefix;
-        D.tile_seg = jtile_seg;
+        D.tiles = jtile_rec;
         D.total_out = d_viable + d;
         D.vpos = h.vpos;
         D.vnxt = h.vnxt;
@@ -518,7 +518,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         if (d == 1)
             for (uint32_t s = 0; s < h.nseg; s++) right_words += h.right_len[s];
         c.begin(ST_JOIN_PROBE);
-        join_tileseg_kernel<<<(jtiles + 255) / 256, 256, 0, c.stream>>>(D.slot_off, D.nseg, jtiles, jtile_seg);
+        join_tileseg_kernel<<<(jtiles + 1 + 127) / 128, 128, 0, c.stream>>>(D, jtiles);
         join_probe_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
         c.end(ST_JOIN_PROBE, 2, (uint64_t)T * 4 + right_words * 4);  // + 12 B per viable slot staged, added below
         c.begin(ST_JOIN_COMPACT);
