@@ -243,13 +243,12 @@ def main():
         r.free()
 
     def step_e2e():
-        parsed = [capi.parse_query(s, capi.SYNTAX_BENCHMARK) for s in query_strings]
-        b = capi.PackedBatch(parsed)
+        b = capi.ParsedBatch(query_strings, capi.SYNTAX_BENCHMARK)  # host strings -> CSR batch, one ABI call
         r, gcounts, _ = searcher.search(b, capi.WANT_STARTS)
         st = capi.last_stats()
         state["e2e_h2d"], state["e2e_d2h"] = st["h2d_bytes"], st["d2h_bytes"]
         csum = 0
-        for q in (0, len(parsed) - 1):
+        for q in (0, len(b) - 1):
             s = r.starts(q)
             csum += int(s[:1].sum())
         state["e2e_matches"] = int(gcounts.sum())

@@ -79,6 +79,12 @@ typedef struct {
  * Returns VLGB_OK or VLGB_ERR_LAZY / _MINMAX / _NUMBER (same conditions, same order of checks as the
  * reference parser).  Empty subpatterns parse fine and are fenced at search time. */
 int vlgb_parse_query(const char* str, size_t len, int syntax, vlgb_batch** out);
+/* Parse n query strings into ONE batch (query i of the batch = strs[i]) with a single call: what the loop over
+ * the pattern file in gm_search.cpp:84-104 does one string at a time.  status (nullable, n entries) receives the
+ * per-query parse code; a query that fails to parse becomes an empty query (0 subpatterns, no matches).  Without
+ * a status array the first parse error fails the whole call. */
+int vlgb_parse_batch(const char* const* strs, const size_t* lens, uint32_t n, int syntax, int32_t* status,
+                     vlgb_batch** out);
 void vlgb_batch_free(vlgb_batch* b);
 
 /* ---- index  (replaces construct(vlg_index&, file, cfg, num_bytes), vlg_index.hpp:375-392; the

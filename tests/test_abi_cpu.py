@@ -72,3 +72,36 @@ def test_zero_symbol_rejected_before_any_device_work():
     with pytest.raises(capi.VlgbError) as e:
         capi.Index.build(b"abc\0def")
     assert e.value.code == capi.ERR_ZERO_SYMBOL  # construct.hpp:35-45
+
+
+def test_parse_batch_equals_per_query_parse():
+    """vlgb_parse_batch = the per-string parser applied to every string, in one call, same codes."""
+    qs = [b"ab.{1,2}cd", b"x", b"a.{0,10}b.{5,7}c", b"a.{3,2}b", b"q.{7,9}"]
+    pb = capi.ParsedBatch(qs, capi.SYNTAX_BENCHMARK, strict=False)
+    assert len(pb) == len(qs)
+    assert pb.status[3] == capi.ERR_MINMAX if hasattr(capi, "ERR_MINMAX") else pb.status[3] == -4
+    assert pb.k[3] == 0
+    for i, q in enumerate(qs):
+        if i == 3:
+            continue
+        subs, gaps = capi.parse_query(q, capi.SYNTAX_BENCHMARK)
+        assert pb.status[i] == 0 and pb.k[i] == len(subs)
+    # the arrays agree with the Python-side packer
+    good = [q for i, q in enumerate(qs) if i != 3]
+    pb2 = capi.ParsedBatch(good, capi.SYNTAX_BENCHMARK)
+    ref = capi.PackedBatch([capi.parse_query(q, capi.SYNTAX_BENCHMARK) for q in good])
+    import ctypes as C
+    import numpy as np
+    n_sub = int(ref.sub_off[-1])
+    so = np.ctypeslib.as_array(C.cast(pb2.c.sub_off, C.POINTER(C.c_uint32)), shape=(len(good) + 1,))
+    po = np.ctypeslib.as_array(C.cast(pb2.c.pat_off, C.POINTER(C.c_uint64)), shape=(n_sub + 1,))
+    gmin = np.ctypeslib.as_array(C.cast(pb2.c.gap_min, C.POINTER(C.c_uint64)), shape=(n_sub,))
+    gmax = np.ctypeslib.as_array(C.cast(pb2.c.gap_max, C.POINTER(C.c_uint64)), shape=(n_sub,))
+    by = np.ctypeslib.as_array(C.cast(pb2.c.pat_bytes, C.POINTER(C.c_uint8)), shape=(int(po[-1]),))
+    assert (so == ref.sub_off).all() and (po == ref.pat_off).all() and (by == ref.blob[: len(by)]).all()
+    # gaps after a query's last subpattern are ignored by the library; compare the meaningful ones
+    for q in range(len(good)):
+        for s_ in range(int(so[q]), int(so[q + 1]) - 1):
+            assert gmin[s_] == ref.gmin[s_] and gmax[s_] == ref.gmax[s_]
+    with pytest.raises(capi.VlgbError):
+        capi.ParsedBatch(qs, capi.SYNTAX_BENCHMARK)  # strict: the bad query fails the call

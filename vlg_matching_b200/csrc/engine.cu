@@ -161,6 +161,37 @@ extern "C" int vlgb_parse_query(const char* str, size_t len, int syntax, vlgb_ba
     return VLGB_OK;
 }
 
+extern "C" int vlgb_parse_batch(const char* const* strs, const size_t* lens, uint32_t n, int syntax, int32_t* status,
+                                vlgb_batch** out)
+{
+    if ((!strs && n) || (!lens && n) || !out) return fail(VLGB_ERR_ARG, "vlgb_parse_batch: null argument");
+    if (syntax != VLGB_SYNTAX_LIBRARY && syntax != VLGB_SYNTAX_BENCHMARK)
+        return fail(VLGB_ERR_ARG, "vlgb_parse_batch: unknown syntax %d", syntax);
+    *out = nullptr;
+    OwnedBatch* b = new (std::nothrow) OwnedBatch();
+    if (!b) return fail(VLGB_ERR_NOMEM, "out of memory");
+    int first_err = VLGB_OK;
+    for (uint32_t i = 0; i < n; i++) {
+        ParsedQuery q;
+        int rc = strs[i] ? parse_query(strs[i], lens[i], syntax, q) : VLGB_ERR_ARG;
+        if (status) status[i] = rc;
+        if (rc != VLGB_OK) {
+            if (first_err == VLGB_OK) first_err = rc;
+            q = ParsedQuery();  // keeps the numbering: an empty query (0 subpatterns) stands in
+        }
+        b->add(q);
+    }
+    b->seal();
+    if (first_err != VLGB_OK && !status) {  // nobody to tell which query failed: fail the call like vlgb_parse_query
+        delete b;
+        if (first_err == VLGB_ERR_LAZY) return fail(first_err, "invalid gap description: expected '?' (lazy semantics)");
+        if (first_err == VLGB_ERR_MINMAX) return fail(first_err, "invalid gap description: min-gap > max-gap");
+        return fail(first_err, "invalid gap description: not a number");
+    }
+    *out = &b->pub;
+    return VLGB_OK;
+}
+
 extern "C" void vlgb_batch_free(vlgb_batch* b)
 {
     if (b) delete reinterpret_cast<OwnedBatch*>(b);  // pub is the first member
