@@ -6,6 +6,8 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -232,5 +234,35 @@ __host__ __device__ inline uint64_t sat_shl64(uint64_t a, uint32_t sh)
 }
 
 constexpr uint32_t NONE32 = 0xFFFFFFFFu;
+
+// Host wall-clock trace of one search call (VLGB_TRACE=1 in the environment; stderr).  Measurement only.
+struct HostTrace {
+    bool on;
+    double t0, last;
+    static double now()
+    {
+        timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+    }
+    HostTrace()
+    {
+        static const bool env = getenv("VLGB_TRACE") != nullptr;
+        on = env;
+        t0 = last = on ? now() : 0;
+    }
+    void mark(const char* what)
+    {
+        if (!on) return;
+        const double t = now();
+        fprintf(stderr, "[vlgb trace] %-28s +%.3f ms (at %.3f)\n", what, t - last, t - t0);
+        last = t;
+    }
+};
+inline HostTrace& trace()
+{
+    static thread_local HostTrace t;
+    return t;
+}
 
 }  // namespace vlgb

@@ -451,6 +451,7 @@ int batch_check(const vlgb_batch* b)
 void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const uint64_t* entry_cursor, uint32_t want,
                ResultImpl& R)
 {
+    trace() = HostTrace();
     const uint32_t nq = batch->n_queries;
     const uint32_t ns = nq ? batch->sub_off[nq] : 0;
     R.nq = nq;
@@ -509,9 +510,11 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
 
     // ---- scan: one sorted occurrence list per distinct subpattern
     ScanOut so;
+    trace().mark("plan + dictionary");
     run_scan(c, idx->d_text, idx->n, idx->owned_len, idx->sym_shift, dict, so);
     BatchView view{batch, &sub_pid, &so, idx->global_offset, idx->sym_shift};
 
+    trace().mark("scan done");
     // queries with an empty list have no match (vlg_index.hpp:316)
     std::vector<PlanQuery> live;
     for (const PlanQuery& pq : plan) {
@@ -577,6 +580,7 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
         i0 = i1;
     }
     c.stats.segments = 1;
+    trace().mark("search done");
 }
 
 }  // namespace

@@ -141,6 +141,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         }
         work_bytes += stream_passes * (Arena::padded((size_t)rows * stream_cap, 4) + Arena::padded(rows, 4)) + Arena::padded(npass, 4);
     }
+    trace().mark("scan: tables built");
     c.scan_arena.reserve(ctl.size() + work_bytes + 4096);
     uint8_t* d_ctl = c.scan_arena.take<uint8_t>(ctl.size());
     VLGB_CUDA(cudaMemcpyAsync(d_ctl, ctl.host.data(), ctl.host.size(), cudaMemcpyHostToDevice, c.stream));
@@ -209,7 +210,9 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     }
     VLGB_CUDA(cudaMemcpyAsync(overflow.data(), d_overflow, (size_t)npass * 4, cudaMemcpyDeviceToHost, c.stream));
     VLGB_CUDA(cudaGetLastError());
+    trace().mark("scan: pass 1 launched");
     VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync 1: list sizes
+    trace().mark("scan: sync 1");
 
     uint64_t words = 0;
     for (uint32_t i = 0; i < P; i++) {
@@ -254,6 +257,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         }
         c.end(ST_SCAN_FILL, launches, bytes);
     }
+    trace().mark("scan: pass 2 launched");
     c.stats.scan_passes += npass;
     c.stats.distinct_patterns += P;
 
@@ -422,6 +426,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     std::vector<uint64_t> zeros64(nq, 0);
     const size_t o_tuple_off = ctl.put(zeros64);
 
+    trace().mark("chunk: host layout");
     // ---- device memory
     size_t need = ctl.size() + 4096;
     const size_t max_jtiles = (max_slots + JF_TILE - 1) / JF_TILE;
@@ -584,7 +589,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         c.end(ST_SELECT_SUCC, 1, (uint64_t)nq * 32);
         VLGB_CUDA(cudaMemcpyAsync(v0_len.data(), d_v0_len, (size_t)nq * 4, cudaMemcpyDeviceToHost, c.stream));
         VLGB_CUDA(cudaGetLastError());
+        trace().mark("chunk: join launched");
         VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: viable-start counts
+        trace().mark("chunk: sync viable");
         c.stats.d2h_bytes += (uint64_t)nq * 4;
     }
     sel_run = 0;
@@ -636,7 +643,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         if (kmax > 1)
             VLGB_CUDA(cudaMemcpyAsync(viable.data(), d_viable, (size_t)(kmax + 1) * 4, cudaMemcpyDeviceToHost, c.stream));
         VLGB_CUDA(cudaGetLastError());
+        trace().mark("chunk: select launched");
         VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: match counts
+        trace().mark("chunk: sync counts");
         c.stats.d2h_bytes += (uint64_t)nq * 8 + (kmax + 1) * 4;
         for (uint32_t d = 1; d < kmax; d++)  // viable slots written; deeper levels read the previous viable list
         {
@@ -694,6 +703,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             }
             VLGB_CUDA(cudaGetLastError());
             VLGB_CUDA(cudaStreamSynchronize(c.stream));
+            trace().mark("chunk: emit + copies done");
         }
     }
 }
