@@ -174,6 +174,10 @@ def main():
     if args.impl == "reference":
         return run_reference_arm(args)
 
+    # stdout carries exactly ONE line (the JSON): anything libraries print there (NCCL's version banner) goes to stderr
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     from vlg_matching_b200 import capi, synth
@@ -324,7 +328,8 @@ def main():
             line["cpu_baseline"] = {"value": r["gbps"], "unit": "GB/s", "cores": threads, "kind": r["kind"],
                                     "sample": f"first {r['n'] >> 20} MiB of the text, all {NQ} queries, {threads} threads, 1 pass",
                                     **r["info"]}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -158,7 +158,8 @@ def test_library_and_benchmark_surfaces(V, tmp_path):
     assert other.search("a.{0,10}a").tolist() == [0, 5, 10]
 
 
-def test_entry_cursor_and_sharded_equivalence(V):
+@pytest.mark.parametrize("path", ["device_state", "search_again"])
+def test_entry_cursor_and_sharded_equivalence(V, path):
     """Text cut into overlapping shards (owned part + halo >= max span): per-shard results, chained
     through exit cursors with vlgb_result_fixup, equal the single-shard result."""
     from vlg_matching_b200 import capi, synth
@@ -181,6 +182,8 @@ def test_entry_cursor_and_sharded_equivalence(V):
         end = min(n, hi + span)
         shard = V.Index.build(text[lo:end], global_offset=lo, owned_len=hi - lo, total_len=n)
         r = shard.search(b, capi.WANT_TUPLES)          # speculative: entry cursor 0
+        if path == "search_again":                     # another search in between: the kept selection state is gone
+            shard.search(V.PackedBatch(queries[:1]), capi.WANT_COUNT).free()
         changed += r.fixup(cursor)                     # true cursors from the left neighbour
         cursor = r.exit_cursors()
         for q in range(len(queries)):
@@ -192,6 +195,32 @@ def test_entry_cursor_and_sharded_equivalence(V):
         got = np.concatenate(parts[q], axis=0)
         assert np.array_equal(got, rw.tuples(q)), (q, queries[q])
     assert changed > 0  # the single-byte queries straddle every boundary
+
+
+def test_repeated_reentry_equals_fresh_search(V):
+    """vlgb_result_fixup applied again and again to ONE result (cursors moving right and left) always equals a
+    fresh search entered at those cursors: the re-entry works on the selection state kept on the device."""
+    from vlg_matching_b200 import capi, synth
+    text = synth.make_text(2, 1 << 19)
+    queries = synth.make_queries(2, text, 80) + synth.sample_queries(text, 40, 3, (1, 3), [(0, 40), (50, 400)], 7, False)
+    queries += [([b"e"], []), ([b"th"], []), ([b"zzzzqq"], []), ([b"e", b"zzzzqq"], [(0, 50)])]
+    idx = V.Index.build(text)
+    b = V.PackedBatch(queries)
+    rng = np.random.default_rng(5)
+    cursors = [rng.integers(0, text.size, len(queries)).astype(np.uint64) for _ in range(4)]
+    cursors.insert(2, np.zeros(len(queries), dtype=np.uint64))                 # back to the beginning
+    cursors.append(np.full(len(queries), text.size + 5, dtype=np.uint64))      # beyond the text: nothing left
+    fresh = []
+    for e in cursors:
+        rf = idx.search(b, capi.WANT_TUPLES, entry_cursor=e)
+        fresh.append(([rf.tuples(q).copy() for q in range(len(queries))], rf.exit_cursors().copy(), rf.counts().copy()))
+    r = idx.search(b, capi.WANT_TUPLES)
+    for e, (tup, ext, cnt) in zip(cursors, fresh):
+        r.fixup(e)
+        assert np.array_equal(r.counts(), cnt)
+        assert np.array_equal(r.exit_cursors(), ext)
+        for q in range(len(queries)):
+            assert np.array_equal(r.tuples(q), tup[q]), (q, queries[q])
 
 
 def test_full_size_properties_config2(V):

@@ -169,6 +169,7 @@ struct Context {
     vlgb_stats stats;
     uint64_t stream_budget = 0;  // 0 = default (a third of the free memory, <= 24 GiB); tiny = no hit stream
     uint64_t join_budget = 0;    // 0 = default
+    uint64_t serial = 0;         // searches run on this thread (validity of the state kept for vlgb_result_fixup)
 
     void begin(uint32_t stage)
     {

@@ -410,6 +410,7 @@ struct vlgb_result_ext {  // what vlgb_result_fixup needs to re-enter the shard
     const vlgb_index* idx = nullptr;
     OwnedBatch batch;
     std::vector<uint64_t> entry, first_start;
+    uint64_t serial = 0;  // Context::serial of the search that produced the result
 };
 
 
@@ -577,8 +578,11 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
         }
         R.total += co.matches;
         c.stats.query_chunks++;
+        if (!(i0 == 0 && i1 == live.size())) retained().valid = false;  // only a single-chunk search stays re-enterable
         i0 = i1;
     }
+    retained().serial = c.serial;
+    R.ext.serial = c.serial;
     c.stats.segments = 1;
     trace().mark("search done");
 }
@@ -598,6 +602,8 @@ extern "C" int vlgb_search_batch(const vlgb_index* idx, const vlgb_batch* batch,
         Context& c = ctx();
         c.flush_timers();
         memset(&c.stats, 0, sizeof c.stats);
+        c.serial++;
+        retained().valid = false;
         std::unique_ptr<ResultImpl> R(new ResultImpl());
         try {
             do_search(c, idx, batch, entry_cursor, want, *R);
@@ -658,6 +664,64 @@ extern "C" int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, u
         redo.push_back(q);
     }
     if (redo.empty()) return VLGB_OK;
+    try {
+        Context& c = ctx();
+        Retained& T = retained();
+        if (c.ready && T.valid && T.serial == R.ext.serial && c.serial == R.ext.serial) {
+            // fast path: the selection state of the search is still on the device (sel_refix_kernel)
+            std::vector<int32_t> chunk_of(R.nq, -1);
+            for (size_t s = 0; s < T.qs.size(); s++) chunk_of[T.qs[s].q] = (int32_t)s;
+            std::vector<std::pair<uint32_t, uint32_t>> order;  // (chunk index, batch index)
+            for (uint32_t q : redo) {
+                if (chunk_of[q] < 0) {  // a query without a viable start: nothing to report under any cursor
+                    R.exit_cursor[q] = entry_cursor[q];
+                    R.ext.entry[q] = entry_cursor[q];
+                } else {
+                    order.emplace_back((uint32_t)chunk_of[q], q);
+                }
+            }
+            std::sort(order.begin(), order.end());
+            if (!order.empty()) {
+                std::vector<uint32_t> rs(order.size());
+                std::vector<uint64_t> re(order.size());
+                for (size_t i = 0; i < order.size(); i++) {
+                    rs[i] = order[i].first;
+                    re[i] = entry_cursor[order[i].second];
+                }
+                vlgb_stats keep = c.stats;
+                RefixOut ro;
+                run_refix(c, T, rs, re, R.want & 3u, (R.want & VLGB_KEEP_ON_DEVICE) != 0,
+                          [&](size_t nbytes) {
+                              HostBlock hb = pinned_pool().take(nbytes ? nbytes : 8);
+                              R.blocks.push_back(hb);
+                              return hb.p;
+                          },
+                          ro);
+                c.flush_timers();
+                c.stats = keep;
+                uint64_t m = 0;
+                const bool host_lists = !(R.want & VLGB_KEEP_ON_DEVICE);
+                for (size_t i = 0; i < order.size(); i++) {
+                    const uint32_t q = order[i].second;
+                    R.total = R.total - R.counts[q] + ro.counts[i];
+                    R.counts[q] = ro.counts[i];
+                    R.exit_cursor[q] = ro.counts[i] ? ro.exit_cursor[i] : entry_cursor[q];
+                    R.ext.first_start[q] = ro.counts[i] ? ro.first_start[i] : ~uint64_t(0);
+                    R.ext.entry[q] = entry_cursor[q];
+                    if (host_lists && (R.want & 3u) >= VLGB_WANT_STARTS) R.starts[q] = ro.counts[i] && ro.h_starts ? ro.h_starts + m : EMPTY_LIST;
+                    if (host_lists && (R.want & 3u) >= VLGB_WANT_TUPLES)
+                        R.tuples[q] = ro.counts[i] && ro.h_tuples ? ro.h_tuples + ro.tuple_off[i] : EMPTY_LIST;
+                    m += ro.counts[i];
+                }
+            }
+            if (n_changed) *n_changed = (uint32_t)redo.size();
+            return VLGB_OK;
+        }
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    } catch (const std::bad_alloc&) {
+        return fail(VLGB_ERR_NOMEM, "out of host memory");
+    }
     OwnedBatch sub;
     std::vector<uint64_t> sub_entry;
     const vlgb_batch& B = R.ext.batch.pub;

@@ -318,6 +318,28 @@ inline uint64_t query_state_bytes(const BatchView& v, const PlanQuery& pq)
     return slots * 36 + sel * 14 + 1024;
 }
 
+// Selection state of the last search of this thread, kept for vlgb_result_fixup (valid while no other search
+// has run on the thread and the batch fitted one chunk): the join arena is left untouched, so succ[] and the
+// flag bits of every query are still on the device.
+struct Retained {
+    bool valid = false;
+    uint64_t serial = 0;
+    SelDesc S;
+    uint32_t nq = 0, ntiles = 0;
+    std::vector<PlanQuery> qs;
+    uint32_t* d_tile_count = nullptr;
+    uint32_t* d_tile_prefix = nullptr;
+    uint32_t* scratch = nullptr;
+    uint64_t* d_counts = nullptr;
+    uint64_t* d_tuple_off = nullptr;
+    DeviceBuffer fix_buf, fix_out;
+};
+inline Retained& retained()
+{
+    static thread_local Retained r;
+    return r;
+}
+
 // `qs` sorted by k descending.  Results land in `co`; starts/tuples (if wanted) in the pinned block
 // `hb` (grown by the caller-supplied allocator).
 template <class PinnedAlloc>
@@ -326,6 +348,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
 {
     const uint32_t nq = (uint32_t)qs.size();
     const uint32_t kmax = qs[0].k;
+    retained().valid = false;
     const vlgb_batch& B = *v.b;
     const ScanOut& so = *v.so;
     auto list_ptr = [&](uint32_t sub) { return (const uint32_t*)(so.d_lists + so.base[(*v.sub_pid)[sub]]); };
@@ -705,6 +728,131 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             VLGB_CUDA(cudaStreamSynchronize(c.stream));
             trace().mark("chunk: emit + copies done");
         }
+        Retained& T = retained();
+        T.S = S;
+        T.nq = nq;
+        T.ntiles = ntiles;
+        T.qs = qs;
+        T.d_tile_count = d_tile_count;
+        T.d_tile_prefix = d_tile_prefix;
+        T.scratch = scratch;
+        T.d_counts = d_counts;
+        T.d_tuple_off = dev_at<uint64_t>(d_ctl, o_tuple_off);
+        T.valid = true;
+    }
+}
+
+// Re-entry of some queries of the retained chunk with new cursors (sel_refix_kernel).  `redo` holds
+// chunk-local query indices in ascending order, `entry` their new whole-text cursors.  Outputs per redo query.
+struct RefixOut {
+    std::vector<uint64_t> counts, exit_cursor, first_start, tuple_off;
+    uint64_t matches = 0, tuple_words = 0;
+    uint64_t* h_starts = nullptr;
+    uint64_t* h_tuples = nullptr;
+};
+
+template <class PinnedAlloc>
+inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo, const std::vector<uint64_t>& entry,
+                      uint32_t want, bool keep_device, PinnedAlloc&& pinned_alloc, RefixOut& ro)
+{
+    const uint32_t nr = (uint32_t)redo.size(), nq = T.nq;
+    SelDesc S = T.S;
+    std::vector<uint64_t> entry_local(nr);
+    for (uint32_t i = 0; i < nr; i++) {
+        const uint64_t eb = sat_shl64(entry[i], S.sym_shift);
+        entry_local[i] = eb > S.global_offset ? eb - S.global_offset : 0;
+    }
+    // device scratch: redo list | cursors | flags | exit / first (nq each)
+    const size_t o_q = 0, o_e = Arena::padded(nr, 4), o_flag = o_e + Arena::padded(nr, 8), o_exit = o_flag + Arena::padded(nq, 4),
+                 o_first = o_exit + Arena::padded(nq, 8), total = o_first + Arena::padded(nq, 8);
+    uint8_t* fb = (uint8_t*)T.fix_buf.get(total);
+    VLGB_CUDA(cudaMemcpyAsync(fb + o_q, redo.data(), (size_t)nr * 4, cudaMemcpyHostToDevice, c.stream));
+    VLGB_CUDA(cudaMemcpyAsync(fb + o_e, entry_local.data(), (size_t)nr * 8, cudaMemcpyHostToDevice, c.stream));
+    VLGB_CUDA(cudaMemsetAsync(fb + o_flag, 0, (size_t)nq * 4, c.stream));
+    VLGB_CUDA(cudaMemsetAsync(fb + o_first, 0xFF, (size_t)nq * 8, c.stream));
+    c.stats.h2d_bytes += (uint64_t)nr * 12;
+    RefixDesc rd;
+    rd.n = nr;
+    rd.q = (const uint32_t*)(fb + o_q);
+    rd.entry_local = (const uint64_t*)(fb + o_e);
+    rd.redo_flag = (uint32_t*)(fb + o_flag);
+    S.exit_cursor = (uint64_t*)(fb + o_exit);
+    S.first_start = (uint64_t*)(fb + o_first);
+    S.starts = nullptr;
+    S.tuples = nullptr;
+    c.begin(ST_SELECT_WALK);
+    sel_refix_kernel<<<(nr + 63) / 64, 64, 0, c.stream>>>(S, rd);
+    sel_recount_kernel<<<(T.ntiles * 32 + 255) / 256, 256, 0, c.stream>>>(S, rd.redo_flag);
+    c.end(ST_SELECT_WALK, 2, (uint64_t)T.ntiles * 136);
+    c.begin(ST_EMIT);
+    uint32_t l = exclusive_scan(ValueU32{T.d_tile_count}, T.ntiles, T.d_tile_prefix, T.scratch, c.stream);
+    sel_counts_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
+    c.end(ST_EMIT, l + 1, (uint64_t)T.ntiles * 12);
+    std::vector<uint64_t> all_counts(nq, 0);
+    VLGB_CUDA(cudaMemcpyAsync(all_counts.data(), T.d_counts, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+    VLGB_CUDA(cudaGetLastError());
+    VLGB_CUDA(cudaStreamSynchronize(c.stream));
+    c.stats.d2h_bytes += (uint64_t)nq * 8;
+
+    ro.counts.assign(nr, 0);
+    ro.exit_cursor.assign(nr, 0);
+    ro.first_start.assign(nr, ~uint64_t(0));
+    ro.tuple_off.assign(nr, 0);
+    ro.matches = ro.tuple_words = 0;
+    std::vector<uint64_t> tuple_off_all(nq, 0);
+    for (uint32_t i = 0; i < nr; i++) {
+        ro.counts[i] = all_counts[redo[i]];
+        ro.tuple_off[i] = ro.tuple_words;
+        tuple_off_all[redo[i]] = ro.tuple_words;
+        ro.matches += ro.counts[i];
+        ro.tuple_words += ro.counts[i] * T.qs[redo[i]].k;
+    }
+    if (!ro.matches) return;
+    const bool want_starts = (want & 3u) >= VLGB_WANT_STARTS, want_tuples = (want & 3u) >= VLGB_WANT_TUPLES;
+    size_t ob = 256;
+    if (want_starts) ob += Arena::padded(ro.matches, 8);
+    if (want_tuples) ob += Arena::padded(ro.tuple_words, 8);
+    uint8_t* o = (uint8_t*)T.fix_out.get(ob);
+    uint64_t *d_starts = nullptr, *d_tuples = nullptr;
+    if (want_starts) {
+        d_starts = (uint64_t*)o;
+        o += Arena::padded(ro.matches, 8);
+    }
+    if (want_tuples) {
+        d_tuples = (uint64_t*)o;
+        VLGB_CUDA(cudaMemcpyAsync(T.d_tuple_off, tuple_off_all.data(), (size_t)nq * 8, cudaMemcpyHostToDevice, c.stream));
+        c.stats.h2d_bytes += (uint64_t)nq * 8;
+    }
+    S.starts = d_starts;
+    S.tuples = d_tuples;
+    c.begin(ST_EMIT);
+    sel_emit_kernel<<<T.ntiles, SEL_TILE, 0, c.stream>>>(S);
+    c.end(ST_EMIT, 1, ro.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? ro.tuple_words * 12 : 0));
+    std::vector<uint64_t> ex(nq), fs(nq);
+    VLGB_CUDA(cudaMemcpyAsync(ex.data(), S.exit_cursor, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+    VLGB_CUDA(cudaMemcpyAsync(fs.data(), S.first_start, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+    c.stats.d2h_bytes += (uint64_t)nq * 16;
+    if (!keep_device && (want_starts || want_tuples)) {
+        size_t hb = (want_starts ? ro.matches * 8 : 0) + (want_tuples ? ro.tuple_words * 8 : 0);
+        uint8_t* h = (uint8_t*)pinned_alloc(hb);
+        if (want_starts) {
+            ro.h_starts = (uint64_t*)h;
+            VLGB_CUDA(cudaMemcpyAsync(h, d_starts, ro.matches * 8, cudaMemcpyDeviceToHost, c.stream));
+            h += ro.matches * 8;
+            c.stats.d2h_bytes += ro.matches * 8;
+        }
+        if (want_tuples) {
+            ro.h_tuples = (uint64_t*)h;
+            VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, ro.tuple_words * 8, cudaMemcpyDeviceToHost, c.stream));
+            c.stats.d2h_bytes += ro.tuple_words * 8;
+        }
+    }
+    VLGB_CUDA(cudaGetLastError());
+    VLGB_CUDA(cudaStreamSynchronize(c.stream));
+    for (uint32_t i = 0; i < nr; i++) {
+        if (!ro.counts[i]) continue;
+        ro.exit_cursor[i] = ex[redo[i]];
+        ro.first_start[i] = fs[redo[i]];
     }
 }
 

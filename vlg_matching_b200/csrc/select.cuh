@@ -208,8 +208,9 @@ __global__ void __launch_bounds__(SEL_TILE) sel_mark_kernel(SelDesc s)
     __shared__ uint32_t s_q;
     const uint32_t slot0 = blockIdx.x * SEL_TILE;
     const uint32_t e = s.entry[blockIdx.x];
-    if (e == NONE32) {  // tile not entered (uniform)
+    if (e == NONE32) {  // tile not entered (uniform): no selected element (the flag words stay meaningful for re-entry)
         if (threadIdx.x == 0) s.tile_count[blockIdx.x] = 0;
+        if (threadIdx.x < 32) s.flagbits[blockIdx.x * 32 + threadIdx.x] = 0u;
         return;
     }
     if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
@@ -294,6 +295,56 @@ __global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
             uint32_t pos = d > 1 ? __ldg(s.depth_vpos[d - 1] + s.depth_vseg[d - 1][q] + idx) : __ldg(s.last_list[q] + idx);
             out[i] = (g + pos) >> sh;
         }
+    }
+}
+
+// ---- re-entry with new cursors (vlgb_result_fixup, multi-shard exactness) -----------------------------------
+// The selection state of the last chunk stays on the device: succ[] for every viable start and one flag bit
+// per start for the reported orbit.  A query that re-enters with another cursor starts its orbit at another
+// element; orbits of the monotone successor coalesce, so only the stretch before the first common element
+// changes: walk the new orbit until it meets a flagged element, clear the flags of the old orbit before that
+// point, set those of the new one.  One thread per re-entered query; the walks are a few hops long.
+struct RefixDesc {
+    uint32_t n;                  // queries that re-enter
+    const uint32_t* q;           // [n] their index in the chunk
+    const uint64_t* entry_local; // [n] new cursor relative to the shard start (bytes, saturated at 0)
+    uint32_t* redo_flag;         // [nq] set for re-entered queries
+};
+
+__device__ __forceinline__ bool sel_flag_get(const uint32_t* fb, uint32_t slot) { return (fb[slot >> 5] >> (slot & 31)) & 1u; }
+
+__global__ void sel_refix_kernel(SelDesc s, RefixDesc r)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= r.n) return;
+    const uint32_t q = r.q[i];
+    r.redo_flag[q] = 1u;
+    const uint32_t len = s.v0_len[q], off = s.sel_off[q];
+    const uint32_t t_old = s.t0[q];
+    const uint32_t t_new = full_lower_bound(s.v0[q], len, r.entry_local[i]);
+    s.t0[q] = t_new;
+    // flag words are laid out [tile][warp] = one bit per slot in slot order, i.e. bit (slot & 31) of word slot >> 5
+    uint32_t* fb = s.flagbits;
+    uint32_t meet = t_new;  // first element of the new orbit that the old orbit reports too (or len)
+    while (meet < len && !sel_flag_get(fb, off + meet)) meet = s.succ[off + meet];
+    for (uint32_t u = t_old; u < len && u < meet; u = s.succ[off + u]) fb[(off + u) >> 5] &= ~(1u << ((off + u) & 31));
+    // an old orbit that started right of `meet` (the cursor moved left) is wholly kept: it is the tail of the new one
+    for (uint32_t m = t_new; m < len && m < meet; m = s.succ[off + m]) fb[(off + m) >> 5] |= 1u << ((off + m) & 31);
+}
+
+// tile_count / entry from the flag words, for the re-entered queries only (all other tiles count 0, so that the
+// prefix scan + emit kernels produce exactly the re-entered queries' matches, back to back)
+__global__ void sel_recount_kernel(SelDesc s, const uint32_t* redo_flag)
+{
+    const uint32_t tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (tile >= s.total_slots / SEL_TILE) return;
+    const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);
+    uint32_t c = 0;
+    if (redo_flag[q]) c = __popc(s.flagbits[tile * 32 + lane]);
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) {
+        s.tile_count[tile] = c;
+        s.entry[tile] = c ? 0u : NONE32;
     }
 }
 

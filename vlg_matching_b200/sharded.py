@@ -3,11 +3,12 @@ GPU, every rank answers the whole query batch on its shard.
 
 The only exchange is tiny: per (query, shard) the match count, the exit cursor and the first reported
 start (24 B).  One all-gather, then the non-overlap cursor is chained left to right: shard g enters
-with the cursor shard g-1 left (vlg_iterator::pull_forward state, vlg_index.hpp:253-264).  A shard
-whose true entry cursor lies beyond its first speculative match re-enters on the device
-(vlgb_result_fixup) and broadcasts its new counters; every rank derives the same decision from the
-gathered data, so the collective sequence is identical on all ranks.  A match is owned by the shard
-that contains its first subpattern's start, so no match is reported twice.
+with the cursor shard g-1 left (vlg_iterator::pull_forward state, vlg_index.hpp:253-264).  Shards
+whose true entry cursor lies beyond their first speculative match re-enter on the device
+(vlgb_result_fixup), all at once, followed by another all-gather; this repeats until no entry cursor
+moves (chain_cursors).  Every rank derives the same decisions from the gathered data, so the collective
+sequence is identical on all ranks.  A match is owned by the shard that contains its first
+subpattern's start, so no match is reported twice.
 
 torch.distributed is plumbing only (NCCL on the GPU box, gloo in the CPU tests); `search_fn` /
 `fixup_fn` are injected so the protocol itself can be tested without a GPU.
@@ -30,28 +31,55 @@ def batch_span(queries) -> int:
     return max((sum(len(s) for s in subs) + sum(g[1] for g in gaps) for subs, gaps in queries), default=0)
 
 
+def implied_entries(table: np.ndarray):
+    """Entry cursor of every shard implied by the gathered rows: shard g enters with the cursor the nearest
+    shard to its left that reported a match left behind (0 for shard 0)."""
+    world, nq = table.shape[0], table.shape[1]
+    cursor = np.zeros(nq, dtype=np.uint64)
+    entries = np.zeros((world, nq), dtype=np.uint64)
+    for g in range(world):
+        entries[g] = cursor
+        cursor = np.where(table[g, :, 0] > 0, table[g, :, 1], cursor)
+    return entries
+
+
 def chain_cursors(rank: int, world: int, local: np.ndarray, all_gather, broadcast, fixup):
     """local: uint64 [Q, 3] = (count, exit_cursor, first_start) of this rank's speculative result
-    (entry cursor 0).  all_gather(arr) -> [world, Q, 3]; broadcast(arr, src) -> arr of rank src;
-    fixup(entry[Q]) -> new local [Q, 3] (runs on this rank only when needed).
-    Returns (table [world, Q, 3] with the final values, number of shards that re-entered)."""
+    (entry cursor 0).  all_gather(arr) -> [world, Q, 3]; fixup(entry[Q]) -> new local [Q, 3] (re-enters the
+    shard on the device for the queries that can change, vlgb_result_fixup).  `broadcast` is unused (kept for
+    callers of the earlier sequential protocol).
+    Returns (table [world, Q, 3] with the final values, number of shard re-entries over all rounds).
+
+    Rounds instead of a left-to-right walk: after the first all-gather every shard knows the cursor its left
+    neighbours would hand it.  All shards whose reported set can change under that cursor re-enter AT THE SAME
+    TIME, then one more all-gather.  A re-entered shard almost always leaves the same exit cursor (orbits of the
+    monotone successor coalesce within a few matches), so the second table already is the fixpoint; when an
+    exit cursor did move, the shards to its right go again.  Shard g is final after round g at the latest, so
+    the loop ends after <= world rounds -- typically 1 -- and costs one small collective per round instead of
+    one per shard.  Every rank derives the same decisions from the same table, so the collective sequence is
+    identical on all ranks."""
+    del broadcast
     table = all_gather(local)
     nq = local.shape[0]
-    cursor = np.zeros(nq, dtype=np.uint64)
+    used = np.zeros((world, nq), dtype=np.uint64)  # entry cursor every shard's current row was computed with
     refixed = 0
-    for g in range(world):
-        cnt, ext, first = table[g, :, 0], table[g, :, 1], table[g, :, 2]
-        need = (cnt > 0) & (cursor > first)
-        if g == rank:
-            mine = fixup(cursor.copy())  # records the entry cursors; re-searches only the `need` queries
-        if need.any():
-            refixed += 1
-            buf = mine if g == rank else np.zeros((nq, 3), dtype=np.uint64)
-            table[g] = broadcast(buf, g)
-            cursor = table[g, :, 1].copy()
-        else:
-            cursor = np.where(cnt > 0, ext, cursor)
-            table[g, :, 1] = cursor
+    for _ in range(world):
+        entries = implied_entries(table)
+        cnt, first = table[:, :, 0], table[:, :, 2]
+        # same rule as vlgb_result_fixup: a query is searched again unless the cursor is unchanged, or moved
+        # right without passing the first reported start (no match: nothing to report either way)
+        moved = entries != used
+        harmless = (entries > used) & ((cnt == 0) | (entries <= first))
+        redo = (moved & ~harmless).any(axis=1)
+        if moved[rank].any():
+            local = fixup(entries[rank].copy())  # records the cursors; searches again only what can change
+        used = entries
+        if not redo.any():
+            # rows of shards without a match carry the cursor through
+            table[:, :, 1] = np.where(cnt > 0, table[:, :, 1], entries)
+            break
+        refixed += int(redo.sum())
+        table = all_gather(local)
     return table, refixed
 
 
