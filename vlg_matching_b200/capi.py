@@ -342,9 +342,9 @@ class Index:
         return Result(r, batch, want)
 
     def free(self):
-        if self.h:
+        if self.h and lib is not None:
             lib.vlgb_index_free(self.h)
-            self.h = None
+        self.h = None
 
     def __del__(self):
         self.free()
