@@ -9,7 +9,8 @@
 //    class = min(len, 8).  Class <= 7 keys are exact; class 8 entries (len >= 8) are verified byte by byte.
 //  * shared memory per CTA: open-addressing hash table of the pass (SoA, SCAN_H slots), the prefilter
 //    f3 (hashed first 3 bytes -> byte with bit c-1 set for every class c = 3..8 that has a pattern with that
-//    prefix; f1/f2 bitmaps for 1- and 2-byte patterns) and one work queue per warp.
+//    prefix) refined by f4 (hashed first 4 bytes, classes 4..8); f1/f2 bitmaps for 1- and 2-byte patterns;
+//    one work queue per warp.
 //  * every warp owns one contiguous chunk of the shard ("row") and walks it 256 positions per step:
 //    lane l holds bytes [8l, 8l+12) of the step in registers (one coalesced 8-byte load + a shuffle), looks
 //    up the class-mask byte of its 8 positions and packs them into 64 bits.  A warp prefix sum of the
@@ -39,6 +40,7 @@ constexpr int SCAN_WARPS = 32;     // warps per CTA (one CTA per SM: the pass ta
 constexpr int SCAN_PPL = 8;        // positions per lane per step
 constexpr int SCAN_STEP = 32 * SCAN_PPL;
 constexpr int SCAN_F3 = 65536;     // 3-byte prefilter entries (u8: bit c-1 set = class c present, c = 3..8)
+constexpr int SCAN_F4 = 32768;     // 4-byte prefilter entries (u8: bit c-1 set = class c present, c = 4..8)
 constexpr int SCAN_F2_WORDS = 64;  // 2048 bits
 constexpr int SCAN_F1_WORDS = 8;   // 256 bits
 constexpr int SCAN_QCAP = 512;     // entries (u32) of a warp's circular work queue
@@ -55,6 +57,7 @@ struct ScanTables {  // one pass; same layout on host, in global memory and in s
     uint32_t klo[SCAN_S];   // first min(len, 8) bytes of pattern pid, zero padded
     uint32_t khi[SCAN_S];
     uint8_t f3[SCAN_F3];
+    uint8_t f4[SCAN_F4];
     uint32_t f2[SCAN_F2_WORDS];
     uint32_t f1[SCAN_F1_WORDS];
 };
@@ -73,6 +76,7 @@ __host__ __device__ inline uint32_t scan_slot_word(uint32_t h, uint32_t c)  // p
     return 0x80000000u | (((h >> 13) & 0x1FFFFu) << 14) | ((c - 1u) << 11);
 }
 __host__ __device__ inline uint32_t scan_h3(uint32_t w) { return ((w & 0xFFFFFFu) * 0x9E3779B1u) >> 16; }
+__host__ __device__ inline uint32_t scan_h4(uint32_t w) { return (w * 0x85EBCA77u) >> 17; }
 __host__ __device__ inline uint32_t scan_h2(uint32_t w) { return ((w & 0xFFFFu) * 0x9E3779B1u) >> 21; }
 
 struct ScanArgs {
@@ -242,7 +246,9 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         uint32_t s0 = 0, s1 = 0;
 #pragma unroll
         for (int j = 0; j < SCAN_PPL; j++) {
-            uint32_t mj = T->f3[scan_h3(wl[j])];
+            // classes >= 4 must also pass the 4-byte filter: most 3-byte prefixes of frequent words are shared by
+            // longer patterns that do not occur here, and every miss costs a full probe sequence
+            uint32_t mj = T->f3[scan_h3(wl[j])] & (T->f4[scan_h4(wl[j])] | 0x07u);
             if (SHORT) {
                 const uint32_t b0 = wl[j] & 0xFFu;
                 mj |= (T->f1[b0 >> 5] >> (b0 & 31)) & 1u;
@@ -531,6 +537,7 @@ inline void build_pass(const PatternDict& d, uint32_t first, uint32_t count, Pas
             ph.tables.f2[i2 >> 5] |= 1u << (i2 & 31);
         } else {
             ph.tables.f3[scan_h3(w32)] |= (uint8_t)(1u << (c - 1));
+            if (c >= 4) ph.tables.f4[scan_h4(w32)] |= (uint8_t)(1u << (c - 1));
         }
         if (c == 8) {
             ph.long_len[i] = len;
