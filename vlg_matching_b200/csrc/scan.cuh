@@ -28,7 +28,6 @@
 #pragma once
 #include <algorithm>
 #include <string>
-#include <unordered_map>
 
 #include "common.cuh"
 
@@ -485,15 +484,47 @@ __global__ void scan_owned_kernel(const uint32_t* pos, const uint64_t* base, con
 // ---- host side: pattern dictionary and pass tables ----------------------------------------------
 struct PatternDict {
     std::vector<std::string> pats;               // distinct subpatterns of the batch
-    std::unordered_map<std::string, uint32_t> id;
+    // open addressing over (hash of the bytes) -> index in pats; no allocation per lookup
+    std::vector<uint32_t> table;
+    uint32_t mask = 0;
+    static uint64_t hash_bytes(const uint8_t* p, uint64_t len)
+    {
+        uint64_t h = 0xcbf29ce484222325ull ^ len;
+        uint64_t i = 0;
+        for (; i + 8 <= len; i += 8) {
+            uint64_t w;
+            memcpy(&w, p + i, 8);
+            h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+            h ^= h >> 29;
+        }
+        uint64_t w = 0;
+        if (i < len) memcpy(&w, p + i, (size_t)(len - i));
+        h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+        return h ^ (h >> 32);
+    }
+    void grow()
+    {
+        const uint32_t cap = mask ? (mask + 1) * 2 : 4096;
+        table.assign(cap, NONE32);
+        mask = cap - 1;
+        for (uint32_t k = 0; k < pats.size(); k++) {
+            uint32_t at = (uint32_t)hash_bytes(reinterpret_cast<const uint8_t*>(pats[k].data()), pats[k].size()) & mask;
+            while (table[at] != NONE32) at = (at + 1) & mask;
+            table[at] = k;
+        }
+    }
     uint32_t add(const uint8_t* p, uint64_t len)
     {
-        std::string s(reinterpret_cast<const char*>(p), (size_t)len);
-        auto it = id.find(s);
-        if (it != id.end()) return it->second;
-        uint32_t k = (uint32_t)pats.size();
-        pats.push_back(s);
-        id.emplace(std::move(s), k);
+        if (pats.size() * 2 >= table.size()) grow();
+        uint32_t at = (uint32_t)hash_bytes(p, len) & mask;
+        while (table[at] != NONE32) {
+            const std::string& s = pats[table[at]];
+            if (s.size() == len && memcmp(s.data(), p, (size_t)len) == 0) return table[at];
+            at = (at + 1) & mask;
+        }
+        const uint32_t k = (uint32_t)pats.size();
+        pats.emplace_back(reinterpret_cast<const char*>(p), (size_t)len);
+        table[at] = k;
         return k;
     }
 };

@@ -128,9 +128,18 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     // (a third of the free device memory, at most 24 GiB) allows; the other passes re-scan in pass 2
     uint32_t stream_cap = 0, stream_passes = 0;
     {
-        size_t free_b = 0, total_b = 0;
-        cudaMemGetInfo(&free_b, &total_b);
-        uint64_t budget = std::min<uint64_t>((uint64_t)24 << 30, (free_b + c.scan_arena.buf.cap) / 3);
+        // free device memory is asked for once per thread and whenever the arena has to grow: cudaMemGetInfo costs
+        // ~0.1 ms, a tenth of the scan itself
+        static thread_local uint64_t cached_avail = 0;
+        static thread_local size_t cached_cap = ~size_t(0);
+        const size_t caps = c.scan_arena.buf.cap + c.list_arena.buf.cap + c.join_arena.buf.cap + c.out_buf.cap;
+        if (cached_cap != caps) {  // some arena of this thread grew (or this is the first call)
+            size_t free_b = 0, total_b = 0;
+            cudaMemGetInfo(&free_b, &total_b);
+            cached_avail = free_b + c.scan_arena.buf.cap;
+            cached_cap = caps;
+        }
+        uint64_t budget = std::min<uint64_t>((uint64_t)24 << 30, cached_avail / 3);
         if (c.stream_budget) budget = std::min(budget, c.stream_budget);
         for (uint32_t per_pos = 2; per_pos >= 1 && !stream_passes; per_pos--) {
             const uint64_t per_pass = (uint64_t)rows * chunk * per_pos * 4;
