@@ -665,7 +665,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         sel_spec_kernel<<<(nchunks + 31) / 32, 32, 0, c.stream>>>(S);
         sel_walk_kernel<<<(nq + 31) / 32, 32, 0, c.stream>>>(S);
         sel_entry_kernel<<<(ntiles + 255) / 256, 256, 0, c.stream>>>(S);
-        sel_mark_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
+        sel_mark_kernel<<<(ntiles + MARK_WARPS - 1) / MARK_WARPS, MARK_WARPS * 32, 0, c.stream>>>(S);
         c.end(ST_SELECT_WALK, 4, (uint64_t)sel_total * 5);
         c.begin(ST_EMIT);
         uint32_t l = exclusive_scan(ValueU32{d_tile_count}, ntiles, d_tile_prefix, scratch, c.stream);

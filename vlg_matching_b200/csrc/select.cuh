@@ -19,7 +19,8 @@
 //             chunk's recorded exit: ~chunks x (a few hops) dependent loads instead of one per tile
 //   entry   : entry[tile] = first selected element in the tile (true hops before the coalescing point,
 //             speculative ones after it)
-//   mark    : per entered tile, one bit per slot for the orbit of entry[tile] (doubling again) + the tile's count
+//   mark    : per entered tile, one bit per slot for the orbit of entry[tile] (one warp per tile walks the staged
+//             succ values) + the tile's count
 //   prefix  : exclusive scan of the tile counts                             (prefix.cuh)
 //   emit    : starts / tuples / exit cursor
 #pragma once
@@ -201,44 +202,51 @@ __global__ void sel_entry_kernel(SelDesc s)
     if (from != NONE32 && tile >= from) s.entry[tile] = s.spec[tile];
 }
 
-__global__ void __launch_bounds__(SEL_TILE) sel_mark_kernel(SelDesc s)
+// One warp per tile: the tile's succ[] values are staged in shared memory (coalesced), lane 0 follows the orbit
+// of entry[tile] through them (a few hundred dependent shared-memory loads) and sets one bit per visited slot.
+// (Marking by pointer doubling with the whole CTA cost 4x the instructions and 20 block barriers per tile.)
+constexpr int MARK_WARPS = 8;  // tiles per CTA
+__global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
 {
-    __shared__ uint32_t ptr[SEL_TILE];
-    __shared__ uint32_t mark[SEL_TILE];
-    __shared__ uint32_t s_q;
-    const uint32_t slot0 = blockIdx.x * SEL_TILE;
-    const uint32_t e = s.entry[blockIdx.x];
-    if (e == NONE32) {  // tile not entered (uniform): no selected element (the flag words stay meaningful for re-entry)
-        if (threadIdx.x == 0) s.tile_count[blockIdx.x] = 0;
-        if (threadIdx.x < 32) s.flagbits[blockIdx.x * 32 + threadIdx.x] = 0u;
+    __shared__ uint32_t s_succ[MARK_WARPS][SEL_TILE];
+    __shared__ uint32_t s_bits[MARK_WARPS][32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tile = blockIdx.x * MARK_WARPS + warp;
+    if (tile >= s.total_slots / SEL_TILE) return;
+    const uint32_t e = s.entry[tile];
+    if (e == NONE32) {  // tile not entered: no selected element (the flag words stay meaningful for re-entry)
+        if (lane == 0) s.tile_count[tile] = 0;
+        s.flagbits[tile * 32 + lane] = 0u;
         return;
     }
-    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
-    __syncthreads();
-    const uint32_t q = s_q;
+    const uint32_t slot0 = tile * SEL_TILE;
+    const uint32_t q = sel_query_of_tile(s, slot0);
     const uint32_t base = slot0 - s.sel_off[q];
     const uint32_t len = s.v0_len[q];
-    const uint32_t t = base + threadIdx.x;
-    uint32_t p = t < len ? s.succ[slot0 + threadIdx.x] : 0xFFFFFFF0u;
-    ptr[threadIdx.x] = p;
-    mark[threadIdx.x] = (t == e) ? 1u : 0u;
-    __syncthreads();
-#pragma unroll 1
-    for (int r = 0; r < SEL_LOG; r++) {
-        // marked elements mark their 2^r-th successor (benign race: only orbit elements get marked)
-        uint32_t rel = p - base;
-        if (mark[threadIdx.x] && rel < (uint32_t)SEL_TILE) mark[rel] = 1u;
-        uint32_t nx = sel_hop(ptr, p, base);
-        __syncthreads();
-        p = nx;
-        ptr[threadIdx.x] = p;
-        __syncthreads();
+    uint32_t* sc = s_succ[warp];
+#pragma unroll 8
+    for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32) sc[i] = base + i < len ? s.succ[slot0 + i] : 0xFFFFFFF0u;
+    s_bits[warp][lane] = 0u;
+    __syncwarp();
+    uint32_t cnt = 0;
+    if (lane == 0) {
+        const uint32_t end = min((uint32_t)SEL_TILE, len - base);  // succ = len ("no successor") may fall inside the tile
+        uint32_t rel = e - base, word = rel >> 5, bits = 0;
+        while (rel < end) {
+            if ((rel >> 5) != word) {
+                s_bits[warp][word] = bits;
+                word = rel >> 5;
+                bits = 0;
+            }
+            bits |= 1u << (rel & 31);
+            cnt++;
+            rel = sc[rel] - base;  // a successor beyond the tile (or the list) wraps to a huge value
+        }
+        s_bits[warp][word] = bits;
+        s.tile_count[tile] = cnt;
     }
-    const bool sel = t < len && mark[threadIdx.x];
-    const uint32_t bits = __ballot_sync(0xffffffffu, sel);
-    if ((threadIdx.x & 31) == 0) s.flagbits[blockIdx.x * 32 + (threadIdx.x >> 5)] = bits;
-    const int total = __syncthreads_count(sel);
-    if (threadIdx.x == 0) s.tile_count[blockIdx.x] = (uint32_t)total;
+    __syncwarp();
+    s.flagbits[tile * 32 + lane] = s_bits[warp][lane];
 }
 
 // counts[q] = selected elements in the query's tiles
