@@ -656,8 +656,9 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         S.chunk_tile0 = dev_at<const uint32_t>(d_ctl2, o_chunk_tile0);
         S.q_chunk0 = dev_at<const uint32_t>(d_ctl2, o_q_chunk0);
         c.begin(ST_SELECT_TILE);
-        sel_tile_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
-        c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 16);
+        sel_succ_kernel<<<ntiles * (SEL_TILE / 256), 256, 0, c.stream>>>(S);
+        sel_tile_kernel<<<(ntiles + MARK_WARPS - 1) / MARK_WARPS, MARK_WARPS * 32, 0, c.stream>>>(S);
+        c.end(ST_SELECT_TILE, 2, (uint64_t)sel_total * 20);
         c.begin(ST_SELECT_WALK);
         VLGB_CUDA(cudaMemsetAsync(d_entry, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
         VLGB_CUDA(cudaMemsetAsync(d_spec, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));

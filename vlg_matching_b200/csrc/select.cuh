@@ -11,8 +11,9 @@
 // Slots: every query owns a TILE-aligned segment of upper-bound size (|L_0| owned part), so a tile
 // never straddles two queries.  Kernels:
 //   resolve : per query, where V_0 / last live (scan list for k = 1, else the deepest join level)
-//   tile    : succ[slot] (gallop from t+1), then exitp[slot] = first orbit element of slot that lies outside its tile (pointer doubling
-//             in shared memory, log2(TILE) rounds)
+//   succ    : succ[slot], gallop from t+1, one thread per slot
+//   tile    : exitp[slot] = first orbit element of slot that lies outside its tile (one warp per tile, segments of
+//             32 resolved from the right)
 //   spec    : one thread per CHUNK of 64 tiles hops tile to tile from the chunk's first element (a guess)
 //   walk    : one thread per query hops from the true start; orbits of a monotone successor coalesce, so
 //             inside a chunk it soon lands on an element the speculative hop also visited and jumps to that
@@ -31,6 +32,7 @@ namespace vlgb {
 constexpr int SEL_TILE = 1024;  // = threads per CTA of the tile kernels
 constexpr int SEL_LOG = 10;
 constexpr int SEL_CHUNK_TILES = 64;  // tiles per speculative chunk
+constexpr int MARK_WARPS = 8;        // tiles per CTA of the warp-per-tile kernels
 
 struct SelDesc {
     uint32_t nq;                 // queries of the chunk
@@ -116,41 +118,67 @@ __device__ __forceinline__ uint32_t sel_hop(const uint32_t* ptr, uint32_t p, uin
     return rel < (uint32_t)SEL_TILE ? ptr[rel] : p;
 }
 
-__global__ void __launch_bounds__(SEL_TILE) sel_tile_kernel(SelDesc s)
+// succ[slot] for every viable start of every query: one thread per slot, gallop from t + 1.
+__global__ void __launch_bounds__(256) sel_succ_kernel(SelDesc s)
 {
-    __shared__ uint32_t ptr[SEL_TILE];
     __shared__ uint32_t s_q;
-    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    const uint32_t tile = blockIdx.x / (SEL_TILE / 256);
+    const uint32_t slot0 = tile * SEL_TILE;
     if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
     __syncthreads();
     const uint32_t q = s_q;
+    const uint32_t slot = blockIdx.x * 256 + threadIdx.x;
+    const uint32_t t = slot - s.sel_off[q];  // V_0 index
+    const uint32_t len = s.v0_len[q];
+    if (t >= len) return;
+    const uint32_t* v = s.v0[q];
+    const uint32_t* vl = s.vlast[q];
+    const uint32_t x = __ldg(v + t);
+    const uint32_t ll = s.last_len[q];
+    uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
+    if (!vl && ll == (1u << s.sym_shift) && ((((uint64_t)x + s.global_offset) >> s.sym_shift) & 1ull) == 0)
+        e = (uint64_t)x + (2u << s.sym_shift);  // k = 1 sibling skip
+    s.succ[slot] = gallop_lower_bound(v, t + 1, len, e);
+}
+
+// exitp[slot] = first element of slot's orbit that lies outside its tile.  One warp per tile: the tile's succ
+// values are staged in shared memory and resolved segment by segment (32 slots) from the right: inside a
+// segment by pointer jumping through shuffles (succ(t) > t, so 5 rounds settle 32 slots), then one look-up
+// into the already final part to the right.  (Pointer doubling over the whole tile by a 1024-thread CTA took
+// 20 block barriers and three times the instructions.)
+__global__ void __launch_bounds__(MARK_WARPS * 32) sel_tile_kernel(SelDesc s)
+{
+    __shared__ uint32_t s_ptr[MARK_WARPS][SEL_TILE];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tile = blockIdx.x * MARK_WARPS + warp;
+    if (tile >= s.total_slots / SEL_TILE) return;
+    const uint32_t slot0 = tile * SEL_TILE;
+    const uint32_t q = sel_query_of_tile(s, slot0);
     const uint32_t base = slot0 - s.sel_off[q];  // V_0 index of the tile's first element
     const uint32_t len = s.v0_len[q];
-    if (base >= len) return;                     // whole tile beyond the viable list (uniform)
-    const uint32_t t = base + threadIdx.x;
-    uint32_t p = 0xFFFFFFF0u;
-    if (t < len) {  // succ(t) = lower_bound(V_0, E(V_0[t]))
-        const uint32_t* v = s.v0[q];
-        const uint32_t* vl = s.vlast[q];
-        const uint32_t x = __ldg(v + t);
-        const uint32_t ll = s.last_len[q];
-        uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
-        if (!vl && ll == (1u << s.sym_shift) && ((((uint64_t)x + s.global_offset) >> s.sym_shift) & 1ull) == 0)
-            e = (uint64_t)x + (2u << s.sym_shift);  // k = 1 sibling skip
-        p = gallop_lower_bound(v, t + 1, len, e);
-        s.succ[slot0 + threadIdx.x] = p;
+    if (base >= len) return;
+    uint32_t* ptr = s_ptr[warp];
+#pragma unroll 8
+    for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32) ptr[i] = base + i < len ? s.succ[slot0 + i] : 0xFFFFFFF0u;
+    __syncwarp();
+    for (int seg = SEL_TILE / 32 - 1; seg >= 0; seg--) {
+        const uint32_t segbase = base + seg * 32;
+        uint32_t p = ptr[seg * 32 + lane];
+#pragma unroll
+        for (int r = 0; r < 5; r++) {
+            const uint32_t rel = p - segbase;
+            const uint32_t o = __shfl_sync(0xffffffffu, p, rel & 31);
+            if (rel < 32u) p = o;
+        }
+        const uint32_t relt = p - base;
+        if (relt < (uint32_t)SEL_TILE) p = ptr[relt];  // a later segment: final already
+        __syncwarp();
+        ptr[seg * 32 + lane] = p;
+        __syncwarp();
     }
-    ptr[threadIdx.x] = p;
-    __syncthreads();
-#pragma unroll 1
-    for (int r = 0; r < SEL_LOG; r++) {
-        uint32_t nx = sel_hop(ptr, p, base);
-        __syncthreads();
-        p = nx;
-        ptr[threadIdx.x] = p;
-        __syncthreads();
-    }
-    if (t < len) s.exitp[slot0 + threadIdx.x] = p;
+#pragma unroll 8
+    for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32)
+        if (base + i < len) s.exitp[slot0 + i] = ptr[i];
 }
 
 __global__ void sel_spec_kernel(SelDesc s)
@@ -205,7 +233,6 @@ __global__ void sel_entry_kernel(SelDesc s)
 // One warp per tile: the tile's succ[] values are staged in shared memory (coalesced), lane 0 follows the orbit
 // of entry[tile] through them (a few hundred dependent shared-memory loads) and sets one bit per visited slot.
 // (Marking by pointer doubling with the whole CTA cost 4x the instructions and 20 block barriers per tile.)
-constexpr int MARK_WARPS = 8;  // tiles per CTA
 __global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
 {
     __shared__ uint32_t s_succ[MARK_WARPS][SEL_TILE];
