@@ -469,7 +469,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     need += 2 * Arena::padded(sel_total_ub, 4) + Arena::padded((size_t)ntiles_ub * 32, 4);  // succ, exitp, flag bits
     need += 4 * Arena::padded(ntiles_ub + 2, 4);                                       // entry, spec, tile count / prefix
     need += 2 * Arena::padded(nchunks_ub + 1, 4);                                      // spec_exit, coalesce
-    const size_t ctl2_bytes = Arena::padded(nq + 1, 4) + Arena::padded(nq, 4) + 2 * Arena::padded(nchunks_ub, 4);
+    const size_t ctl2_bytes = Arena::padded(nq + 1, 4) + Arena::padded(nq, 4) + 2 * Arena::padded(nchunks_ub, 4) + Arena::padded(ntiles_ub + 1, 4);
     need += ctl2_bytes + 1024;                                                         // selection layout (second blob)
     need += Arena::padded(nq, 8) + Arena::padded(kmax + 1, 4);                         // counts, viable totals
     const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(max_slots, sel_total_ub));
@@ -570,6 +570,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.nq = nq;
     S.total_slots = 0;     // layout fields are set once the V_0 sizes are known (below)
     S.sel_off = nullptr;
+    S.tile_q = nullptr;
     S.kq = dev_at<const uint32_t>(d_ctl, o_kq);
     S.last_len = dev_at<const uint32_t>(d_ctl, o_last_len);
     S.entry_local = dev_at<const uint64_t>(d_ctl, o_entry);
@@ -634,9 +635,11 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     sel_off[nq] = (uint32_t)sel_run;
     const uint32_t sel_total = (uint32_t)sel_run;
     const uint32_t ntiles = sel_total / SEL_TILE;
+    std::vector<uint32_t> tile_q(ntiles + 1, 0);
     for (uint32_t s = 0; s < nq; s++) {
         q_chunk0[s] = (uint32_t)chunk_q.size();
         const uint32_t t0 = sel_off[s] / SEL_TILE, t1 = sel_off[s + 1] / SEL_TILE;
+        for (uint32_t t = t0; t < t1; t++) tile_q[t] = s;
         for (uint32_t t = t0; t < t1; t += SEL_CHUNK_TILES) {
             chunk_q.push_back(s);
             chunk_tile0.push_back(t);
@@ -646,11 +649,12 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     if (sel_total) {
         Packer ctl2;
         const size_t o_sel_off = ctl2.put(sel_off), o_q_chunk0 = ctl2.put(q_chunk0), o_chunk_q = ctl2.put(chunk_q),
-                     o_chunk_tile0 = ctl2.put(chunk_tile0);
+                     o_chunk_tile0 = ctl2.put(chunk_tile0), o_tile_q = ctl2.put(tile_q);
         VLGB_CUDA(cudaMemcpyAsync(d_ctl2, ctl2.host.data(), ctl2.host.size(), cudaMemcpyHostToDevice, c.stream));
         c.stats.h2d_bytes += ctl2.host.size();
         S.total_slots = sel_total;
         S.sel_off = dev_at<const uint32_t>(d_ctl2, o_sel_off);
+        S.tile_q = dev_at<const uint32_t>(d_ctl2, o_tile_q);
         S.nchunks = nchunks;
         S.chunk_q = dev_at<const uint32_t>(d_ctl2, o_chunk_q);
         S.chunk_tile0 = dev_at<const uint32_t>(d_ctl2, o_chunk_tile0);

@@ -37,7 +37,8 @@ constexpr int MARK_WARPS = 8;        // tiles per CTA of the warp-per-tile kerne
 struct SelDesc {
     uint32_t nq;                 // queries of the chunk
     uint32_t total_slots;        // sel_off[nq], multiple of SEL_TILE
-    const uint32_t* sel_off;     // [nq+1], TILE-aligned prefix of upper-bound V_0 sizes
+    const uint32_t* sel_off;     // [nq+1], TILE-aligned prefix of the V_0 sizes
+    const uint32_t* tile_q;      // [total_slots / SEL_TILE] query of every tile
     const uint32_t* kq;          // subpatterns of each query
     const uint32_t* last_len;    // |P_k|
     const uint64_t* entry_local; // entry cursor relative to the shard start (saturated at 0)
@@ -107,7 +108,7 @@ __global__ void sel_resolve_kernel(SelDesc s)
 
 __device__ __forceinline__ uint32_t sel_query_of_tile(const SelDesc& s, uint32_t slot0)
 {
-    return find_segment(s.sel_off, 0, s.nq - 1, slot0);
+    return __ldg(s.tile_q + slot0 / SEL_TILE);  // host-built map: one load instead of a binary search over sel_off
 }
 
 // Pointer doubling inside one tile.  ptr[i] (shared) holds a V_0 index; indices inside
