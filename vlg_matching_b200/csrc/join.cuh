@@ -57,7 +57,8 @@ struct DepthDesc {
     // right side: depth > 1 -> the compacted viable list of the previous depth
     const uint32_t* prev_vpos;
     const uint32_t* prev_vlast;
-    const uint32_t* prev_vseg;   // [prev nseg + 1]
+    const uint32_t* prev_vseg;   // [prev nseg] first index of each segment inside the previous depth's arrays
+    const uint32_t* prev_vlen;   // [prev nseg] its length
     const uint64_t* lo;          // start-to-start lower bound of this level (saturated)
     const uint64_t* hi;
     // outputs
@@ -172,9 +173,8 @@ __global__ void join_tileseg_kernel(DepthDesc d, uint32_t ntiles)
         jt.R = d.right_list[seg];
         jt.rlen = d.right_len[seg];
     } else {
-        const uint32_t b = __ldg(d.prev_vseg + seg);
-        jt.R = d.prev_vpos + b;
-        jt.rlen = __ldg(d.prev_vseg + seg + 1) - b;
+        jt.R = d.prev_vpos + __ldg(d.prev_vseg + seg);
+        jt.rlen = __ldg(d.prev_vlen + seg);
     }
     jt.left = d.left[seg] + (slot - so);
     // positions are < 2^32: bounds clamped to 2^33 compare the same and cannot overflow a 64-bit add
@@ -310,9 +310,8 @@ __global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
                 R = d.right_list[seg];
                 rlen = d.right_len[seg];
             } else {
-                const uint32_t b = __ldg(d.prev_vseg + seg);
-                R = d.prev_vpos + b;
-                rlen = __ldg(d.prev_vseg + seg + 1) - b;
+                R = d.prev_vpos + __ldg(d.prev_vseg + seg);
+                rlen = __ldg(d.prev_vlen + seg);
             }
             xs[i] = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
             const uint32_t j = full_lower_bound(R, rlen, sat_add64(xs[i], d.lo[seg]));
@@ -416,6 +415,118 @@ __global__ void join_vseg_kernel(DepthDesc d, uint32_t ntiles)
     const uint32_t slot = sg < d.nseg ? __ldg(d.slot_off + sg) : d.total_slots;
     d.vseg[sg] = slot >= d.total_slots ? all : __ldg(d.tile_prefix + slot / JF_TILE) + d.seg_rank[sg];
     if (sg == d.nseg) *d.total_out = all;
+}
+
+// The segments of a pass are a subset of the chunk's queries (seg_map[i] = query).  Publishes where every
+// query's viable list starts and how long it is: gseg / glen are indexed by QUERY and are what the next depth
+// and the selection read.  `base` = viable slots other passes of the depth have already written.
+__global__ void join_publish_kernel(const uint32_t* vseg_local, const uint32_t* seg_map, uint32_t nseg, const uint32_t* base,
+                                    uint32_t* gseg, uint32_t* glen, uint32_t* total_out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t b = base ? *base : 0u;
+    if (i < nseg) {
+        const uint32_t q = seg_map[i];
+        gseg[q] = b + vseg_local[i];
+        glen[q] = vseg_local[i + 1] - vseg_local[i];
+    }
+    if (i == nseg) *total_out = b + vseg_local[nseg];
+}
+
+// ---- right-driven join (depth 1 only) ---------------------------------------------------------------------
+// When the right list is far shorter than the left one (a frequent first word followed by a rare one: four
+// fifths of the join slots of BASELINE config 2), almost no left element is viable and visiting them all is
+// wasted work.  Driven from the right: the left elements whose partner is y_j are exactly
+//     L  intersected with  [ max(y_j - hi, y_{j-1} - lo + 1),  y_j - lo ]
+// (x + lo <= y_j picks y_j or an earlier partner, x + lo > y_{j-1} excludes the earlier ones, y_j <= x + hi is
+// the gap bound).  The ranges are disjoint and ascending in j, so the viable list comes out sorted and already
+// compact: two binary searches in L per right element, a prefix sum over the counts, then the elements are copied.
+struct RevDesc {
+    uint32_t nseg;                 // right-driven segments
+    uint32_t total_slots;          // slot_off[nseg] = right elements of all of them
+    const uint32_t* slot_off;      // [nseg+1]
+    const uint32_t* const* left;   // [nseg]
+    const uint32_t* left_len;      // [nseg]
+    const uint32_t* const* right;  // [nseg]
+    const uint64_t* lo;            // [nseg] start-to-start bounds
+    const uint64_t* hi;
+    uint32_t* first;               // [total_slots] index in L of the first element paired with this right element
+    uint32_t* count;               // [total_slots] how many
+    const uint32_t* prefix;        // [total_slots+1] exclusive scan of count
+    const uint32_t* base;          // viable slots written by the left-driven pass of the depth
+    uint32_t* vpos;
+    uint32_t* vnxt;
+    uint32_t* vlast;
+};
+
+__global__ void __launch_bounds__(256) join_rev_count_kernel(RevDesc r)
+{
+    const uint32_t slot = blockIdx.x * 256 + threadIdx.x;
+    if (slot >= r.total_slots) return;
+    const uint32_t seg = find_segment(r.slot_off, 0, r.nseg - 1, slot);
+    const uint32_t j = slot - __ldg(r.slot_off + seg);
+    const uint32_t* R = r.right[seg];
+    const uint32_t* L = r.left[seg];
+    const uint32_t nl = r.left_len[seg];
+    const uint64_t lo = r.lo[seg], hi = r.hi[seg];
+    const uint64_t y = __ldg(R + j);
+    uint32_t a = 0, n = 0;
+    if (y >= lo) {
+        const uint64_t x_hi = y - lo;                       // largest x with x + lo <= y
+        uint64_t x_lo = y > hi ? y - hi : 0;                // smallest x with y <= x + hi
+        if (j > 0) {
+            const uint64_t yp = __ldg(R + j - 1);
+            if (yp >= lo) x_lo = max(x_lo, yp - lo + 1);    // x + lo > y_{j-1}
+        }
+        if (x_lo <= x_hi) {
+            a = full_lower_bound(L, nl, x_lo);
+            const uint32_t b = full_lower_bound(L, nl, x_hi + 1);
+            n = b - a;
+        }
+    }
+    r.first[slot] = a;
+    r.count[slot] = n;
+}
+
+// one warp per 32 right elements; the lanes copy each element's run of left positions together
+__global__ void __launch_bounds__(256) join_rev_expand_kernel(RevDesc r)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t slot = blockIdx.x * 256 + threadIdx.x;
+    uint32_t a = 0, n = 0, o = 0, j = 0, y = 0;
+    const uint32_t* L = nullptr;
+    if (slot < r.total_slots) {
+        n = r.count[slot];
+        if (n) {
+            const uint32_t seg = find_segment(r.slot_off, 0, r.nseg - 1, slot);
+            j = slot - __ldg(r.slot_off + seg);
+            a = r.first[slot];
+            o = *r.base + __ldg(r.prefix + slot);
+            L = r.left[seg];
+            y = __ldg(r.right[seg] + j);
+        }
+    }
+    uint32_t todo = __ballot_sync(0xffffffffu, n != 0);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t sn = __shfl_sync(0xffffffffu, n, src), sa = __shfl_sync(0xffffffffu, a, src),
+                       so = __shfl_sync(0xffffffffu, o, src), sj = __shfl_sync(0xffffffffu, j, src),
+                       sy = __shfl_sync(0xffffffffu, y, src);
+        const uint32_t* sL = reinterpret_cast<const uint32_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(L), src));
+        for (uint32_t t = lane; t < sn; t += 32) {
+            r.vpos[so + t] = __ldg(sL + sa + t);
+            r.vnxt[so + t] = sj;
+            r.vlast[so + t] = sy;
+        }
+    }
+}
+
+// local vseg of the right-driven pass: viable slots before each segment's first right element
+__global__ void join_rev_vseg_kernel(RevDesc r, uint32_t* vseg_local)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= r.nseg) vseg_local[i] = __ldg(r.prefix + __ldg(r.slot_off + i));
 }
 
 }  // namespace vlgb

@@ -318,6 +318,16 @@ inline uint64_t list_len(const BatchView& v, uint32_t sub, bool level0)
     return level0 ? v.so->own[pid] : v.so->tot[pid];
 }
 
+// Depth 1 of a query is joined from the right when its last list is far shorter than the list to its left: two
+// binary searches per right element instead of one window search per left element (join.cuh, RevDesc).
+constexpr uint64_t JOIN_REV_FACTOR = 16;
+inline bool join_right_driven(const BatchView& v, const PlanQuery& pq)
+{
+    if (pq.k < 2) return false;
+    const uint64_t nl = list_len(v, pq.s0 + pq.k - 2, pq.k == 2), nr = list_len(v, pq.s0 + pq.k - 1, false);
+    return nr * JOIN_REV_FACTOR < nl;
+}
+
 // bytes of device state a query needs in the join/select stage (upper bound, used for chunking)
 inline uint64_t query_state_bytes(const BatchView& v, const PlanQuery& pq)
 {
@@ -365,48 +375,66 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
 
     // ---- sizes per depth
     struct DepthHost {
-        uint32_t nseg = 0;
-        std::vector<uint32_t> slot_off;
+        uint32_t nseg = 0;                       // queries that have this depth (a prefix of the chunk)
+        // left-driven pass: segments fmap[i] (query index); every array below is indexed by i
+        std::vector<uint32_t> fmap, slot_off;
         std::vector<const uint32_t*> left, right_list;
         std::vector<uint32_t> right_len;
         std::vector<uint64_t> lo, hi;
-        size_t o_slot_off, o_left, o_right_list, o_right_len, o_lo, o_hi;
-        uint32_t *vpos, *vnxt, *vlast, *vseg;
+        size_t o_fmap, o_slot_off, o_left, o_right_list, o_right_len, o_lo, o_hi;
+        // right-driven pass (depth 1 only): segments rmap[i]
+        std::vector<uint32_t> rmap, r_slot_off, r_left_len;
+        std::vector<const uint32_t*> r_left, r_right;
+        std::vector<uint64_t> r_lo, r_hi;
+        size_t o_rmap, o_r_slot_off, o_r_left_len, o_r_left, o_r_right, o_r_lo, o_r_hi;
+        uint64_t out_cap = 0;                    // upper bound of the viable slots = all left elements
+        uint32_t *vpos, *vnxt, *vlast, *gseg, *glen, *vseg_f, *vseg_r, *ftotal;
     };
     std::vector<DepthHost> dh(kmax);  // index 1 .. kmax-1
-    uint64_t max_slots = 0;
+    uint64_t max_slots = 0, max_rslots = 0;
     for (uint32_t d = 1; d < kmax; d++) {
         DepthHost& h = dh[d];
         uint32_t nseg = 0;
         while (nseg < nq && qs[nseg].k > d) nseg++;
         h.nseg = nseg;
-        h.slot_off.resize(nseg + 1);
-        h.left.resize(nseg);
-        h.lo.resize(nseg);
-        h.hi.resize(nseg);
-        if (d == 1) {
-            h.right_list.resize(nseg);
-            h.right_len.resize(nseg);
-        }
-        uint64_t run = 0;
+        uint64_t run = 0, rrun = 0;
         for (uint32_t s = 0; s < nseg; s++) {
             const PlanQuery& pq = qs[s];
-            uint32_t lvl = pq.k - 1 - d, sub = pq.s0 + lvl;
-            h.slot_off[s] = (uint32_t)run;
-            run += list_len(v, sub, lvl == 0);
-            h.left[s] = list_ptr(sub);
+            const uint32_t lvl = pq.k - 1 - d, sub = pq.s0 + lvl;
+            const uint64_t nl = list_len(v, sub, lvl == 0);
             // start-to-start bounds, vlg_index.hpp:95, in bytes (gaps are given in symbols)
-            h.lo[s] = sat_add64(sat_shl64(B.gap_min[sub], v.sym_shift), plen(sub));
-            h.hi[s] = sat_add64(sat_shl64(B.gap_max[sub], v.sym_shift), plen(sub));
+            const uint64_t glo = sat_add64(sat_shl64(B.gap_min[sub], v.sym_shift), plen(sub));
+            const uint64_t ghi = sat_add64(sat_shl64(B.gap_max[sub], v.sym_shift), plen(sub));
+            h.out_cap += nl;
+            if (d == 1 && join_right_driven(v, pq)) {
+                h.rmap.push_back(s);
+                h.r_slot_off.push_back((uint32_t)rrun);
+                rrun += list_len(v, pq.s0 + pq.k - 1, false);
+                h.r_left.push_back(list_ptr(sub));
+                h.r_left_len.push_back((uint32_t)nl);
+                h.r_right.push_back(list_ptr(pq.s0 + pq.k - 1));
+                h.r_lo.push_back(glo);
+                h.r_hi.push_back(ghi);
+                continue;
+            }
+            h.fmap.push_back(s);
+            h.slot_off.push_back((uint32_t)run);
+            run += nl;
+            h.left.push_back(list_ptr(sub));
+            h.lo.push_back(glo);
+            h.hi.push_back(ghi);
             if (d == 1) {
-                h.right_list[s] = list_ptr(pq.s0 + pq.k - 1);
-                h.right_len[s] = (uint32_t)list_len(v, pq.s0 + pq.k - 1, false);
+                h.right_list.push_back(list_ptr(pq.s0 + pq.k - 1));
+                h.right_len.push_back((uint32_t)list_len(v, pq.s0 + pq.k - 1, false));
             }
         }
-        if (run >= 0xFFFF0000ull) throw CudaError{cudaErrorInvalidValue, __FILE__, __LINE__};  // chunking keeps this away
-        h.slot_off[nseg] = (uint32_t)run;
+        if (run >= 0xFFFF0000ull || rrun >= 0xFFFF0000ull || h.out_cap >= 0xFFFF0000ull)
+            throw CudaError{cudaErrorInvalidValue, __FILE__, __LINE__};  // chunking keeps this away
+        h.slot_off.push_back((uint32_t)run);
+        h.r_slot_off.push_back((uint32_t)rrun);
         max_slots = std::max(max_slots, run);
-        c.stats.join_slots += run;
+        max_rslots = std::max(max_rslots, rrun);
+        c.stats.join_slots += run + rrun;
     }
 
     // ---- selection layout
@@ -441,6 +469,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     Packer ctl;
     for (uint32_t d = 1; d < kmax; d++) {
         DepthHost& h = dh[d];
+        h.o_fmap = ctl.put(h.fmap);
         h.o_slot_off = ctl.put(h.slot_off);
         h.o_left = ctl.put(h.left);
         h.o_lo = ctl.put(h.lo);
@@ -448,12 +477,19 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         if (d == 1) {
             h.o_right_list = ctl.put(h.right_list);
             h.o_right_len = ctl.put(h.right_len);
+            h.o_rmap = ctl.put(h.rmap);
+            h.o_r_slot_off = ctl.put(h.r_slot_off);
+            h.o_r_left_len = ctl.put(h.r_left_len);
+            h.o_r_left = ctl.put(h.r_left);
+            h.o_r_right = ctl.put(h.r_right);
+            h.o_r_lo = ctl.put(h.r_lo);
+            h.o_r_hi = ctl.put(h.r_hi);
         }
     }
     const size_t o_kq = ctl.put(kq), o_last_len = ctl.put(last_len),
                  o_entry = ctl.put(entry_local), o_exit = ctl.put(exit_init), o_first = ctl.put(first_init), o_list0 = ctl.put(list0),
                  o_list0_len = ctl.put(list0_len), o_last_list = ctl.put(last_list);
-    std::vector<const uint32_t*> tab(4 * MAX_K, nullptr);  // depth_vpos | depth_vnxt | depth_vlast | depth_vseg
+    std::vector<const uint32_t*> tab(5 * MAX_K, nullptr);  // depth_vpos | depth_vnxt | depth_vlast | depth_vseg | depth_vlen
     const size_t o_tab = ctl.put(tab);                     // patched below once the arena addresses are known
     std::vector<uint64_t> zeros64(nq, 0);
     const size_t o_tuple_off = ctl.put(zeros64);
@@ -464,7 +500,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     const size_t max_jtiles = (max_slots + JF_TILE - 1) / JF_TILE;
     need += 3 * Arena::padded(max_slots, 4) + 2 * Arena::padded(max_jtiles + 4, 4) + Arena::padded(max_jtiles + 2, sizeof(JoinTile)) + Arena::padded(nq + 2, 4);  // staging, tile counts / prefix / segments, seg_rank
     for (uint32_t d = 1; d < kmax; d++)
-        need += 3 * Arena::padded(dh[d].slot_off[dh[d].nseg], 4) + Arena::padded(dh[d].nseg + 1, 4);
+        need += 3 * Arena::padded(dh[d].out_cap, 4) + 4 * Arena::padded(dh[d].nseg + 2, 4) + 256;
+    need += 3 * Arena::padded(max_rslots + 4, 4);                                       // right-driven pass: first, count, prefix
     need += 2 * Arena::padded(nq, 8) + 2 * Arena::padded(nq, 4);                       // v0, vlast, v0_len, t0
     need += 2 * Arena::padded(sel_total_ub, 4) + Arena::padded((size_t)ntiles_ub * 32, 4);  // succ, exitp, flag bits
     need += 4 * Arena::padded(ntiles_ub + 2, 4);                                       // entry, spec, tile count / prefix
@@ -472,7 +509,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     const size_t ctl2_bytes = Arena::padded(nq + 1, 4) + Arena::padded(nq, 4) + 2 * Arena::padded(nchunks_ub, 4) + Arena::padded(ntiles_ub + 1, 4);
     need += ctl2_bytes + 1024;                                                         // selection layout (second blob)
     need += Arena::padded(nq, 8) + Arena::padded(kmax + 1, 4);                         // counts, viable totals
-    const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(max_slots, sel_total_ub));
+    const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(std::max<uint64_t>(max_slots, max_rslots), sel_total_ub));
     need += Arena::padded(scratch_words, 4);
     c.join_arena.reserve(need);
     Arena& A = c.join_arena;
@@ -484,16 +521,24 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     uint32_t* jtile_count = A.take<uint32_t>(max_jtiles + 4);
     uint32_t* jtile_prefix = A.take<uint32_t>(max_jtiles + 4);
     JoinTile* jtile_rec = A.take<JoinTile>(max_jtiles + 2);
+    uint32_t* rev_first = A.take<uint32_t>(max_rslots + 4);
+    uint32_t* rev_count = A.take<uint32_t>(max_rslots + 4);
+    uint32_t* rev_prefix = A.take<uint32_t>(max_rslots + 4);
     for (uint32_t d = 1; d < kmax; d++) {
-        size_t t = dh[d].slot_off[dh[d].nseg];
+        const size_t t = dh[d].out_cap;
         dh[d].vpos = A.take<uint32_t>(t);
         dh[d].vnxt = A.take<uint32_t>(t);
         dh[d].vlast = A.take<uint32_t>(t);
-        dh[d].vseg = A.take<uint32_t>(dh[d].nseg + 1);
+        dh[d].gseg = A.take<uint32_t>(dh[d].nseg + 2);
+        dh[d].glen = A.take<uint32_t>(dh[d].nseg + 2);
+        dh[d].vseg_f = A.take<uint32_t>(dh[d].nseg + 2);
+        dh[d].vseg_r = A.take<uint32_t>(dh[d].nseg + 2);
+        dh[d].ftotal = A.take<uint32_t>(1);
         tab[0 * MAX_K + d] = dh[d].vpos;
         tab[1 * MAX_K + d] = dh[d].vnxt;
         tab[2 * MAX_K + d] = dh[d].vlast;
-        tab[3 * MAX_K + d] = dh[d].vseg;
+        tab[3 * MAX_K + d] = dh[d].gseg;
+        tab[4 * MAX_K + d] = dh[d].glen;
     }
     memcpy(ctl.host.data() + o_tab, tab.data(), tab.size() * sizeof(tab[0]));
     const uint32_t** d_v0 = A.take<const uint32_t*>(nq);
@@ -517,52 +562,89 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     VLGB_CUDA(cudaMemcpyAsync(d_ctl, ctl.host.data(), ctl.host.size(), cudaMemcpyHostToDevice, c.stream));
     c.stats.h2d_bytes += ctl.host.size();
 
-    // ---- join, depth by depth
+    // ---- join, depth by depth: a left-driven pass over the segments of fmap, then (depth 1) a right-driven pass
+    // over those of rmap; both publish where every query's viable list starts (gseg / glen, indexed by query)
     for (uint32_t d = 1; d < kmax; d++) {
         DepthHost& h = dh[d];
-        DepthDesc D;
-        D.nseg = h.nseg;
-        D.total_slots = h.slot_off[h.nseg];
-        D.slot_off = dev_at<const uint32_t>(d_ctl, h.o_slot_off);
-        D.left = dev_at<const uint32_t* const>(d_ctl, h.o_left);
-        D.right_list = d == 1 ? dev_at<const uint32_t* const>(d_ctl, h.o_right_list) : nullptr;
-        D.right_len = d == 1 ? dev_at<const uint32_t>(d_ctl, h.o_right_len) : nullptr;
-        D.prev_vpos = d > 1 ? dh[d - 1].vpos : nullptr;
-        D.prev_vlast = d > 1 ? dh[d - 1].vlast : nullptr;
-        D.prev_vseg = d > 1 ? dh[d - 1].vseg : nullptr;
-        D.lo = dev_at<const uint64_t>(d_ctl, h.o_lo);
-        D.hi = dev_at<const uint64_t>(d_ctl, h.o_hi);
-        D.stage_x = stage_x;
-        D.stage_j = stage_j;
-        D.stage_last = stage_last;
-        D.seg_rank = seg_rank;
-        D.tile_count = jtile_count;
-        D.tile_prefix = jtile_prefix;
-        D.tiles = jtile_rec;
-        D.total_out = d_viable + d;
-        D.vpos = h.vpos;
-        D.vnxt = h.vnxt;
-        D.vlast = h.vlast;
-        D.vseg = h.vseg;
-        const uint32_t T = D.total_slots;
-        if (T == 0) {
-            VLGB_CUDA(cudaMemsetAsync(h.vseg, 0, (h.nseg + 1) * 4, c.stream));
-            VLGB_CUDA(cudaMemsetAsync(d_viable + d, 0, 4, c.stream));
-            continue;
+        const uint32_t nf = (uint32_t)h.fmap.size(), nr = (uint32_t)h.rmap.size();
+        const uint32_t T = h.slot_off[nf];
+        VLGB_CUDA(cudaMemsetAsync(h.gseg, 0, (size_t)(h.nseg + 1) * 4, c.stream));  // segments no pass publishes are empty
+        VLGB_CUDA(cudaMemsetAsync(h.glen, 0, (size_t)(h.nseg + 1) * 4, c.stream));
+        if (nf && T) {
+            DepthDesc D;
+            D.nseg = nf;
+            D.total_slots = T;
+            D.slot_off = dev_at<const uint32_t>(d_ctl, h.o_slot_off);
+            D.left = dev_at<const uint32_t* const>(d_ctl, h.o_left);
+            D.right_list = d == 1 ? dev_at<const uint32_t* const>(d_ctl, h.o_right_list) : nullptr;
+            D.right_len = d == 1 ? dev_at<const uint32_t>(d_ctl, h.o_right_len) : nullptr;
+            D.prev_vpos = d > 1 ? dh[d - 1].vpos : nullptr;
+            D.prev_vlast = d > 1 ? dh[d - 1].vlast : nullptr;
+            D.prev_vseg = d > 1 ? dh[d - 1].gseg : nullptr;  // at depth > 1 segment i IS query i (fmap = identity)
+            D.prev_vlen = d > 1 ? dh[d - 1].glen : nullptr;
+            D.lo = dev_at<const uint64_t>(d_ctl, h.o_lo);
+            D.hi = dev_at<const uint64_t>(d_ctl, h.o_hi);
+            D.stage_x = stage_x;
+            D.stage_j = stage_j;
+            D.stage_last = stage_last;
+            D.seg_rank = seg_rank;
+            D.tile_count = jtile_count;
+            D.tile_prefix = jtile_prefix;
+            D.tiles = jtile_rec;
+            D.total_out = h.ftotal;
+            D.vpos = h.vpos;
+            D.vnxt = h.vnxt;
+            D.vlast = h.vlast;
+            D.vseg = h.vseg_f;
+            const uint32_t jtiles = (T + JF_TILE - 1) / JF_TILE;
+            uint64_t right_words = 0;
+            if (d == 1)
+                for (uint32_t s = 0; s < nf; s++) right_words += h.right_len[s];
+            c.begin(ST_JOIN_PROBE);
+            join_tileseg_kernel<<<(jtiles + 1 + 127) / 128, 128, 0, c.stream>>>(D, jtiles);
+            join_probe_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
+            c.end(ST_JOIN_PROBE, 2, (uint64_t)T * 4 + right_words * 4);  // + 12 B per viable slot staged, added below
+            c.begin(ST_JOIN_COMPACT);
+            const uint32_t l = exclusive_scan(ValueU32{jtile_count}, jtiles, jtile_prefix, scratch, c.stream);
+            join_vseg_kernel<<<(D.nseg + 1 + 255) / 256, 256, 0, c.stream>>>(D, jtiles);
+            join_compact_kernel<<<jtiles, JC_THREADS, 0, c.stream>>>(D);
+            join_publish_kernel<<<(nf + 1 + 255) / 256, 256, 0, c.stream>>>(h.vseg_f, dev_at<const uint32_t>(d_ctl, h.o_fmap), nf, nullptr,
+                                                                          h.gseg, h.glen, h.ftotal);
+            c.end(ST_JOIN_COMPACT, l + 3, (uint64_t)jtiles * 12);  // + 24 B per viable slot, added below
+        } else {
+            VLGB_CUDA(cudaMemsetAsync(h.ftotal, 0, 4, c.stream));
         }
-        const uint32_t jtiles = (T + JF_TILE - 1) / JF_TILE;
-        uint64_t right_words = 0;
-        if (d == 1)
-            for (uint32_t s = 0; s < h.nseg; s++) right_words += h.right_len[s];
-        c.begin(ST_JOIN_PROBE);
-        join_tileseg_kernel<<<(jtiles + 1 + 127) / 128, 128, 0, c.stream>>>(D, jtiles);
-        join_probe_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
-        c.end(ST_JOIN_PROBE, 2, (uint64_t)T * 4 + right_words * 4);  // + 12 B per viable slot staged, added below
-        c.begin(ST_JOIN_COMPACT);
-        const uint32_t l = exclusive_scan(ValueU32{jtile_count}, jtiles, jtile_prefix, scratch, c.stream);
-        join_vseg_kernel<<<(D.nseg + 1 + 255) / 256, 256, 0, c.stream>>>(D, jtiles);
-        join_compact_kernel<<<jtiles, JC_THREADS, 0, c.stream>>>(D);
-        c.end(ST_JOIN_COMPACT, l + 2, (uint64_t)jtiles * 12);  // + 24 B per viable slot, added below
+        const uint32_t RT = nr ? h.r_slot_off[nr] : 0;
+        if (nr && RT) {
+            RevDesc RD;
+            RD.nseg = nr;
+            RD.total_slots = RT;
+            RD.slot_off = dev_at<const uint32_t>(d_ctl, h.o_r_slot_off);
+            RD.left = dev_at<const uint32_t* const>(d_ctl, h.o_r_left);
+            RD.left_len = dev_at<const uint32_t>(d_ctl, h.o_r_left_len);
+            RD.right = dev_at<const uint32_t* const>(d_ctl, h.o_r_right);
+            RD.lo = dev_at<const uint64_t>(d_ctl, h.o_r_lo);
+            RD.hi = dev_at<const uint64_t>(d_ctl, h.o_r_hi);
+            RD.first = rev_first;
+            RD.count = rev_count;
+            RD.prefix = rev_prefix;
+            RD.base = h.ftotal;
+            RD.vpos = h.vpos;
+            RD.vnxt = h.vnxt;
+            RD.vlast = h.vlast;
+            c.begin(ST_JOIN_PROBE);
+            join_rev_count_kernel<<<(RT + 255) / 256, 256, 0, c.stream>>>(RD);
+            c.end(ST_JOIN_PROBE, 1, (uint64_t)RT * 12);
+            c.begin(ST_JOIN_COMPACT);
+            const uint32_t l = exclusive_scan(ValueU32{rev_count}, RT, rev_prefix, scratch, c.stream);
+            join_rev_vseg_kernel<<<(nr + 1 + 255) / 256, 256, 0, c.stream>>>(RD, h.vseg_r);
+            join_rev_expand_kernel<<<(RT + 255) / 256, 256, 0, c.stream>>>(RD);
+            join_publish_kernel<<<(nr + 1 + 255) / 256, 256, 0, c.stream>>>(h.vseg_r, dev_at<const uint32_t>(d_ctl, h.o_rmap), nr, h.ftotal,
+                                                                          h.gseg, h.glen, d_viable + d);
+            c.end(ST_JOIN_COMPACT, l + 3, (uint64_t)RT * 16);  // + 16 B per viable slot, added below
+        } else {
+            VLGB_CUDA(cudaMemcpyAsync(d_viable + d, h.ftotal, 4, cudaMemcpyDeviceToDevice, c.stream));
+        }
     }
 
     // ---- selection
@@ -580,6 +662,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.depth_vnxt = S.depth_vpos + MAX_K;
     S.depth_vlast = S.depth_vpos + 2 * MAX_K;
     S.depth_vseg = S.depth_vpos + 3 * MAX_K;
+    S.depth_vlen = S.depth_vpos + 4 * MAX_K;
     S.last_list = dev_at<const uint32_t* const>(d_ctl, o_last_list);
     S.global_offset = v.global_offset;
     S.sym_shift = v.sym_shift;

@@ -49,7 +49,8 @@ struct SelDesc {
     const uint32_t* const* depth_vpos;   // [MAX_K] by depth
     const uint32_t* const* depth_vnxt;
     const uint32_t* const* depth_vlast;
-    const uint32_t* const* depth_vseg;
+    const uint32_t* const* depth_vseg;   // [MAX_K][queries] first index of the query's segment at that depth
+    const uint32_t* const* depth_vlen;   // [MAX_K][queries] its length
     const uint32_t* const* last_list;    // scan list of the last subpattern (tuple resolve at depth 1)
     uint64_t global_offset;      // of the shard, in BYTES (symbol offset << sym_shift)
     uint32_t sym_shift;          // log2(bytes per symbol): 0 for byte texts; reported positions are >> sym_shift
@@ -95,10 +96,10 @@ __global__ void sel_resolve_kernel(SelDesc s)
         len = s.list0_len[q];
     } else {
         const uint32_t d = k - 1;
-        const uint32_t* seg = s.depth_vseg[d];
-        v = s.depth_vpos[d] + seg[q];
-        vl = s.depth_vlast[d] + seg[q];
-        len = seg[q + 1] - seg[q];
+        const uint32_t first = s.depth_vseg[d][q];
+        v = s.depth_vpos[d] + first;
+        vl = s.depth_vlast[d] + first;
+        len = s.depth_vlen[d][q];
     }
     s.v0[q] = v;
     s.vlast[q] = vl;
