@@ -186,22 +186,29 @@ __global__ void join_tileseg_kernel(DepthDesc d, uint32_t ntiles)
 }
 
 // lower_bound in shared memory, galloping from `from` (answers of consecutive slots are a few elements apart)
-__device__ __forceinline__ uint32_t smem_gallop(const uint32_t* w, uint32_t from, uint32_t len, uint64_t need)
+__device__ __forceinline__ uint32_t smem_gallop(const uint32_t* w, uint32_t from, uint32_t len, uint32_t need)
 {
-    if (from >= len || (uint64_t)w[from] >= need) return min(from, len);
+    if (from >= len || w[from] >= need) return min(from, len);
     uint32_t lo = from, step = 1, hi;  // w[lo] < need; answer in (lo, hi]
     for (;;) {
         const uint32_t nx = lo + step;
         if (nx >= len) { hi = len; break; }
-        if ((uint64_t)w[nx] >= need) { hi = nx; break; }
+        if (w[nx] >= need) { hi = nx; break; }
         lo = nx;
         step <<= 1;
     }
     while (hi - lo > 1) {
         const uint32_t mid = (lo + hi) >> 1;
-        if ((uint64_t)w[mid] >= need) hi = mid; else lo = mid;
+        if (w[mid] >= need) hi = mid; else lo = mid;
     }
     return hi;
+}
+
+// x + bound as a 32-bit value: list entries are < 2^32 - 4096, so anything larger compares like 0xFFFFFFFF
+__device__ __forceinline__ uint32_t clamp_add32(uint32_t x, uint64_t bound)
+{
+    const uint64_t v = x + bound;  // bound <= 2^33: no overflow
+    return v > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)v;
 }
 
 // A tile = JF_TILE consecutive slots, JF_ITEMS consecutive ones per thread.  Inside a tile of one segment the
@@ -261,12 +268,12 @@ __global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
 #pragma unroll
             for (int i = 0; i < JF_ITEMS; i++) {
                 if ((uint32_t)i >= live) break;
-                const uint64_t need = xs[i] + glo;
+                const uint32_t need = clamp_add32(xs[i], glo);
                 if (i == 0) {
                     uint32_t lo = 0, hi = wlen;
                     while (lo < hi) {
                         const uint32_t mid = (lo + hi) >> 1;
-                        if ((uint64_t)s_win[mid] < need) lo = mid + 1; else hi = mid;
+                        if (s_win[mid] < need) lo = mid + 1; else hi = mid;
                     }
                     at = lo;
                 } else {
@@ -275,22 +282,35 @@ __global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
                 js[i] = j_first + at;
                 if (at < wlen) {
                     ls[i] = s_win[at];
-                    if ((uint64_t)ls[i] <= xs[i] + ghi) okbits |= 1u << i;
+                    if (ls[i] <= clamp_add32(xs[i], ghi)) okbits |= 1u << i;
                 }
             }
         } else {
-            // warp-uniform branch: lane 0 gallops from the tile's first answer, the rest from lane 0's
-            uint32_t j0 = 0;
-            if (lane == 0 && live) j0 = gallop_lower_bound(R1, j_first, rlen1, xs[0] + glo);
-            j0 = __shfl_sync(0xffffffffu, j0, 0);
-            uint32_t at = j0;
+            // dense right list (window too large to stage): the thread's slots are searched in lock-step inside the
+            // tile's window, one independent load per slot and round -- dependent global loads are the cost here,
+            // and eight serial gallops per thread cost eight times the latency
+            const uint32_t* W = R1 + j_first;
+            uint32_t lo_[JF_ITEMS], hi_[JF_ITEMS];
+#pragma unroll
+            for (int i = 0; i < JF_ITEMS; i++) {
+                lo_[i] = 0;
+                hi_[i] = (uint32_t)i < live ? wlen : 0u;
+            }
+            for (uint32_t span = wlen; span; span >>= 1) {  // ceil(log2(wlen + 1)) rounds settle every slot
+#pragma unroll
+                for (int i = 0; i < JF_ITEMS; i++) {
+                    if (lo_[i] < hi_[i]) {
+                        const uint32_t mid = (lo_[i] + hi_[i]) >> 1;
+                        if ((uint64_t)__ldg(W + mid) < xs[i] + glo) lo_[i] = mid + 1; else hi_[i] = mid;
+                    }
+                }
+            }
 #pragma unroll
             for (int i = 0; i < JF_ITEMS; i++) {
                 if ((uint32_t)i >= live) break;
-                if (i > 0 || lane > 0) at = gallop_lower_bound(R1, at, rlen1, xs[i] + glo);
-                js[i] = at;
-                if (at < rlen1) {
-                    ls[i] = __ldg(R1 + at);
+                js[i] = j_first + lo_[i];
+                if (lo_[i] < wlen) {
+                    ls[i] = __ldg(W + lo_[i]);
                     if ((uint64_t)ls[i] <= xs[i] + ghi) okbits |= 1u << i;
                 }
             }

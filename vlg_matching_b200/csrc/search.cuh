@@ -320,10 +320,15 @@ inline uint64_t list_len(const BatchView& v, uint32_t sub, bool level0)
 
 // Depth 1 of a query is joined from the right when its last list is far shorter than the list to its left: two
 // binary searches per right element instead of one window search per left element (join.cuh, RevDesc).
-constexpr uint64_t JOIN_REV_FACTOR = 16;
+inline uint64_t join_rev_factor()
+{
+    static const uint64_t f = getenv("VLGB_REV_FACTOR") ? strtoull(getenv("VLGB_REV_FACTOR"), nullptr, 10) : 16;  // tuning hook
+    return f;
+}
 inline bool join_right_driven(const BatchView& v, const PlanQuery& pq)
 {
-    if (pq.k < 2) return false;
+    const uint64_t JOIN_REV_FACTOR = join_rev_factor();
+    if (pq.k < 2 || JOIN_REV_FACTOR == 0) return false;
     const uint64_t nl = list_len(v, pq.s0 + pq.k - 2, pq.k == 2), nr = list_len(v, pq.s0 + pq.k - 1, false);
     return nr * JOIN_REV_FACTOR < nl;
 }
