@@ -24,6 +24,8 @@
 // Algorithmic bytes per depth: 4 B per slot (x) + 4 B per right-list element read; per VIABLE slot 12 B staged,
 // 12 B read back (+ 4 B gather of the tuple end at depth > 1) and 12 B written.
 #pragma once
+#include <cuda_pipeline.h>
+
 #include "common.cuh"
 
 namespace vlgb {
@@ -220,7 +222,7 @@ __device__ __forceinline__ uint32_t clamp_add32(uint32_t x, uint64_t bound)
 // The viable slots are compacted INSIDE the tile (order kept) into stage_{x,j,last}[tile start + rank]: only
 // viable slots ever reach memory (a sixth of the slots on BASELINE config 2), join_compact_kernel then moves
 // tile_count[tile] records per tile to their final place.
-__global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
+__global__ void __launch_bounds__(JF_THREADS, 2) join_probe_kernel(DepthDesc d)
 {
     __shared__ uint32_t s_win[JF_WIN];
     __shared__ uint32_t s_wsum[32];
@@ -246,8 +248,10 @@ __global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
     }
     const bool use_win = single && wlen <= (uint32_t)JF_WIN;
     if (use_win) {
-        for (uint32_t i = tid; i < wlen; i += JF_THREADS) s_win[i] = __ldg(R1 + j_first + i);
-        __syncthreads();
+        // asynchronous global -> shared copies (LDGSTS): all of a thread's up to 16 requests are in flight at once
+        // instead of one load latency per loop trip; the left positions below are fetched while they land
+        for (uint32_t i = tid; i < wlen; i += JF_THREADS) __pipeline_memcpy_async(&s_win[i], R1 + j_first + i, 4);
+        __pipeline_commit();
     }
 
     // ---- probe
@@ -264,6 +268,8 @@ __global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
             segs[i] = seg_lo;
         }
         if (use_win) {
+            __pipeline_wait_prior(0);
+            __syncthreads();  // CTA-uniform branch: the window is complete
             uint32_t at = 0;
 #pragma unroll
             for (int i = 0; i < JF_ITEMS; i++) {
@@ -316,29 +322,53 @@ __global__ void __launch_bounds__(JF_THREADS, 3) join_probe_kernel(DepthDesc d)
             }
         }
     } else {
+        // tile with segment boundaries: every slot finds its own segment and searches that segment's whole right
+        // list in place -- all slots of the thread in lock-step, so that their dependent loads overlap
+        const uint32_t* Rs[JF_ITEMS];
+        uint32_t lo_[JF_ITEMS], hi_[JF_ITEMS], needs[JF_ITEMS], limits[JF_ITEMS];
+        uint32_t longest = 0;
 #pragma unroll
         for (int i = 0; i < JF_ITEMS; i++) {
             const uint32_t slot = sbase + i;
             segs[i] = seg_lo;
             xs[i] = 0;
+            Rs[i] = nullptr;
+            lo_[i] = hi_[i] = needs[i] = limits[i] = 0;
             if (slot >= slot0 + nslots) continue;
             const uint32_t seg = find_segment(d.slot_off, seg_lo, seg_hi, slot);
             segs[i] = seg;
-            const uint32_t* R;
-            uint32_t rlen;
             if (d.right_list) {
-                R = d.right_list[seg];
-                rlen = d.right_len[seg];
+                Rs[i] = d.right_list[seg];
+                hi_[i] = d.right_len[seg];
             } else {
-                R = d.prev_vpos + __ldg(d.prev_vseg + seg);
-                rlen = __ldg(d.prev_vlen + seg);
+                Rs[i] = d.prev_vpos + __ldg(d.prev_vseg + seg);
+                hi_[i] = __ldg(d.prev_vlen + seg);
             }
             xs[i] = __ldg(d.left[seg] + (slot - __ldg(d.slot_off + seg)));
-            const uint32_t j = full_lower_bound(R, rlen, sat_add64(xs[i], d.lo[seg]));
-            js[i] = j;
-            if (j < rlen) {
-                ls[i] = __ldg(R + j);
-                if ((uint64_t)ls[i] <= sat_add64(xs[i], d.hi[seg])) okbits |= 1u << i;
+            const uint64_t cap = 1ull << 33;
+            needs[i] = clamp_add32(xs[i], d.lo[seg] < cap ? d.lo[seg] : cap);
+            limits[i] = clamp_add32(xs[i], d.hi[seg] < cap ? d.hi[seg] : cap);
+            longest = max(longest, hi_[i]);
+        }
+        uint32_t rl[JF_ITEMS];
+#pragma unroll
+        for (int i = 0; i < JF_ITEMS; i++) rl[i] = hi_[i];
+        for (uint32_t span = longest; span; span >>= 1) {
+#pragma unroll
+            for (int i = 0; i < JF_ITEMS; i++) {
+                if (lo_[i] < hi_[i]) {
+                    const uint32_t mid = (lo_[i] + hi_[i]) >> 1;
+                    if (__ldg(Rs[i] + mid) < needs[i]) lo_[i] = mid + 1; else hi_[i] = mid;
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < JF_ITEMS; i++) {
+            if (sbase + i >= slot0 + nslots) break;
+            js[i] = lo_[i];
+            if (lo_[i] < rl[i]) {
+                ls[i] = __ldg(Rs[i] + lo_[i]);
+                if (ls[i] <= limits[i]) okbits |= 1u << i;
             }
         }
     }
