@@ -223,6 +223,30 @@ def test_repeated_reentry_equals_fresh_search(V):
             assert np.array_equal(r.tuples(q), tup[q]), (q, queries[q])
 
 
+@pytest.mark.parametrize("cfg", [3, 5])
+def test_large_dna_configs_vs_oracle(V, cfg):
+    """Configs 3 (three subpatterns, mixed gaps, two scan passes) and 5 (occurrence lists > 10^7, several query
+    chunks) on a 256 MiB slice of the DNA text: counts of ALL queries are consistent between count-only and
+    start-producing runs, and the match starts of a sample equal the oracle's.  (tools/full_config_check.py runs
+    the same at the full 1 GiB.)"""
+    from vlg_matching_b200 import capi, synth
+    text = synth.make_text(cfg, 256 << 20)
+    queries = synth.make_queries(cfg, text)
+    idx = V.Index.build(text)
+    r = idx.search(V.PackedBatch(queries), capi.WANT_COUNT)
+    gc = r.counts().copy()
+    st = capi.last_stats()
+    assert st["total_occurrences"] > (10**7 if cfg == 5 else 10**6)
+    r.free()
+    sample = list(range(0, len(queries), len(queries) // 4))[:4]
+    qs = [queries[i] for i in sample]
+    oc = O.search(text, qs, want_tuples=False, threads=2)
+    rb = idx.search(V.PackedBatch(qs), capi.WANT_STARTS)
+    for k, i in enumerate(sample):
+        assert int(gc[i]) == len(oc[k][1]) == int(rb.counts()[k]), (cfg, i)
+        assert np.array_equal(rb.starts(k), oc[k][1]), (cfg, i)
+
+
 def test_full_size_properties_config2(V):
     """Config 2 at full size (200 MiB, 1000 queries): size-independent properties instead of the oracle:
     every reported tuple really occurs in the text with gaps inside bounds, starts strictly ascending and
