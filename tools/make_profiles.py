@@ -24,8 +24,8 @@ def g(name):
     for kk, v in k.items():
         if name in kk: return sum(v) / len(v)
     return None
-stage = {"scan_count": g("scan_kernel"), "scan_fill": g("scan_scatter"), "join_probe": g("join_probe"),
-         "join_compact": g("join_compact"), "select_tile": (g("sel_succ") or 0) + (g("sel_tile") or 0),
+stage = {"scan_count": g("scan_kernel"), "scan_fill": g("scan_scatter"), "join_probe": (g("join_probe") or 0) + (g("join_rev_count") or 0),
+         "join_compact": (g("join_compact") or 0) + (g("join_rev_expand") or 0), "select_tile": (g("sel_succ") or 0) + (g("sel_tile") or 0),
          "select_walk": g("sel_mark"), "emit": g("sel_emit")}
 json.dump({"source": f"profiles/{tag}_full_summary.txt (dram__bytes_read.sum + dram__bytes_write.sum per launch)", **stage},
           open(os.path.join(pr, "traffic.json"), "w"), indent=1)
