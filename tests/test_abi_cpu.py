@@ -105,3 +105,21 @@ def test_parse_batch_equals_per_query_parse():
             assert gmin[s_] == ref.gmin[s_] and gmax[s_] == ref.gmax[s_]
     with pytest.raises(capi.VlgbError):
         capi.ParsedBatch(qs, capi.SYNTAX_BENCHMARK)  # strict: the bad query fails the call
+
+
+def test_product_never_touches_the_oracle():
+    """oracle/ is test infrastructure: nothing under vlg_matching_b200/ (Python, CUDA, C++ host code) may import,
+    include, link or execute it, and the Python package must fail loudly without the CUDA library."""
+    pkg = os.path.join(ROOT, "vlg_matching_b200")
+    offenders = []
+    for d, _, files in os.walk(pkg):
+        if "__pycache__" in d:
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".hpp", ".cpp", ".h", "Makefile")):
+                text = open(os.path.join(d, f), errors="replace").read()
+                if re.search(r"\boracle\b|pyoracle|vlgo_|_ref/", text):
+                    offenders.append(os.path.relpath(os.path.join(d, f), ROOT))
+    assert offenders == [], offenders
+    src = open(os.path.join(pkg, "capi.py")).read()
+    assert "raise" in src and "libvlgb200.so" in src  # import fails when the extension is missing
