@@ -123,12 +123,8 @@ __device__ __forceinline__ uint32_t sel_hop(const uint32_t* ptr, uint32_t p, uin
 // succ[slot] for every viable start of every query: one thread per slot, gallop from t + 1.
 __global__ void __launch_bounds__(256) sel_succ_kernel(SelDesc s)
 {
-    __shared__ uint32_t s_q;
     const uint32_t tile = blockIdx.x / (SEL_TILE / 256);
-    const uint32_t slot0 = tile * SEL_TILE;
-    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
-    __syncthreads();
-    const uint32_t q = s_q;
+    const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);  // same word for the whole CTA: one L1 line
     const uint32_t slot = blockIdx.x * 256 + threadIdx.x;
     const uint32_t t = slot - s.sel_off[q];  // V_0 index
     const uint32_t len = s.v0_len[q];
@@ -287,17 +283,19 @@ __global__ void sel_counts_kernel(SelDesc s)
 
 __global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
 {
-    __shared__ uint32_t s_q;
     const uint32_t slot0 = blockIdx.x * SEL_TILE;
-    if (s.entry[blockIdx.x] == NONE32) return;
-    if (threadIdx.x == 0) s_q = sel_query_of_tile(s, slot0);
-    __syncthreads();
-    const uint32_t q = s_q;
-    const uint32_t slot = slot0 + threadIdx.x;
-    const uint32_t t = slot - s.sel_off[q];
-    // rank of the element = matches of earlier tiles + of earlier warps of this tile + of earlier lanes
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // independent loads first (every thread reads the same few words: one L1 line each), then what depends on q
+    const uint32_t entered = s.entry[blockIdx.x];
+    const uint32_t q = sel_query_of_tile(s, slot0);
     const uint32_t wbits = s.flagbits[blockIdx.x * 32 + lane];  // lane l holds warp l's bits
+    const uint32_t tile_base = s.tile_prefix[blockIdx.x];
+    if (entered == NONE32) return;
+    const uint32_t off = s.sel_off[q], off_end = s.sel_off[q + 1];
+    const uint32_t* v0 = s.v0[q];
+    const uint32_t slot = slot0 + threadIdx.x;
+    const uint32_t t = slot - off;
+    // rank of the element = matches of earlier tiles + of earlier warps of this tile + of earlier lanes
     uint32_t inc = __popc(wbits);
 #pragma unroll
     for (int dd = 1; dd < 32; dd <<= 1) {
@@ -307,11 +305,11 @@ __global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
     const uint32_t before = __shfl_sync(0xffffffffu, inc - __popc(wbits), warp);
     const uint32_t bits = __shfl_sync(0xffffffffu, wbits, warp);
     if (!((bits >> lane) & 1u)) return;
-    const uint32_t o = s.tile_prefix[blockIdx.x] + before + __popc(bits & ((1u << lane) - 1u));
-    const uint32_t qfirst = s.tile_prefix[s.sel_off[q] / SEL_TILE];
-    const uint32_t qend = s.tile_prefix[s.sel_off[q + 1] / SEL_TILE];
+    const uint32_t o = tile_base + before + __popc(bits & ((1u << lane) - 1u));
+    const uint32_t x = __ldg(v0 + t);
+    const uint32_t qfirst = s.tile_prefix[off / SEL_TILE];
+    const uint32_t qend = s.tile_prefix[off_end / SEL_TILE];
     const uint32_t k = s.kq[q];
-    const uint32_t x = __ldg(s.v0[q] + t);
     const uint64_t g = s.global_offset;
     const uint32_t sh = s.sym_shift;
     if (s.starts) s.starts[o] = (g + x) >> sh;
