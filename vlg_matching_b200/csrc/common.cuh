@@ -156,7 +156,24 @@ struct Context {
     Arena list_arena;    // occurrence lists of the current segment
     Arena join_arena;    // per-chunk join / selection state
     DeviceBuffer out_buf; // starts / tuples of the current chunk before they go to the host
-    PinnedBuffer pinned; // small host staging
+    PinnedBuffer pinned; // small host staging: control blobs on their way up, sizes / counters on their way down
+    size_t stage_used = 0;
+    struct PendingD2H {
+        void* host;
+        const void* pinned;
+        size_t bytes;
+    };
+    std::vector<PendingD2H> pending;
+    static constexpr size_t STAGE_BYTES = 8u << 20;
+    // bump allocation inside the pinned block; nullptr when the block is full (the caller then copies directly)
+    void* stage_take(size_t bytes)
+    {
+        if (!pinned.p) pinned.get(STAGE_BYTES);
+        const size_t at = (stage_used + 63) & ~size_t(63);
+        if (at + bytes > pinned.cap) return nullptr;
+        stage_used = at + bytes;
+        return static_cast<char*>(pinned.p) + at;
+    }
     // timers
     cudaEvent_t ev[2 * 512] = {};
     bool ev_ready = false;
@@ -235,6 +252,36 @@ __host__ __device__ inline uint64_t sat_shl64(uint64_t a, uint32_t sh)
 }
 
 constexpr uint32_t NONE32 = 0xFFFFFFFFu;
+
+// Small host<->device copies go through pinned memory: a copy from/to pageable memory is staged by the driver
+// synchronously (tens of microseconds each, a dozen per search).
+inline void h2d(Context& c, void* dst, const void* src, size_t bytes)
+{
+    if (!bytes) return;
+    void* p = c.stage_take(bytes);
+    if (p) {
+        memcpy(p, src, bytes);
+        src = p;
+    }
+    VLGB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream));
+}
+inline void d2h(Context& c, void* host_dst, const void* dev_src, size_t bytes)  // lands in host_dst at the next sync_stream()
+{
+    if (!bytes) return;
+    void* p = c.stage_take(bytes);
+    if (p) {
+        VLGB_CUDA(cudaMemcpyAsync(p, dev_src, bytes, cudaMemcpyDeviceToHost, c.stream));
+        c.pending.push_back({host_dst, p, bytes});
+    } else {
+        VLGB_CUDA(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, c.stream));
+    }
+}
+inline void sync_stream(Context& c)
+{
+    VLGB_CUDA(cudaStreamSynchronize(c.stream));
+    for (auto& d : c.pending) memcpy(d.host, d.pinned, d.bytes);
+    c.pending.clear();
+}
 
 // Host wall-clock trace of one search call (VLGB_TRACE=1 in the environment; stderr).  Measurement only.
 struct HostTrace {

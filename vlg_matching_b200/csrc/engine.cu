@@ -604,6 +604,10 @@ extern "C" int vlgb_search_batch(const vlgb_index* idx, const vlgb_batch* batch,
         memset(&c.stats, 0, sizeof c.stats);
         c.serial++;
         retained().valid = false;
+        if (c.stage_used) {  // the pinned staging block is reused: nothing of the previous call may still be in flight
+            sync_stream(c);
+            c.stage_used = 0;
+        }
         std::unique_ptr<ResultImpl> R(new ResultImpl());
         try {
             do_search(c, idx, batch, entry_cursor, want, *R);

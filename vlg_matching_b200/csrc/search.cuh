@@ -153,7 +153,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     trace().mark("scan: tables built");
     c.scan_arena.reserve(ctl.size() + work_bytes + 4096);
     uint8_t* d_ctl = c.scan_arena.take<uint8_t>(ctl.size());
-    VLGB_CUDA(cudaMemcpyAsync(d_ctl, ctl.host.data(), ctl.host.size(), cudaMemcpyHostToDevice, c.stream));
+    h2d(c, d_ctl, ctl.host.data(), ctl.host.size());
     c.stats.h2d_bytes += ctl.host.size();
     for (uint32_t p = 0; p < npass; p++) {
         pd[p].matrix = c.scan_arena.take<uint32_t>((size_t)rows * pd[p].stride);
@@ -213,14 +213,13 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         scan_colbase_kernel<<<(pd[p].stride + 127) / 128, 128, 0, c.stream>>>(pd[p].part, nrb, pd[p].stride, pd[p].total);
         scan_rowoff_kernel<<<g, 128, 0, c.stream>>>(pd[p].matrix, rows, pd[p].stride, pd[p].part);
         c.end(ST_SCAN_OFFSETS, 3, (uint64_t)rows * pd[p].stride * 12);
-        VLGB_CUDA(cudaMemcpyAsync(so.tot.data() + p * SCAN_S, pd[p].total, pd[p].s_act * 4, cudaMemcpyDeviceToHost,
-                                  c.stream));
+        d2h(c, so.tot.data() + p * SCAN_S, pd[p].total, pd[p].s_act * 4);
         c.stats.d2h_bytes += pd[p].s_act * 4;
     }
-    VLGB_CUDA(cudaMemcpyAsync(overflow.data(), d_overflow, (size_t)npass * 4, cudaMemcpyDeviceToHost, c.stream));
+    d2h(c, overflow.data(), d_overflow, (size_t)npass * 4);
     VLGB_CUDA(cudaGetLastError());
     trace().mark("scan: pass 1 launched");
-    VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync 1: list sizes
+    sync_stream(c);  // sync 1: list sizes
     trace().mark("scan: sync 1");
 
     uint64_t words = 0;
@@ -233,9 +232,8 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     c.list_arena.reserve(words * 4 + 4096);
     so.d_lists = c.list_arena.take<uint32_t>(words + 16);
     for (uint32_t p = 0; p < npass; p++)
-        VLGB_CUDA(cudaMemcpyAsync(d_ctl + pd[p].o_base, so.base.data() + p * SCAN_S, pd[p].s_act * 8,
-                                  cudaMemcpyHostToDevice, c.stream));
-    VLGB_CUDA(cudaMemcpyAsync(d_ctl + o_allbase, so.base.data(), (P + 1) * 8, cudaMemcpyHostToDevice, c.stream));
+        h2d(c, d_ctl + pd[p].o_base, so.base.data() + p * SCAN_S, pd[p].s_act * 8);
+    h2d(c, d_ctl + o_allbase, so.base.data(), (P + 1) * 8);
     c.stats.h2d_bytes += (uint64_t)P * 16 + 8;
 
     // pass 2: fill
@@ -275,12 +273,12 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     } else {
         // totals of all patterns, contiguous on the device for the owned-prefix search
         uint32_t* d_tot = c.scan_arena.take<uint32_t>(P);
-        VLGB_CUDA(cudaMemcpyAsync(d_tot, so.tot.data(), (size_t)P * 4, cudaMemcpyHostToDevice, c.stream));
+        h2d(c, d_tot, so.tot.data(), (size_t)P * 4);
         scan_owned_kernel<<<(P + 127) / 128, 128, 0, c.stream>>>(so.d_lists, dev_at<const uint64_t>(d_ctl, o_allbase), d_tot,
                                                                  P, (uint32_t)owned_len, d_owned);
-        VLGB_CUDA(cudaMemcpyAsync(so.own.data(), d_owned, (size_t)P * 4, cudaMemcpyDeviceToHost, c.stream));
+        d2h(c, so.own.data(), d_owned, (size_t)P * 4);
         VLGB_CUDA(cudaGetLastError());
-        VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync 2 (sharded texts only)
+        sync_stream(c);  // sync 2 (sharded texts only)
         c.stats.h2d_bytes += (uint64_t)P * 4;
         c.stats.d2h_bytes += (uint64_t)P * 4;
     }
@@ -564,7 +562,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     uint32_t* d_viable = A.take<uint32_t>(kmax + 1);
     uint32_t* scratch = A.take<uint32_t>(scratch_words);
 
-    VLGB_CUDA(cudaMemcpyAsync(d_ctl, ctl.host.data(), ctl.host.size(), cudaMemcpyHostToDevice, c.stream));
+    h2d(c, d_ctl, ctl.host.data(), ctl.host.size());
     c.stats.h2d_bytes += ctl.host.size();
 
     // ---- join, depth by depth: a left-driven pass over the segments of fmap, then (depth 1) a right-driven pass
@@ -708,10 +706,10 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         c.begin(ST_SELECT_SUCC);
         sel_resolve_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
         c.end(ST_SELECT_SUCC, 1, (uint64_t)nq * 32);
-        VLGB_CUDA(cudaMemcpyAsync(v0_len.data(), d_v0_len, (size_t)nq * 4, cudaMemcpyDeviceToHost, c.stream));
+        d2h(c, v0_len.data(), d_v0_len, (size_t)nq * 4);
         VLGB_CUDA(cudaGetLastError());
         trace().mark("chunk: join launched");
-        VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: viable-start counts
+        sync_stream(c);  // sync: viable-start counts
         trace().mark("chunk: sync viable");
         c.stats.d2h_bytes += (uint64_t)nq * 4;
     }
@@ -738,7 +736,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         Packer ctl2;
         const size_t o_sel_off = ctl2.put(sel_off), o_q_chunk0 = ctl2.put(q_chunk0), o_chunk_q = ctl2.put(chunk_q),
                      o_chunk_tile0 = ctl2.put(chunk_tile0), o_tile_q = ctl2.put(tile_q);
-        VLGB_CUDA(cudaMemcpyAsync(d_ctl2, ctl2.host.data(), ctl2.host.size(), cudaMemcpyHostToDevice, c.stream));
+        h2d(c, d_ctl2, ctl2.host.data(), ctl2.host.size());
         c.stats.h2d_bytes += ctl2.host.size();
         S.total_slots = sel_total;
         S.sel_off = dev_at<const uint32_t>(d_ctl2, o_sel_off);
@@ -764,12 +762,12 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         uint32_t l = exclusive_scan(ValueU32{d_tile_count}, ntiles, d_tile_prefix, scratch, c.stream);
         sel_counts_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
         c.end(ST_EMIT, l + 1, (uint64_t)ntiles * 12);
-        VLGB_CUDA(cudaMemcpyAsync(co.counts.data(), d_counts, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+        d2h(c, co.counts.data(), d_counts, (size_t)nq * 8);
         if (kmax > 1)
-            VLGB_CUDA(cudaMemcpyAsync(viable.data(), d_viable, (size_t)(kmax + 1) * 4, cudaMemcpyDeviceToHost, c.stream));
+            d2h(c, viable.data(), d_viable, (size_t)(kmax + 1) * 4);
         VLGB_CUDA(cudaGetLastError());
         trace().mark("chunk: select launched");
-        VLGB_CUDA(cudaStreamSynchronize(c.stream));  // sync: match counts
+        sync_stream(c);  // sync: match counts
         trace().mark("chunk: sync counts");
         c.stats.d2h_bytes += (uint64_t)nq * 8 + (kmax + 1) * 4;
         for (uint32_t d = 1; d < kmax; d++)  // viable slots written; deeper levels read the previous viable list
@@ -799,8 +797,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             }
             if (want_tuples) {
                 d_tuples = (uint64_t*)o;
-                VLGB_CUDA(cudaMemcpyAsync(d_ctl + o_tuple_off, co.tuple_off.data(), (size_t)nq * 8, cudaMemcpyHostToDevice,
-                                          c.stream));
+                h2d(c, d_ctl + o_tuple_off, co.tuple_off.data(), (size_t)nq * 8);
                 c.stats.h2d_bytes += (uint64_t)nq * 8;
             }
             S.starts = d_starts;
@@ -808,8 +805,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             c.begin(ST_EMIT);
             sel_emit_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
             c.end(ST_EMIT, 1, co.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? co.tuple_words * 12 : 0));
-            VLGB_CUDA(cudaMemcpyAsync(co.exit_cursor.data(), S.exit_cursor, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
-            VLGB_CUDA(cudaMemcpyAsync(co.first_start.data(), S.first_start, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+            d2h(c, co.exit_cursor.data(), S.exit_cursor, (size_t)nq * 8);
+            d2h(c, co.first_start.data(), S.first_start, (size_t)nq * 8);
             c.stats.d2h_bytes += (uint64_t)nq * 16;
             if (!keep_device && (want_starts || want_tuples)) {
                 size_t hb = (want_starts ? co.matches * 8 : 0) + (want_tuples ? co.tuple_words * 8 : 0);
@@ -827,7 +824,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
                 }
             }
             VLGB_CUDA(cudaGetLastError());
-            VLGB_CUDA(cudaStreamSynchronize(c.stream));
+            sync_stream(c);
             trace().mark("chunk: emit + copies done");
         }
         Retained& T = retained();
