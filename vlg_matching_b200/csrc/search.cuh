@@ -865,8 +865,8 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     const size_t o_q = 0, o_e = Arena::padded(nr, 4), o_flag = o_e + Arena::padded(nr, 8), o_exit = o_flag + Arena::padded(nq, 4),
                  o_first = o_exit + Arena::padded(nq, 8), total = o_first + Arena::padded(nq, 8);
     uint8_t* fb = (uint8_t*)T.fix_buf.get(total);
-    VLGB_CUDA(cudaMemcpyAsync(fb + o_q, redo.data(), (size_t)nr * 4, cudaMemcpyHostToDevice, c.stream));
-    VLGB_CUDA(cudaMemcpyAsync(fb + o_e, entry_local.data(), (size_t)nr * 8, cudaMemcpyHostToDevice, c.stream));
+    h2d(c, fb + o_q, redo.data(), (size_t)nr * 4);
+    h2d(c, fb + o_e, entry_local.data(), (size_t)nr * 8);
     VLGB_CUDA(cudaMemsetAsync(fb + o_flag, 0, (size_t)nq * 4, c.stream));
     VLGB_CUDA(cudaMemsetAsync(fb + o_first, 0xFF, (size_t)nq * 8, c.stream));
     c.stats.h2d_bytes += (uint64_t)nr * 12;
@@ -888,9 +888,9 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     sel_counts_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
     c.end(ST_EMIT, l + 1, (uint64_t)T.ntiles * 12);
     std::vector<uint64_t> all_counts(nq, 0);
-    VLGB_CUDA(cudaMemcpyAsync(all_counts.data(), T.d_counts, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+    d2h(c, all_counts.data(), T.d_counts, (size_t)nq * 8);
     VLGB_CUDA(cudaGetLastError());
-    VLGB_CUDA(cudaStreamSynchronize(c.stream));
+    sync_stream(c);
     c.stats.d2h_bytes += (uint64_t)nq * 8;
 
     ro.counts.assign(nr, 0);
@@ -919,7 +919,7 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     }
     if (want_tuples) {
         d_tuples = (uint64_t*)o;
-        VLGB_CUDA(cudaMemcpyAsync(T.d_tuple_off, tuple_off_all.data(), (size_t)nq * 8, cudaMemcpyHostToDevice, c.stream));
+        h2d(c, T.d_tuple_off, tuple_off_all.data(), (size_t)nq * 8);
         c.stats.h2d_bytes += (uint64_t)nq * 8;
     }
     S.starts = d_starts;
@@ -928,8 +928,8 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     sel_emit_kernel<<<T.ntiles, SEL_TILE, 0, c.stream>>>(S);
     c.end(ST_EMIT, 1, ro.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? ro.tuple_words * 12 : 0));
     std::vector<uint64_t> ex(nq), fs(nq);
-    VLGB_CUDA(cudaMemcpyAsync(ex.data(), S.exit_cursor, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
-    VLGB_CUDA(cudaMemcpyAsync(fs.data(), S.first_start, (size_t)nq * 8, cudaMemcpyDeviceToHost, c.stream));
+    d2h(c, ex.data(), S.exit_cursor, (size_t)nq * 8);
+    d2h(c, fs.data(), S.first_start, (size_t)nq * 8);
     c.stats.d2h_bytes += (uint64_t)nq * 16;
     if (!keep_device && (want_starts || want_tuples)) {
         size_t hb = (want_starts ? ro.matches * 8 : 0) + (want_tuples ? ro.tuple_words * 8 : 0);
@@ -947,7 +947,7 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
         }
     }
     VLGB_CUDA(cudaGetLastError());
-    VLGB_CUDA(cudaStreamSynchronize(c.stream));
+    sync_stream(c);
     for (uint32_t i = 0; i < nr; i++) {
         if (!ro.counts[i]) continue;
         ro.exit_cursor[i] = ex[redo[i]];

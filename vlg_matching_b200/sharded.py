@@ -94,10 +94,21 @@ class ShardedSearcher:
         if self.world == 1:
             return arr[None].copy()
         import torch
-        t = torch.from_numpy(arr.view(np.int64)).to(self.device)
-        out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=self.device)
-        self.dist.all_gather_into_tensor(out, t)
-        return out.cpu().numpy().view(np.uint64)
+        # persistent pinned host + device buffers: two async copies and one NCCL call, no allocation per step
+        key = arr.shape
+        if getattr(self, "_ag_key", None) != key:
+            n = int(np.prod(arr.shape))
+            self._ag_host_in = torch.empty(n, dtype=torch.int64).pin_memory()
+            self._ag_host_out = torch.empty(self.world * n, dtype=torch.int64).pin_memory()
+            self._ag_dev_in = torch.empty(n, dtype=torch.int64, device=self.device)
+            self._ag_dev_out = torch.empty(self.world * n, dtype=torch.int64, device=self.device)
+            self._ag_key = key
+        self._ag_host_in.numpy()[:] = arr.reshape(-1).view(np.int64)
+        self._ag_dev_in.copy_(self._ag_host_in, non_blocking=True)
+        self.dist.all_gather_into_tensor(self._ag_dev_out, self._ag_dev_in)
+        self._ag_host_out.copy_(self._ag_dev_out, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return self._ag_host_out.numpy().view(np.uint64).reshape((self.world,) + tuple(arr.shape)).copy()
 
     def _broadcast(self, arr, src):
         import torch
