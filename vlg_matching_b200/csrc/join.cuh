@@ -7,10 +7,11 @@
 //
 // One "depth" d = k-1-i is processed per launch set for ALL queries of the chunk that have such a level.
 // The slots of a depth are the concatenation of the left lists (one segment per query), cut into tiles of
-// 4096 slots, 4 consecutive slots per thread:
+// 2048 slots (256 threads x 8 consecutive slots; a tile costs a fixed ~10 us of dependent memory latency whatever its
+// size, so many small tiles in flight beat few large ones):
 //   probe   : j = lower_bound(V_right, x + lo); viable iff V_right[j] <= x + hi.  Viable slots are compacted
 //             inside the tile (order kept) into a staging area; viable count per tile
-//   prefix  : exclusive scan of the tile counts (prefix.cuh; ~1 value per 4096 slots)
+//   prefix  : exclusive scan of the tile counts (prefix.cuh; ~1 value per 2048 slots)
 //   vseg    : vseg[seg] = rank of the segment's first slot, so that every query finds its segment inside the
 //             compacted arrays and no size ever has to travel to the host between depths
 //   compact : vpos / vnxt / vlast [tile prefix + i] = staged x / j / last position of the tuple
@@ -71,6 +72,7 @@ struct DepthDesc {
     uint32_t* tile_count;        // [tiles] viable slots per tile
     const uint32_t* tile_prefix; // [tiles+1] exclusive scan of tile_count
     JoinTile* tiles;             // [tiles+1] per-tile records (join_tileseg_kernel); the last one is a sentinel
+    unsigned long long* dbg;     // measurement hook (VLGB_JOIN_DEBUG): per tile kind {sum of ns, tiles}, else nullptr
     uint32_t* total_out;         // number of viable slots of the depth
     uint32_t* vpos;              // [total_slots] compacted
     uint32_t* vnxt;
@@ -141,7 +143,7 @@ __device__ __forceinline__ uint32_t warp_lower_bound(const uint32_t* __restrict_
     return b ? min(hi, lo + (uint32_t)__ffs(b) - 1u) : hi;
 }
 
-constexpr int JF_THREADS = 512;
+constexpr int JF_THREADS = 256;
 constexpr int JF_ITEMS = 8;                          // CONSECUTIVE slots per thread
 constexpr int JF_TILE = JF_THREADS * JF_ITEMS;       // slots per tile
 constexpr int JF_WIN = 8192;                         // right-list window staged in shared memory (elements)
@@ -222,7 +224,7 @@ __device__ __forceinline__ uint32_t clamp_add32(uint32_t x, uint64_t bound)
 // The viable slots are compacted INSIDE the tile (order kept) into stage_{x,j,last}[tile start + rank]: only
 // viable slots ever reach memory (a sixth of the slots on BASELINE config 2), join_compact_kernel then moves
 // tile_count[tile] records per tile to their final place.
-__global__ void __launch_bounds__(JF_THREADS, 2) join_probe_kernel(DepthDesc d)
+__global__ void __launch_bounds__(JF_THREADS, 4) join_probe_kernel(DepthDesc d)
 {
     __shared__ uint32_t s_win[JF_WIN];
     __shared__ uint32_t s_wsum[32];
@@ -230,6 +232,8 @@ __global__ void __launch_bounds__(JF_THREADS, 2) join_probe_kernel(DepthDesc d)
     const uint32_t tile = blockIdx.x;
     const uint32_t slot0 = tile * JF_TILE;
     const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot0);
+    unsigned long long dbg_t0 = 0;
+    if (d.dbg && tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_t0));
     const JoinTile jt = d.tiles[tile], jn = d.tiles[tile + 1];  // two independent 64-byte loads
     const uint32_t seg_lo = jt.seg;  // segment of the tile's first slot
     // upper bound for the segment searches of this tile's slots: the segment of the next tile's first slot
@@ -418,6 +422,13 @@ __global__ void __launch_bounds__(JF_THREADS, 2) join_probe_kernel(DepthDesc d)
             if (d.right_list) d.stage_last[slot0 + rank] = ls[i];  // deeper levels gather the tuple's end later
             rank++;
         }
+    }
+    if (d.dbg && tid == 0) {
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+        const int kind = !single ? 2 : (use_win ? 0 : 1);
+        atomicAdd(d.dbg + kind * 2, t1 - dbg_t0);
+        atomicAdd(d.dbg + kind * 2 + 1, 1ull);
     }
 }
 

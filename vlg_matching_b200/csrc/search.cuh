@@ -594,6 +594,13 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             D.tile_count = jtile_count;
             D.tile_prefix = jtile_prefix;
             D.tiles = jtile_rec;
+            D.dbg = nullptr;
+            static const bool join_debug = getenv("VLGB_JOIN_DEBUG") != nullptr;
+            static thread_local DeviceBuffer dbg_buf;
+            if (join_debug) {
+                D.dbg = (unsigned long long*)dbg_buf.get(64);
+                VLGB_CUDA(cudaMemsetAsync(D.dbg, 0, 48, c.stream));
+            }
             D.total_out = h.ftotal;
             D.vpos = h.vpos;
             D.vnxt = h.vnxt;
@@ -607,6 +614,15 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             join_tileseg_kernel<<<(jtiles + 1 + 127) / 128, 128, 0, c.stream>>>(D, jtiles);
             join_probe_kernel<<<jtiles, JF_THREADS, 0, c.stream>>>(D);
             c.end(ST_JOIN_PROBE, 2, (uint64_t)T * 4 + right_words * 4);  // + 12 B per viable slot staged, added below
+            if (D.dbg) {
+                unsigned long long h[6];
+                VLGB_CUDA(cudaMemcpyAsync(h, D.dbg, 48, cudaMemcpyDeviceToHost, c.stream));
+                VLGB_CUDA(cudaStreamSynchronize(c.stream));
+                const char* names[3] = {"window", "dense", "multi-segment"};
+                for (int i = 0; i < 3; i++)
+                    fprintf(stderr, "[vlgb join] depth %u %-14s tiles %8llu  mean %8.1f us  sum %10.1f us\n", d, names[i], h[2 * i + 1],
+                            h[2 * i + 1] ? h[2 * i] / 1e3 / h[2 * i + 1] : 0.0, h[2 * i] / 1e3);
+            }
             c.begin(ST_JOIN_COMPACT);
             const uint32_t l = exclusive_scan(ValueU32{jtile_count}, jtiles, jtile_prefix, scratch, c.stream);
             join_vseg_kernel<<<(D.nseg + 1 + 255) / 256, 256, 0, c.stream>>>(D, jtiles);
