@@ -274,27 +274,26 @@ __global__ void __launch_bounds__(JF_THREADS, 4) join_probe_kernel(DepthDesc d)
         if (use_win) {
             __pipeline_wait_prior(0);
             __syncthreads();  // CTA-uniform branch: the window is complete
-            uint32_t at = 0;
+            // first slot: binary search; the others gallop on from their left neighbour's answer.  Dead slots of
+            // the last tile carry x = 0 and are masked out of okbits at the end (no per-slot liveness branches)
+            uint32_t at;
+            {
+                const uint32_t need = clamp_add32(xs[0], glo);
+                uint32_t lo = 0, hi = wlen;
+                while (lo < hi) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (s_win[mid] < need) lo = mid + 1; else hi = mid;
+                }
+                at = lo;
+            }
 #pragma unroll
             for (int i = 0; i < JF_ITEMS; i++) {
-                if ((uint32_t)i >= live) break;
-                const uint32_t need = clamp_add32(xs[i], glo);
-                if (i == 0) {
-                    uint32_t lo = 0, hi = wlen;
-                    while (lo < hi) {
-                        const uint32_t mid = (lo + hi) >> 1;
-                        if (s_win[mid] < need) lo = mid + 1; else hi = mid;
-                    }
-                    at = lo;
-                } else {
-                    at = smem_gallop(s_win, at, wlen, need);
-                }
+                if (i > 0) at = smem_gallop(s_win, at, wlen, clamp_add32(xs[i], glo));
                 js[i] = j_first + at;
-                if (at < wlen) {
-                    ls[i] = s_win[at];
-                    if (ls[i] <= clamp_add32(xs[i], ghi)) okbits |= 1u << i;
-                }
+                ls[i] = s_win[min(at, (uint32_t)JF_WIN - 1)];
+                if (at < wlen && ls[i] <= clamp_add32(xs[i], ghi)) okbits |= 1u << i;
             }
+            okbits &= (1u << live) - 1u;
         } else {
             // dense right list (window too large to stage): the thread's slots are searched in lock-step inside the
             // tile's window, one independent load per slot and round -- dependent global loads are the cost here,
@@ -400,26 +399,39 @@ __global__ void __launch_bounds__(JF_THREADS, 4) join_probe_kernel(DepthDesc d)
     }
     __syncthreads();
     uint32_t rank = s_wsum[warp] + inc - mine;  // viable slots of the tile before this thread's first slot
+    // segment starts: seg_rank[seg] = viable slots of this tile before the segment's first slot; also covers the
+    // empty segments that start at the same slot.  In a single-segment tile only the first slot can be one.
+    if (single) {
+        if (tid == 0 && slot0 == __ldg(d.slot_off + seg_lo)) {
+            for (uint32_t sg = seg_lo;; sg--) {
+                d.seg_rank[sg] = 0;
+                if (sg == 0 || __ldg(d.slot_off + sg - 1) != slot0) break;
+            }
+        }
+    } else {
+        uint32_t r2 = rank;
 #pragma unroll
-    for (int i = 0; i < JF_ITEMS; i++) {
-        const uint32_t slot = sbase + i;
-        if (slot >= slot0 + nslots) break;
-        // segment starts: seg_rank[seg] = viable slots of this tile before the segment's first slot; also
-        // covers the empty segments that start at the same slot
-        if ((!single || (i == 0 && tid == 0)) ) {
+        for (int i = 0; i < JF_ITEMS; i++) {
+            const uint32_t slot = sbase + i;
+            if (slot >= slot0 + nslots) break;
             uint32_t sg = segs[i];
             if (slot == __ldg(d.slot_off + sg)) {
                 for (;;) {
-                    d.seg_rank[sg] = rank;
+                    d.seg_rank[sg] = r2;
                     if (sg == 0 || __ldg(d.slot_off + sg - 1) != slot) break;
                     sg--;
                 }
             }
+            r2 += (okbits >> i) & 1u;
         }
-        if ((okbits >> i) & 1u) {
+    }
+    const bool keep_last = d.right_list != nullptr;  // deeper levels gather the tuple's end later
+#pragma unroll
+    for (int i = 0; i < JF_ITEMS; i++) {
+        if ((okbits >> i) & 1u) {  // dead slots never set their bit
             d.stage_x[slot0 + rank] = xs[i];
             d.stage_j[slot0 + rank] = js[i];
-            if (d.right_list) d.stage_last[slot0 + rank] = ls[i];  // deeper levels gather the tuple's end later
+            if (keep_last) d.stage_last[slot0 + rank] = ls[i];
             rank++;
         }
     }
