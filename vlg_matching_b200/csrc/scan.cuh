@@ -24,6 +24,10 @@
 //    gives every row its write cursor per pattern; pass 2 scatters the stream (scan_scatter_kernel) -- or, for
 //    rows whose stream overflowed, repeats the walk -- writing positions at cursor + rank (rank among equal
 //    patterns of the round by __match_any_sync), which makes every list sorted and the result deterministic.
+//  * measured alternatives that lost: per-position queue entries with a class loop in the drain (idle lanes in
+//    every class visit), shared-memory row counters (16 warps/SM instead of 32), one warp per row in the scatter
+//    (4x DRAM traffic), and probing every lane's candidates in place without a queue (lane imbalance: 1.44 ms
+//    against 0.87 ms for the queue on BASELINE config 2).
 //  * algorithmic bytes per pass: 2 x shard bytes read + 4 B per occurrence written (+ count matrix).
 #pragma once
 #include <algorithm>
