@@ -85,6 +85,9 @@ int vlgb_parse_query(const char* str, size_t len, int syntax, vlgb_batch** out);
  * a status array the first parse error fails the whole call. */
 int vlgb_parse_batch(const char* const* strs, const size_t* lens, uint32_t n, int syntax, int32_t* status,
                      vlgb_batch** out);
+/* Same for a pattern FILE image: one query per line ('\n'-separated, a trailing newline is optional), exactly what
+ * gm_search.cpp:84-104 reads with std::getline.  The first parse error fails the call. */
+int vlgb_parse_lines(const char* buf, size_t len, int syntax, vlgb_batch** out);
 void vlgb_batch_free(vlgb_batch* b);
 
 /* ---- index  (replaces construct(vlg_index&, file, cfg, num_bytes), vlg_index.hpp:375-392; the

@@ -105,6 +105,14 @@ def test_parse_batch_equals_per_query_parse():
             assert gmin[s_] == ref.gmin[s_] and gmax[s_] == ref.gmax[s_]
     with pytest.raises(capi.VlgbError):
         capi.ParsedBatch(qs, capi.SYNTAX_BENCHMARK)  # strict: the bad query fails the call
+    # a pattern-file image gives the same batch (with and without the trailing newline)
+    for image in (b"\n".join(good) + b"\n", b"\n".join(good)):
+        pb3 = capi.ParsedBatch(image, capi.SYNTAX_BENCHMARK)
+        assert pb3.k == pb2.k
+        so3 = np.ctypeslib.as_array(C.cast(pb3.c.sub_off, C.POINTER(C.c_uint32)), shape=(len(good) + 1,))
+        po3 = np.ctypeslib.as_array(C.cast(pb3.c.pat_off, C.POINTER(C.c_uint64)), shape=(n_sub + 1,))
+        by3 = np.ctypeslib.as_array(C.cast(pb3.c.pat_bytes, C.POINTER(C.c_uint8)), shape=(int(po3[-1]),))
+        assert (so3 == so).all() and (po3 == po).all() and (by3 == by).all()
 
 
 def test_product_never_touches_the_oracle():

@@ -30,7 +30,7 @@ SYMBOLS = [
     "vlgb_result_tuples", "vlgb_result_exit_cursors", "vlgb_result_first_starts", "vlgb_result_occurrences",
     "vlgb_result_fixup", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
     "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
-    "vlgb_parse_batch",
+    "vlgb_parse_batch", "vlgb_parse_lines",
 ]
 
 
@@ -65,6 +65,7 @@ lib.vlgb_version.restype = C.c_char_p
 lib.vlgb_parse_query.argtypes = [C.c_char_p, C.c_size_t, C.c_int, C.POINTER(C.POINTER(Batch))]
 lib.vlgb_parse_batch.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_uint32, C.c_int, C.c_void_p,
                                  C.POINTER(C.POINTER(Batch))]
+lib.vlgb_parse_lines.argtypes = [C.c_char_p, C.c_size_t, C.c_int, C.POINTER(C.POINTER(Batch))]
 lib.vlgb_batch_free.argtypes = [C.POINTER(Batch)]
 lib.vlgb_index_build.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_P)]
 lib.vlgb_index_build_file.argtypes = [C.c_char_p, C.POINTER(_P)]
@@ -182,6 +183,15 @@ class ParsedBatch:
     status[i] != 0 marks a query that failed to parse (it stays in the batch as an empty query)."""
 
     def __init__(self, strings, syntax: int = SYNTAX_LIBRARY, strict: bool = True):
+        if isinstance(strings, (bytes, bytearray)):  # a pattern-file image: one query per line (vlgb_parse_lines)
+            self._pb = C.POINTER(Batch)()
+            check(lib.vlgb_parse_lines(bytes(strings), len(strings), syntax, C.byref(self._pb)))
+            self.c = self._pb.contents
+            n = int(self.c.n_queries)
+            self.status = np.zeros(max(n, 1), dtype=np.int32)
+            so = np.ctypeslib.as_array(C.cast(self.c.sub_off, C.POINTER(C.c_uint32)), shape=(n + 1,))
+            self.k = np.diff(so).astype(np.int64).tolist()
+            return
         raw = [q.encode("latin-1") if isinstance(q, str) else bytes(q) for q in strings]
         n = len(raw)
         arr = (C.c_char_p * max(n, 1))(*raw)

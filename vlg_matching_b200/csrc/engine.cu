@@ -192,6 +192,22 @@ extern "C" int vlgb_parse_batch(const char* const* strs, const size_t* lens, uin
     return VLGB_OK;
 }
 
+extern "C" int vlgb_parse_lines(const char* buf, size_t len, int syntax, vlgb_batch** out)
+{
+    if ((!buf && len) || !out) return fail(VLGB_ERR_ARG, "vlgb_parse_lines: null argument");
+    std::vector<const char*> strs;
+    std::vector<size_t> lens;
+    size_t at = 0;
+    while (at < len) {
+        const char* nl = static_cast<const char*>(memchr(buf + at, '\n', len - at));
+        const size_t end = nl ? (size_t)(nl - buf) : len;
+        strs.push_back(buf + at);
+        lens.push_back(end - at);
+        at = end + 1;
+    }
+    return vlgb_parse_batch(strs.data(), lens.data(), (uint32_t)strs.size(), syntax, nullptr, out);
+}
+
 extern "C" void vlgb_batch_free(vlgb_batch* b)
 {
     if (b) delete reinterpret_cast<OwnedBatch*>(b);  // pub is the first member
