@@ -222,9 +222,9 @@ class Result:
         self.free()
 
     def free(self):
-        if self.h:
+        if self.h and lib is not None:  # `lib` is gone during interpreter shutdown
             lib.vlgb_result_free(self.h)
-            self.h = None
+        self.h = None
 
     @property
     def n(self):
