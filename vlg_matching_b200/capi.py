@@ -233,17 +233,24 @@ class Result:
     def status(self, q):
         return lib.vlgb_result_status(self.h, q)
 
+    def _u64(self, ptr) -> np.ndarray:
+        # copy of n uint64 at a library-owned address (np.ctypeslib.as_array builds a new ctypes type per call: slow)
+        if not self.n:
+            return np.zeros(0, dtype=np.uint64)
+        addr = C.cast(ptr, C.c_void_p).value
+        return np.frombuffer((C.c_uint64 * self.n).from_address(addr), dtype=np.uint64).copy()
+
     def counts(self) -> np.ndarray:
-        return np.ctypeslib.as_array(lib.vlgb_result_counts(self.h), shape=(max(self.n, 1),))[:self.n].copy()
+        return self._u64(lib.vlgb_result_counts(self.h))
 
     def total(self) -> int:
         return lib.vlgb_result_total(self.h)
 
     def exit_cursors(self) -> np.ndarray:
-        return np.ctypeslib.as_array(lib.vlgb_result_exit_cursors(self.h), shape=(max(self.n, 1),))[:self.n].copy()
+        return self._u64(lib.vlgb_result_exit_cursors(self.h))
 
     def first_starts(self) -> np.ndarray:
-        return np.ctypeslib.as_array(lib.vlgb_result_first_starts(self.h), shape=(max(self.n, 1),))[:self.n].copy()
+        return self._u64(lib.vlgb_result_first_starts(self.h))
 
     def occurrences(self, q) -> int:
         return lib.vlgb_result_occurrences(self.h, q)
