@@ -191,6 +191,10 @@ void* vlgb_stream_handle(void);
  * occurrences so that pass 2 need not read the text again; 1 = never, pass 2 always re-scans), and the device
  * memory budget for join state. */
 int vlgb_set_tuning(uint64_t stream_budget_bytes, uint64_t join_budget_bytes);
+/* Environment hooks read once per process, measurement only (stderr), no effect on results:
+ *   VLGB_TRACE=1        host wall-clock trace of every search call
+ *   VLGB_JOIN_DEBUG=1   per-tile-kind device time of the join probe kernel
+ *   VLGB_REV_FACTOR=n   the join is driven from the right list when it is n times shorter than the left (default 16, 0 = never) */
 
 #ifdef __cplusplus
 }
