@@ -870,6 +870,7 @@ template <class PinnedAlloc>
 inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo, const std::vector<uint64_t>& entry,
                       uint32_t want, bool keep_device, PinnedAlloc&& pinned_alloc, RefixOut& ro)
 {
+    trace() = HostTrace();
     const uint32_t nr = (uint32_t)redo.size(), nq = T.nq;
     SelDesc S = T.S;
     std::vector<uint64_t> entry_local(nr);
@@ -906,7 +907,9 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     std::vector<uint64_t> all_counts(nq, 0);
     d2h(c, all_counts.data(), T.d_counts, (size_t)nq * 8);
     VLGB_CUDA(cudaGetLastError());
+    trace().mark("refix: walk + recount launched");
     sync_stream(c);
+    trace().mark("refix: sync counts");
     c.stats.d2h_bytes += (uint64_t)nq * 8;
 
     ro.counts.assign(nr, 0);
@@ -963,7 +966,9 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
         }
     }
     VLGB_CUDA(cudaGetLastError());
+    trace().mark("refix: emit launched");
     sync_stream(c);
+    trace().mark("refix: done");
     for (uint32_t i = 0; i < nr; i++) {
         if (!ro.counts[i]) continue;
         ro.exit_cursor[i] = ex[redo[i]];
