@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define VLGB_ABI_VERSION 1
+#define VLGB_ABI_VERSION 2
 
 enum vlgb_status {
     VLGB_OK = 0,
@@ -123,6 +123,34 @@ uint32_t vlgb_index_symbol_width(const vlgb_index* idx);   /* bytes per symbol: 
 /* out[0 .. n*width).  VLGB_ERR_TOO_LARGE if a symbol does not fit `width` bytes (such a subpattern
  * cannot occur in the text), VLGB_ERR_ZERO_SYMBOL for a 0. */
 int vlgb_encode_symbols(uint32_t width, const uint64_t* symbols, uint64_t n, uint8_t* out);
+/* ---- rank path  (replaces the structure the reference index actually stores and queries: the wavelet tree over the
+ *      suffix array, vlg_index.hpp:116-138 wt_int<bit_vector_il<>>; its construction, vlg_index.hpp:375-392 ->
+ *      construct_sa.hpp:145-171 + wt_int.hpp:180-269 + bit_vector_il.hpp:114-154; and its three query primitives:
+ *      forward_search suffix_array_algorithm.hpp:48-115, wt_int::operator[] wt_int.hpp:339-361, the in-order range
+ *      walk wt_helper.hpp:726-785 over rank_support_il::rank1 bit_vector_il.hpp:264-278) ------------------------
+ * Builds, ON THE DEVICE, the suffix array of the shard (prefix doubling) and the wavelet tree over it in flat
+ * 64-byte rank blocks.  With it, a batch whose subpatterns are RARE gets its occurrence lists from SA ranges
+ * (cost proportional to the occurrences, like the reference) instead of a pass over the text; frequent
+ * subpatterns keep using the scan.  vlgb_set_path() overrides the choice.  Byte texts only (symbol width 1).
+ * One-time cost, reported by vlgb_index_rank_info (north_star: construction is reported separately). */
+#define VLGB_RANK_KEEP_SA 0u  /* keep the plain suffix array next to the tree (4 B/char more, SA probes cost one read) */
+#define VLGB_RANK_COMPACT 1u  /* tree only (what the reference stores): SA probes walk the tree (wt_int::operator[])   */
+int vlgb_index_attach_rank(vlgb_index* idx, uint32_t flags);
+typedef struct {
+    uint32_t present, levels, compact, doubling_rounds;
+    uint64_t bytes;              /* device bytes of suffix array + rank blocks */
+    double build_ms, sa_ms;      /* whole construction / suffix sort alone, host wall clock around the device work */
+} vlgb_rank_info;
+int vlgb_index_rank_info(const vlgb_index* idx, vlgb_rank_info* out);
+/* Copy SA[first .. first+count) to the host, read THROUGH the wavelet tree on the device (wt_int::operator[],
+ * wt_int.hpp:339-361) -- what a caller of vlg_index::wt[i] gets.  Needs vlgb_index_attach_rank. */
+int vlgb_index_sa_extract(const vlgb_index* idx, uint64_t first, uint64_t count, uint64_t* out);
+/* Which path produces the occurrence lists of the calling thread's searches. */
+#define VLGB_PATH_AUTO 0   /* cost model: rank path when the index has one and the batch is small and rare */
+#define VLGB_PATH_SCAN 1
+#define VLGB_PATH_RANK 2   /* fails with VLGB_ERR_ARG at search time if the index has no rank structures */
+int vlgb_set_path(int path);
+
 int vlgb_index_save(const vlgb_index* idx, const char* path);
 int vlgb_index_load(const char* path, vlgb_index** out);
 uint64_t vlgb_index_size(const vlgb_index* idx);          /* n (shard symbols incl. halo) */
@@ -181,6 +209,8 @@ typedef struct {
     uint32_t distinct_patterns, scan_passes, segments, query_chunks;
     uint64_t total_occurrences;         /* sum of list sizes of the distinct patterns   */
     uint64_t join_slots;                /* sum over (query, level) of |L_i|             */
+    uint32_t list_path;                 /* VLGB_PATH_SCAN or VLGB_PATH_RANK: where the occurrence lists came from */
+    uint32_t host_syncs;                /* host<->device synchronisations inside the call */
 } vlgb_stats;
 int vlgb_last_stats(vlgb_stats* out);
 const char* vlgb_stage_name(uint32_t stage);

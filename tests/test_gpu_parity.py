@@ -72,6 +72,24 @@ def test_reference_random_vectors(V):
     assert run_vectors(V, golden("random_ref.json")) >= 1500
 
 
+def test_reference_experiment_grid(V):
+    """k in {2,4,8,16,32} x the subpattern-length / gap grid of patterns.config, answered by the
+    unmodified reference (tests/golden/grid_ref.json, made by make_golden_grid.py)."""
+    from test_oracle_golden import check_grid_case, grid_sections
+    from vlg_matching_b200 import capi
+    n = 0
+    for text, cells, cases, hashlib in grid_sections():
+        idx = V.Index.build(text)
+        qs = [capi.parse_query(c["query"]) for c in cases]
+        r = idx.search(V.PackedBatch(qs), capi.WANT_TUPLES)
+        for q, c in enumerate(cases):
+            assert r.status(q) == 0
+            check_grid_case(c, r.tuples(q), hashlib)
+            n += 1
+        idx.free()
+    assert n >= 600
+
+
 def compare_with_oracle(V, text, queries, want_tuples=True, **build_kw):
     from vlg_matching_b200 import capi
     idx = V.Index.build(text, **build_kw)

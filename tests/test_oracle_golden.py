@@ -83,3 +83,36 @@ def test_live_reference_differential():
         for q, r, (st, starts, tup) in zip(qs, ref, got):
             assert r[0] == "Q" and st == 0
             assert [list(t) for t in r[2]] == tup.tolist(), (text, q)
+
+
+def grid_sections():
+    """tests/golden/grid_ref.json: the reference's experiment grid (patterns.config:2-16 x num_subpatterns.config:1-5,
+    k up to 32, gaps up to [10000,11000]) answered by the unmodified reference; texts are regenerated and checked by hash."""
+    import hashlib
+    from vlg_matching_b200 import synth
+    with open(os.path.join(HERE, "golden", "grid_ref.json")) as f:
+        g = json.load(f)
+    for sec in g["sections"]:
+        text = synth.make_text(sec["text"]["cfg"], sec["text"]["n"])
+        assert synth.sha256(text) == sec["text"]["sha256"]
+        yield text, sec["cells"], sec["cases"], hashlib
+
+
+def check_grid_case(c, tup, hashlib):
+    tup = np.ascontiguousarray(tup, dtype="<u8")
+    assert tup.shape[0] == c["count"], c["query"]
+    assert hashlib.sha256(tup.tobytes()).hexdigest() == c["sha256"], c["query"]
+    if c["count"]:
+        assert tup[0].tolist() == c["first"] and tup[-1].tolist() == c["last"], c["query"]
+
+
+def test_reference_experiment_grid():
+    n = deep = 0
+    for text, cells, cases, hashlib in grid_sections():
+        res = O.search(text, [c["query"] for c in cases], want_tuples=True, threads=8)
+        for c, (st, starts, tup) in zip(cases, res):
+            assert st == 0
+            check_grid_case(c, tup, hashlib)
+            n += 1
+            deep += c["count"] > 0 and tup.shape[1] >= 16
+    assert n >= 600 and deep >= 30

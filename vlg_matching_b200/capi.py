@@ -19,6 +19,8 @@ OK, ERR_CUDA, ERR_ARG, ERR_LAZY, ERR_MINMAX, ERR_NUMBER, ERR_EMPTY_SUB, ERR_ZERO
     ERR_TOO_LARGE = 0, -1, -2, -3, -4, -5, -6, -7, -8, -9, -10
 SYNTAX_LIBRARY, SYNTAX_BENCHMARK = 0, 1
 WANT_COUNT, WANT_STARTS, WANT_TUPLES, KEEP_ON_DEVICE = 0, 1, 2, 16
+RANK_KEEP_SA, RANK_COMPACT = 0, 1
+PATH_AUTO, PATH_SCAN, PATH_RANK = 0, 1, 2
 MAX_STAGES = 16
 
 # every symbol include/vlgb200.h declares
@@ -30,7 +32,8 @@ SYMBOLS = [
     "vlgb_result_tuples", "vlgb_result_exit_cursors", "vlgb_result_first_starts", "vlgb_result_occurrences",
     "vlgb_result_fixup", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
     "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
-    "vlgb_parse_batch", "vlgb_parse_lines",
+    "vlgb_parse_batch", "vlgb_parse_lines", "vlgb_index_attach_rank", "vlgb_index_rank_info", "vlgb_index_sa_extract",
+    "vlgb_set_path",
 ]
 
 
@@ -49,7 +52,13 @@ class Stats(C.Structure):
     _fields_ = [("n_stages", C.c_uint32), ("ms", C.c_float * MAX_STAGES), ("bytes", C.c_uint64 * MAX_STAGES),
                 ("launches", C.c_uint32 * MAX_STAGES), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("distinct_patterns", C.c_uint32), ("scan_passes", C.c_uint32), ("segments", C.c_uint32),
-                ("query_chunks", C.c_uint32), ("total_occurrences", C.c_uint64), ("join_slots", C.c_uint64)]
+                ("query_chunks", C.c_uint32), ("total_occurrences", C.c_uint64), ("join_slots", C.c_uint64),
+                ("list_path", C.c_uint32), ("host_syncs", C.c_uint32)]
+
+
+class RankInfo(C.Structure):
+    _fields_ = [("present", C.c_uint32), ("levels", C.c_uint32), ("compact", C.c_uint32), ("doubling_rounds", C.c_uint32),
+                ("bytes", C.c_uint64), ("build_ms", C.c_double), ("sa_ms", C.c_double)]
 
 
 if not os.path.exists(LIB_PATH):
@@ -104,6 +113,10 @@ lib.vlgb_index_build_symbols.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64,
 lib.vlgb_index_symbol_width.argtypes = [_P]
 lib.vlgb_index_symbol_width.restype = C.c_uint32
 lib.vlgb_encode_symbols.argtypes = [C.c_uint32, _P, C.c_uint64, _P]
+lib.vlgb_index_attach_rank.argtypes = [_P, C.c_uint32]
+lib.vlgb_index_rank_info.argtypes = [_P, C.POINTER(RankInfo)]
+lib.vlgb_index_sa_extract.argtypes = [_P, C.c_uint64, C.c_uint64, _P]
+lib.vlgb_set_path.argtypes = [C.c_int]
 
 
 def check(rc):
@@ -129,7 +142,12 @@ def last_stats() -> dict:
     return {"stages": stages, "h2d_bytes": int(s.h2d_bytes), "d2h_bytes": int(s.d2h_bytes),
             "distinct_patterns": int(s.distinct_patterns), "scan_passes": int(s.scan_passes),
             "segments": int(s.segments), "query_chunks": int(s.query_chunks),
-            "total_occurrences": int(s.total_occurrences), "join_slots": int(s.join_slots)}
+            "total_occurrences": int(s.total_occurrences), "join_slots": int(s.join_slots),
+            "list_path": {PATH_SCAN: "scan", PATH_RANK: "rank"}.get(int(s.list_path), "none"), "host_syncs": int(s.host_syncs)}
+
+
+def set_path(path: int):
+    check(lib.vlgb_set_path(path))
 
 
 def parse_query(q: bytes | str, syntax: int = SYNTAX_LIBRARY):
@@ -349,6 +367,21 @@ class Index:
         out = np.zeros(max(length, 1), dtype=np.uint8)
         check(lib.vlgb_index_extract(self.h, pos, length, out.ctypes.data))
         return out[:length].tobytes()
+
+    def attach_rank(self, flags: int = RANK_KEEP_SA) -> dict:
+        """Build suffix array + wavelet tree (flat rank blocks) on the device; -> rank_info()."""
+        check(lib.vlgb_index_attach_rank(self.h, flags))
+        return self.rank_info()
+
+    def rank_info(self) -> dict:
+        r = RankInfo()
+        check(lib.vlgb_index_rank_info(self.h, C.byref(r)))
+        return {k: getattr(r, k) for k, _ in RankInfo._fields_}
+
+    def sa_extract(self, first: int, count: int) -> np.ndarray:
+        out = np.zeros(max(count, 1), dtype=np.uint64)
+        check(lib.vlgb_index_sa_extract(self.h, first, count, out.ctypes.data))
+        return out[:count]
 
     def search(self, batch: PackedBatch, want=WANT_TUPLES, entry_cursor=None) -> Result:
         e = None

@@ -61,13 +61,15 @@ enum Stage : uint32_t {
     ST_SELECT_WALK,     // tile-to-tile walk + marking
     ST_EMIT,            // compaction of selected matches + tuple chain resolve
     ST_PREFIX,          // stand-alone device prefix sums
+    ST_RANK_RANGE,      // rank path: SA range of every distinct subpattern (warp-cooperative search)
+    ST_RANK_ENUM,       // rank path: in-order enumeration of the SA ranges through the wavelet tree
     ST_COUNT
 };
 
 inline const char* stage_name(uint32_t s)
 {
     static const char* names[ST_COUNT] = {"scan_count", "scan_offsets", "scan_fill", "join_probe", "join_compact",
-                                          "select_succ", "select_tile", "select_walk", "emit", "prefix"};
+                                          "select_succ", "select_tile", "select_walk", "emit", "prefix", "rank_range", "rank_enum"};
     return s < ST_COUNT ? names[s] : "";
 }
 
@@ -187,6 +189,7 @@ struct Context {
     uint64_t stream_budget = 0;  // 0 = default (a third of the free memory, <= 24 GiB); tiny = no hit stream
     uint64_t join_budget = 0;    // 0 = default
     uint64_t serial = 0;         // searches run on this thread (validity of the state kept for vlgb_result_fixup)
+    int list_path = 0;           // VLGB_PATH_AUTO / _SCAN / _RANK (vlgb_set_path)
 
     void begin(uint32_t stage)
     {
@@ -279,6 +282,7 @@ inline void d2h(Context& c, void* host_dst, const void* dev_src, size_t bytes)  
 inline void sync_stream(Context& c)
 {
     VLGB_CUDA(cudaStreamSynchronize(c.stream));
+    c.stats.host_syncs++;
     for (auto& d : c.pending) memcpy(d.host, d.pinned, d.bytes);
     c.pending.clear();
 }

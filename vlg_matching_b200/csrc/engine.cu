@@ -20,6 +20,8 @@ struct vlgb_index {
     bool owns = false;
     uint64_t n = 0, global_offset = 0, owned_len = 0, total_len = 0;  // all in BYTES
     uint32_t sym_shift = 0;  // log2(bytes per symbol): 0 = byte text, 1..3 = encoded integer alphabet
+    WtSaOwned* rank = nullptr;  // suffix array + wavelet tree in rank blocks (vlgb_index_attach_rank), else nullptr
+    uint32_t rank_flags = 0;
 };
 static constexpr uint64_t TEXT_PAD = 64;
 static constexpr uint64_t MAX_SHARD = 0xFFFFF000ull;  // positions are shard-local u32 on the device
@@ -321,7 +323,9 @@ extern "C" int vlgb_index_save(const vlgb_index* idx, const char* path)
         if (idx->n) VLGB_CUDA(cudaMemcpy(buf.data(), idx->d_text, idx->n, cudaMemcpyDeviceToHost));
         FILE* f = fopen(path, "wb");
         if (!f) return fail(VLGB_ERR_IO, "cannot create %s", path);
-        uint64_t hdr[5] = {idx->n, idx->global_offset, idx->owned_len, idx->total_len, idx->sym_shift};
+        // the rank structures are rebuilt on the device at load time (seconds; cheaper than reading them back)
+        uint64_t hdr[5] = {idx->n, idx->global_offset, idx->owned_len, idx->total_len,
+                           idx->sym_shift | (idx->rank ? 0x100ull | ((uint64_t)idx->rank_flags << 16) : 0ull)};
         bool ok = fwrite(INDEX_MAGIC, 1, 8, f) == 8 && fwrite(hdr, 8, 5, f) == 5 &&
                   (idx->n == 0 || fwrite(buf.data(), 1, idx->n, f) == idx->n);
         ok = (fclose(f) == 0) && ok;
@@ -341,9 +345,16 @@ extern "C" int vlgb_index_load(const char* path, vlgb_index** out)
     if (buf.size() < INDEX_HDR || memcmp(buf.data(), INDEX_MAGIC, 8) != 0) return fail(VLGB_ERR_IO, "%s: not a vlgb200 index", path);
     uint64_t hdr[5];
     memcpy(hdr, buf.data() + 8, 40);
-    if (buf.size() - INDEX_HDR != hdr[0] || hdr[4] > 3) return fail(VLGB_ERR_IO, "%s: size mismatch", path);
+    if (buf.size() - INDEX_HDR != hdr[0] || (hdr[4] & 0xFF) > 3) return fail(VLGB_ERR_IO, "%s: size mismatch", path);
     rc = vlgb_index_build(buf.data() + INDEX_HDR, hdr[0], hdr[1], hdr[2], hdr[3], out);
-    if (rc == VLGB_OK) (*out)->sym_shift = (uint32_t)hdr[4];
+    if (rc == VLGB_OK) (*out)->sym_shift = (uint32_t)(hdr[4] & 0xFF);
+    if (rc == VLGB_OK && (hdr[4] & 0x100)) {
+        rc = vlgb_index_attach_rank(*out, (uint32_t)(hdr[4] >> 16) & 0xFFu);
+        if (rc != VLGB_OK) {
+            vlgb_index_free(*out);
+            *out = nullptr;
+        }
+    }
     return rc;
 }
 
@@ -412,10 +423,97 @@ extern "C" int vlgb_index_extract(const vlgb_index* idx, uint64_t pos, uint64_t 
     }
 }
 
+// ---- rank path: suffix array + wavelet tree in flat rank blocks, built on the device (sa_build.cu)
+extern "C" int vlgb_index_attach_rank(vlgb_index* idx, uint32_t flags)
+{
+    if (!idx) return fail(VLGB_ERR_ARG, "vlgb_index_attach_rank: null index");
+    if (flags > VLGB_RANK_COMPACT) return fail(VLGB_ERR_ARG, "vlgb_index_attach_rank: unknown flags");
+    if (idx->sym_shift) return fail(VLGB_ERR_ARG, "vlgb_index_attach_rank: byte texts only (symbol width %u)", 1u << idx->sym_shift);
+    if (idx->n < 2) return fail(VLGB_ERR_ARG, "vlgb_index_attach_rank: text too short");
+    if (idx->rank && idx->rank_flags == flags) return VLGB_OK;
+    try {
+        ensure_ready();
+        Context& c = ctx();
+        if (idx->rank) {
+            wtsa_free(*idx->rank);
+            delete idx->rank;
+            idx->rank = nullptr;
+        }
+        std::unique_ptr<WtSaOwned> w(new WtSaOwned());
+        try {
+            wtsa_build(c.stream, idx->d_text, idx->n, flags != VLGB_RANK_COMPACT, *w);
+        } catch (...) {
+            wtsa_free(*w);
+            throw;
+        }
+        idx->rank = w.release();
+        idx->rank_flags = flags;
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+extern "C" int vlgb_index_rank_info(const vlgb_index* idx, vlgb_rank_info* out)
+{
+    if (!idx || !out) return fail(VLGB_ERR_ARG, "vlgb_index_rank_info: null argument");
+    memset(out, 0, sizeof *out);
+    if (!idx->rank) return VLGB_OK;
+    out->present = 1;
+    out->levels = idx->rank->view.levels;
+    out->compact = idx->rank->view.sa == nullptr;
+    out->doubling_rounds = idx->rank->doubling_rounds;
+    out->bytes = idx->rank->bytes();
+    out->build_ms = idx->rank->build_ms;
+    out->sa_ms = idx->rank->sa_ms;
+    return VLGB_OK;
+}
+
+namespace {
+__global__ void sa_extract_kernel(WtSa W, uint32_t first, uint32_t count, uint64_t* out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) out[i] = wt_access(W, first + i);
+}
+}  // namespace
+
+extern "C" int vlgb_index_sa_extract(const vlgb_index* idx, uint64_t first, uint64_t count, uint64_t* out)
+{
+    if (!idx || (!out && count)) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract: null argument");
+    if (!idx->rank) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract: the index has no rank structures (vlgb_index_attach_rank)");
+    if (first > idx->n || count > idx->n - first) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract: range outside the suffix array");
+    if (!count) return VLGB_OK;
+    try {
+        ensure_ready();
+        Context& c = ctx();
+        DeviceBuffer buf;
+        uint64_t* d = (uint64_t*)buf.get(count * 8);
+        sa_extract_kernel<<<(unsigned)((count + 255) / 256), 256, 0, c.stream>>>(idx->rank->view, (uint32_t)first, (uint32_t)count, d);
+        cudaError_t e = cudaMemcpyAsync(out, d, count * 8, cudaMemcpyDeviceToHost, c.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+        buf.release();
+        if (e != cudaSuccess) throw CudaError{e, __FILE__, __LINE__};
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+extern "C" int vlgb_set_path(int path)
+{
+    if (path != VLGB_PATH_AUTO && path != VLGB_PATH_SCAN && path != VLGB_PATH_RANK) return fail(VLGB_ERR_ARG, "vlgb_set_path: unknown path %d", path);
+    ctx().list_path = path;
+    return VLGB_OK;
+}
+
 extern "C" void vlgb_index_free(vlgb_index* idx)
 {
     if (!idx) return;
     if (idx->owns && idx->d_text) cudaFree(idx->d_text);
+    if (idx->rank) {
+        wtsa_free(*idx->rank);
+        delete idx->rank;
+    }
     delete idx;
 }
 
@@ -528,7 +626,11 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
     // ---- scan: one sorted occurrence list per distinct subpattern
     ScanOut so;
     trace().mark("plan + dictionary");
-    run_scan(c, idx->d_text, idx->n, idx->owned_len, idx->sym_shift, dict, so);
+    bool listed = false;
+    if (idx->rank && c.list_path != VLGB_PATH_SCAN)
+        listed = run_rank_lists(c, idx->d_text, idx->n, idx->owned_len, idx->rank->view, dict, so, c.list_path == VLGB_PATH_RANK);
+    c.stats.list_path = listed ? VLGB_PATH_RANK : VLGB_PATH_SCAN;
+    if (!listed) run_scan(c, idx->d_text, idx->n, idx->owned_len, idx->sym_shift, dict, so);
     BatchView view{batch, &sub_pid, &so, idx->global_offset, idx->sym_shift};
 
     trace().mark("scan done");
@@ -613,6 +715,8 @@ extern "C" int vlgb_search_batch(const vlgb_index* idx, const vlgb_batch* batch,
     int rc = batch_check(batch);
     if (rc) return rc;
     if ((want & 3u) > VLGB_WANT_TUPLES) return fail(VLGB_ERR_ARG, "vlgb_search_batch: bad `want`");
+    if (ctx().list_path == VLGB_PATH_RANK && !idx->rank)
+        return fail(VLGB_ERR_ARG, "vlgb_search_batch: VLGB_PATH_RANK but the index has no rank structures (vlgb_index_attach_rank)");
     try {
         ensure_ready();
         Context& c = ctx();

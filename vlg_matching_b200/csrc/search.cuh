@@ -15,6 +15,7 @@
 #include "common.cuh"
 #include "prefix.cuh"
 #include "scan.cuh"
+#include "wtsa.cuh"
 #include "join.cuh"
 #include "select.cuh"
 
@@ -282,6 +283,129 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         c.stats.h2d_bytes += (uint64_t)P * 4;
         c.stats.d2h_bytes += (uint64_t)P * 4;
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// rank path: occurrence lists from SA ranges (wtsa.cuh) instead of a pass over the text
+// ---------------------------------------------------------------------------------------------
+// Cost model (measured on B200): a scan pass costs a fixed launch/offset overhead plus the text at the
+// scan's rate; the rank path costs ~0.25 us of device time per distinct subpattern for the range search (latency
+// bound, hidden by parallel warps) and ~L dependent rank blocks per occurrence for the enumeration.
+inline double scan_cost_ms(uint64_t n, uint32_t patterns)
+{
+    const uint32_t passes = (patterns + SCAN_S - 1) / SCAN_S;
+    return passes * (0.12 + (double)n * 6.0e-9);
+}
+inline double rank_range_cost_ms(uint32_t patterns) { return 0.05 + patterns * 2.5e-4; }
+inline double rank_enum_cost_ms(uint64_t occurrences, uint32_t levels) { return 0.02 + (double)occurrences * levels * 1.0e-7; }
+
+// Returns false (and leaves `so` untouched apart from sizes) when the cost model prefers the scan.
+inline bool run_rank_lists(Context& c, const uint8_t* d_text, uint64_t n, uint64_t owned_len, const WtSa& W,
+                           const PatternDict& dict, ScanOut& so, bool forced)
+{
+    const uint32_t P = (uint32_t)dict.pats.size();
+    so.tot.assign(P, 0);
+    so.own.assign(P, 0);
+    so.base.assign(P + 1, 0);
+    so.d_lists = nullptr;
+    so.total_words = 0;
+    if (P == 0 || n == 0) return true;
+    const double scan_ms = scan_cost_ms(n, P);
+    if (!forced && rank_range_cost_ms(P) > scan_ms) return false;
+
+    // ---- SA range of every distinct subpattern
+    std::vector<uint32_t> pat_off(P + 1, 0);
+    std::string blob;
+    for (uint32_t i = 0; i < P; i++) {
+        blob += dict.pats[i];
+        pat_off[i + 1] = (uint32_t)blob.size();
+    }
+    Packer ctl;
+    const size_t o_blob = ctl.put(blob.data(), blob.size()), o_off = ctl.put(pat_off);
+    const size_t ctl_bytes = ctl.size();
+    const size_t work = ctl_bytes + Arena::padded(2 * (size_t)P, 4) + 2 * Arena::padded(P + 1, 8) + 3 * Arena::padded(P, 4) + 4096;
+    c.scan_arena.reserve(work);
+    uint8_t* d_ctl = c.scan_arena.take<uint8_t>(ctl_bytes);
+    uint32_t* d_bound = c.scan_arena.take<uint32_t>(2 * (size_t)P);
+    uint64_t* d_first = c.scan_arena.take<uint64_t>(P + 1);
+    uint64_t* d_base = c.scan_arena.take<uint64_t>(P + 1);
+    uint32_t* d_sp = c.scan_arena.take<uint32_t>(P);
+    uint32_t* d_tot = c.scan_arena.take<uint32_t>(P);
+    uint32_t* d_owned = c.scan_arena.take<uint32_t>(P);
+    h2d(c, d_ctl, ctl.host.data(), ctl.host.size());
+    c.stats.h2d_bytes += ctl.host.size();
+    WtsaRangeArgs ra;
+    ra.W = W;
+    ra.text = d_text;
+    ra.n_pat = P;
+    ra.pat_bytes = dev_at<const uint8_t>(d_ctl, o_blob);
+    ra.pat_off = dev_at<const uint32_t>(d_ctl, o_off);
+    ra.bound = d_bound;
+    uint32_t rounds = 1;
+    for (uint64_t span = n; span > 32; span /= 33) rounds++;
+    c.begin(ST_RANK_RANGE);
+    wtsa_range_kernel<<<(2 * P * 32 + 127) / 128, 128, 0, c.stream>>>(ra);
+    // per probe: one SA entry (or `levels` rank blocks) + one 32-byte sector of text
+    c.end(ST_RANK_RANGE, 1, (uint64_t)2 * P * rounds * 32 * (32 + (W.sa ? 4 : (uint64_t)W.levels * 64)));
+    std::vector<uint32_t> bound(2 * (size_t)P);
+    d2h(c, bound.data(), d_bound, bound.size() * 4);
+    VLGB_CUDA(cudaGetLastError());
+    sync_stream(c);  // sync: list sizes (the scan path pays the same one)
+    c.stats.d2h_bytes += bound.size() * 4;
+    uint64_t occ = 0;
+    std::vector<uint32_t> sp(P);
+    std::vector<uint64_t> first(P + 1, 0);
+    for (uint32_t i = 0; i < P; i++) {
+        sp[i] = bound[2 * i];
+        so.tot[i] = bound[2 * i + 1] - bound[2 * i];
+        first[i] = occ;
+        occ += so.tot[i];
+    }
+    first[P] = occ;
+    if (!forced && rank_enum_cost_ms(occ, W.levels) > scan_ms) return false;
+
+    // ---- in-order enumeration: the lists come out ascending
+    uint64_t words = 0;
+    for (uint32_t i = 0; i < P; i++) {
+        so.base[i] = words;
+        words += ((uint64_t)so.tot[i] + 3) & ~3ull;
+    }
+    so.base[P] = words;
+    so.total_words = words;
+    c.list_arena.reserve(words * 4 + 4096);
+    so.d_lists = c.list_arena.take<uint32_t>(words + 16);
+    h2d(c, d_sp, sp.data(), (size_t)P * 4);
+    h2d(c, d_first, first.data(), (size_t)(P + 1) * 8);
+    h2d(c, d_base, so.base.data(), (size_t)(P + 1) * 8);
+    c.stats.h2d_bytes += (uint64_t)P * 20 + 16;
+    if (occ) {
+        WtsaEnumArgs ea;
+        ea.W = W;
+        ea.n_pat = P;
+        ea.sp = d_sp;
+        ea.out_first = d_first;
+        ea.list_base = d_base;
+        ea.out = so.d_lists;
+        ea.total = occ;
+        c.begin(ST_RANK_ENUM);
+        wtsa_enum_kernel<<<(unsigned)((occ + 255) / 256), 256, 0, c.stream>>>(ea);
+        c.end(ST_RANK_ENUM, 1, occ * ((uint64_t)W.levels * 64 + 4));  // >= one rank block per level and element + the position
+    }
+    c.stats.total_occurrences += occ;
+    c.stats.distinct_patterns += P;
+    if (owned_len >= n) {
+        so.own = so.tot;
+    } else {
+        h2d(c, d_tot, so.tot.data(), (size_t)P * 4);
+        scan_owned_kernel<<<(P + 127) / 128, 128, 0, c.stream>>>(so.d_lists, d_base, d_tot, P, (uint32_t)owned_len, d_owned);
+        d2h(c, so.own.data(), d_owned, (size_t)P * 4);
+        VLGB_CUDA(cudaGetLastError());
+        sync_stream(c);
+        c.stats.h2d_bytes += (uint64_t)P * 4;
+        c.stats.d2h_bytes += (uint64_t)P * 4;
+    }
+    VLGB_CUDA(cudaGetLastError());
+    return true;
 }
 
 // ---------------------------------------------------------------------------------------------

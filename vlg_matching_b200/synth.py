@@ -8,7 +8,9 @@ Stands in for the reference's collections and frequent-phrase patterns
 """
 from __future__ import annotations
 
+import ctypes as C
 import hashlib
+import os
 
 import numpy as np
 
@@ -38,8 +40,17 @@ _LEN_TABLE = np.asarray([1, 2, 2, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 6, 6, 6, 7, 7
 VOCAB = 50000
 
 
+_VOCAB_CACHE = {}
+
+
 def _vocabulary(seed: int):
     """-> (blob uint8, off int64[VOCAB+1]); words 0..63 are real function words, the rest pseudo-words."""
+    if seed not in _VOCAB_CACHE:
+        _VOCAB_CACHE[seed] = _vocabulary_build(seed)
+    return _VOCAB_CACHE[seed]
+
+
+def _vocabulary_build(seed: int):
     r = splitmix64(seed ^ 0x5EED0001, 0, VOCAB * 13)
     words = []
     seen = set()
@@ -64,6 +75,28 @@ def _vocabulary(seed: int):
     return np.frombuffer(b"".join(words), dtype=np.uint8), off
 
 
+_GEN = None
+
+
+def _native():
+    """libvlgsynth.so (csrc/host/synth_gen.c): the same generators, threaded C.  None if it was not built; the
+    numpy code below is the definition and the fallback (tests compare the two)."""
+    global _GEN
+    if _GEN is None:
+        p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libvlgsynth.so")
+        _GEN = False
+        if os.path.exists(p) and not os.environ.get("VLGB_SYNTH_NUMPY"):
+            try:
+                g = C.CDLL(p)
+                g.vlgs_english.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_uint32, C.c_uint64, C.c_int]
+                g.vlgs_dna.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]
+                _GEN = g
+            except OSError:
+                _GEN = False
+    return _GEN or None
+
+
 def english_text(n: int, seed: int, block_words: int = 1 << 21) -> np.ndarray:
     """n bytes of Zipf(1.0) word stream over a 50k vocabulary, single spaces, occasional '. , ;';
     bytes in [0x20, 0x7e] only (so create_collection.cpp:87-90 would leave it unchanged)."""
@@ -72,6 +105,14 @@ def english_text(n: int, seed: int, block_words: int = 1 << 21) -> np.ndarray:
     weights = (np.uint64(1 << 32) // np.arange(1, VOCAB + 1, dtype=np.uint64))
     cum = np.cumsum(weights)
     total = cum[-1]
+    g = _native()
+    if g is not None and n >= (1 << 16):
+        out = np.empty(n, dtype=np.uint8)
+        blob_c, off_c, cum_c = np.ascontiguousarray(blob), np.ascontiguousarray(off, dtype=np.int64), np.ascontiguousarray(cum, dtype=np.uint64)
+        rc = g.vlgs_english(out.ctypes.data, n, seed & 0xFFFFFFFFFFFFFFFF, blob_c.ctypes.data, off_c.ctypes.data, cum_c.ctypes.data,
+                            VOCAB, block_words, min(os.cpu_count() or 1, 64))
+        if rc == 0:
+            return out
     out = np.empty(n, dtype=np.uint8)
     filled = 0
     w0 = 0
@@ -105,6 +146,10 @@ def dna_text(n: int, seed: int, block: int = 1 << 24) -> np.ndarray:
     """n bytes iid uniform over ACGT."""
     acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
     out = np.empty(n, dtype=np.uint8)
+    g = _native()
+    if g is not None and n >= (1 << 16):
+        g.vlgs_dna(out.ctypes.data, n, seed & 0xFFFFFFFFFFFFFFFF, min(os.cpu_count() or 1, 64))
+        return out
     shifts = (np.arange(32, dtype=np.uint64) * np.uint64(2))[None, :]
     filled = 0
     d0 = 0
@@ -186,3 +231,65 @@ def make_queries(cfg: int, text: np.ndarray, nq: int | None = None):
     c = CONFIGS[cfg]
     return sample_queries(text, c["nq"] if nq is None else nq, c["k"], c["lens"], c["gaps"], c["qseed"],
                           word_aligned=c["kind"] == "english")
+
+
+# ---- the reference's experiment grid -------------------------------------------------
+# benchmark/gapped-matching/patterns.config:2-16 (subpattern length x gap), num_subpatterns.config:1-5
+GRID_LENGTHS = (3, 5, 7)
+GRID_GAPS = ((100, 110), (1000, 1100), (10000, 11000), (10, 20), (0, 100))
+GRID_K = (2, 4, 8, 16, 32)
+
+
+def frequent_phrases(text: np.ndarray, count: int, length: int):
+    """What examples/generate-pattern.cpp:1-120 prints for `file count length 1 0`: the `count` most frequent
+    substrings of `length` alpha-numerical bytes (isalnum or '_').  The reference walks its suffix tree in
+    lexicographic order and keeps a min-heap of (occurrences, phrase): a phrase enters while the heap is not full
+    or when it occurs MORE often than the heap's minimum (which is then dropped); the heap is finally popped in
+    ascending (occurrences, phrase) order, and short results are padded by repetition.  numpy definition (the
+    device generator, tools built on the SA index, is tested against this)."""
+    import heapq
+    n = text.size
+    if n < length:
+        return [b"x" * length] * count
+    ok = np.zeros(256, dtype=bool)
+    for c in range(256):
+        ch = bytes([c])
+        ok[c] = (ch.isalnum() and c < 128) or ch == b"_"
+    good = ok[text]
+    # windows whose `length` bytes are all in the charset
+    run = np.cumsum(~good)
+    win_ok = (run[length - 1:] - np.concatenate([[0], run[:n - length]])) == 0
+    pos = np.nonzero(win_ok)[0]
+    key = np.zeros(pos.size, dtype=np.uint64)
+    for j in range(length):
+        key = (key << np.uint64(8)) | text[pos + j].astype(np.uint64)
+    grams, occ = np.unique(key, return_counts=True)  # ascending key = lexicographic (big-endian packing)
+    heap = []
+    for g, o in zip(grams.tolist(), occ.tolist()):
+        if len(heap) == count and o <= heap[0][0]:
+            continue
+        heapq.heappush(heap, (o, g))
+        if len(heap) > count:
+            heapq.heappop(heap)
+    res = []
+    while heap and len(res) < count:
+        o, g = heapq.heappop(heap)
+        res.append(int(g).to_bytes(8, "big")[8 - length:])
+    if not res:
+        res.append(b"x" * length)
+    si = len(res)
+    while len(res) < count:
+        res.append(res[len(res) % si])
+    return res
+
+
+def grid_queries(words, k: int, gap, samples: int):
+    """benchmark/gapped-matching/Makefile:98-106: the word list cut into lines of k words (`xargs -n k`), joined
+    by the gap, first `samples` lines."""
+    out = []
+    for i in range(0, len(words), k):
+        line = words[i:i + k]
+        out.append((list(line), [gap] * (len(line) - 1)))
+        if len(out) == samples:
+            break
+    return out
