@@ -181,6 +181,12 @@ uint64_t vlgb_result_total(const vlgb_result* r);                  /* sum over t
 const uint64_t* vlgb_result_counts(const vlgb_result* r);          /* n_queries counts                */
 const uint64_t* vlgb_result_starts(const vlgb_result* r, uint32_t q);  /* host, ascending; NULL if not wanted */
 const uint64_t* vlgb_result_tuples(const vlgb_result* r, uint32_t q);  /* host, k(q) per match            */
+/* VLGB_KEEP_ON_DEVICE: the same lists in DEVICE memory (whole-text u64 positions; k(q) per match for tuples), NULL
+ * for a query without matches or when not kept.  The memory belongs to the result and stays valid until
+ * vlgb_result_free; it was written on vlgb_stream_handle() and the search call returns after that stream has been
+ * synchronised, so any stream may read it. */
+const uint64_t* vlgb_result_device_starts(const vlgb_result* r, uint32_t q);
+const uint64_t* vlgb_result_device_tuples(const vlgb_result* r, uint32_t q);
 /* Non-overlap cursor each query leaves this shard with (= entry cursor of the next shard). */
 const uint64_t* vlgb_result_exit_cursors(const vlgb_result* r);
 /* Whole-text position of the first reported match of every query (~0 if none). */
@@ -194,6 +200,42 @@ uint64_t vlgb_result_occurrences(const vlgb_result* r, uint32_t q);
  * *n_changed = number of queries searched again.  The index must still be alive. */
 int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, uint32_t* n_changed);
 void vlgb_result_free(vlgb_result* r);
+
+/* ---- multi-GPU  (the text is cut into contiguous shards that overlap by the largest query span; a
+ *      match belongs to the shard that contains its first subpattern's start.  The only coupling between shards is
+ *      the non-overlap cursor pull_forward leaves behind, vlg_index.hpp:253-264.) -------------------------------------
+ * One host thread drives one GPU = one rank (one process per GPU under torchrun, or one thread per GPU inside one
+ * process: gm_search --gpus N).  The communicator is NCCL, bound at run time (libnccl.so.2); it carries ONE
+ * all-gather of 24 bytes per query and rank per round.  n_ranks = 1 needs no NCCL and no id. */
+#define VLGB_COMM_ID_BYTES 128
+int vlgb_comm_unique_id(uint8_t* id /* VLGB_COMM_ID_BYTES, out */);  /* ncclGetUniqueId: call on ONE rank, hand the bytes to all */
+int vlgb_comm_init(const uint8_t* id, int n_ranks, int rank);        /* after vlgb_init(device) on the calling thread */
+int vlgb_comm_destroy(void);
+typedef struct {
+    uint32_t n_ranks, rounds;              /* all-gather rounds (1 = nobody had to re-enter) */
+    uint32_t reentered_shards;             /* over all ranks and rounds */
+    uint32_t reentered_queries;            /* on this rank */
+    float exchange_ms;                     /* host wall clock of the exchange on this rank: collectives + re-entry + waiting */
+    uint64_t global_matches;               /* over all ranks */
+} vlgb_shard_stats;
+/* Search the whole batch on this rank's shards.  The shards of the WHOLE text are ordered rank-major: all shards of
+ * rank 0 in the order given, then rank 1's, ...; a rank's shards must be consecutive pieces of the text (each built
+ * with its global_offset / owned_len / halo).  Inside the rank the shards are searched left to right and shard j
+ * enters with the cursors shard j-1 left (exact, no re-entry needed: this is how a text larger than one shard, e.g.
+ * 8 GiB on one GPU, is searched); across ranks every rank first searches speculatively from cursor 0, then the
+ * ranks all-gather (count, exit cursor, first start) per query, derive every rank's true entry cursor, and the ranks
+ * whose reported set can change re-enter (vlgb_result_fixup) -- repeated until no cursor moves (<= n_ranks
+ * rounds, typically 1-2).  Collective: every rank must call it with the same batch.
+ * results[j] receives shard j's result (its own matches, whole-text positions); global_counts (nullable, n_queries)
+ * the per-query totals over ALL ranks. */
+int vlgb_search_sharded(const vlgb_index* const* shards, uint32_t n_local, const vlgb_batch* batch, uint32_t want,
+                        vlgb_result** results, uint64_t* global_counts, vlgb_shard_stats* st);
+/* The host logic of the exchange, exported so that it is testable without a GPU: rows[n_shards][nq][3] = (count,
+ * exit cursor, first start) as reported, used[n_shards][nq] = the entry cursor each row was computed with ->
+ * entries[n_shards][nq] = true entry cursors implied by the rows, redo[n_shards] = 1 where a shard's reported set
+ * can change.  Returns the number of shards to redo (or a negative status). */
+int vlgb_chain_plan(const uint64_t* rows, const uint64_t* used, uint32_t n_shards, uint32_t nq, uint64_t* entries,
+                    uint8_t* redo);
 
 /* ---- measurement hooks (bench.py / profiles; no effect on results) ------------------------------ */
 

@@ -13,8 +13,9 @@
 // Usage:
 //   ref_vlg locate <text-file> <query-file>            print every match tuple of every query
 //   ref_vlg build  <text-file> <index-file>            construct + serialize (vlg_index.hpp:183-191)
-//   ref_vlg bench  <text-file|index-file> <query-file> <threads> [--index]
-//                                                       time locate() over all queries; JSON on stdout
+//   ref_vlg bench  <text-file|index-file> <query-file> <threads> [--index] [--steps K] [--warmup W]
+//                                                       time locate() over all queries, W + K passes in ONE process
+//                                                       (the index is loaded once); JSON on stdout
 // Query file: one query per line in the LIBRARY syntax  P1.{a,b}?P2...   (vlg_index.hpp:54-105).
 // Output of `locate`, one block per query:
 //   Q <line-no> <count>            or   E <line-no> <exception text>
@@ -119,7 +120,14 @@ int main(int argc, char** argv)
         if (argc < 5) return 2;
         auto queries = read_lines(abspath(argv[3]));
         int threads = atoi(argv[4]);
-        bool from_index = argc > 5 && std::string(argv[5]) == "--index";
+        bool from_index = false;
+        int steps = 1, warmup = 0;
+        for (int a = 5; a < argc; ++a) {
+            std::string opt = argv[a];
+            if (opt == "--index") from_index = true;
+            else if (opt == "--steps" && a + 1 < argc) steps = atoi(argv[++a]);
+            else if (opt == "--warmup" && a + 1 < argc) warmup = atoi(argv[++a]);
+        }
         vlg_index<> idx;
         auto t0 = std::chrono::steady_clock::now();
         if (from_index) {
@@ -133,30 +141,37 @@ int main(int argc, char** argv)
 
         // The matcher is single-threaded and const: split the query list over
         // worker threads that share the one index.
-        std::atomic<size_t> next(0);
-        std::vector<uint64_t> nres(threads, 0), csum(threads, 0);
-        auto t1 = std::chrono::steady_clock::now();
-        std::vector<std::thread> pool;
-        for (int t = 0; t < threads; ++t) {
-            pool.emplace_back([&, t]() {
-                size_t q;
-                while ((q = next.fetch_add(1)) < queries.size()) {
-                    try {
-                        auto res = locate(idx, queries[q]);
-                        for (auto it = res.begin(); it != res.end(); ++it) {
-                            nres[t]++;
-                            csum[t] += *it;  // same checksum as gm_search.cpp:110-114
-                        }
-                    } catch (const std::exception&) {
-                    }
-                }
-            });
-        }
-        for (auto& th : pool) th.join();
-        double search_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
+        std::vector<double> step_s;
         uint64_t r = 0, c = 0;
-        for (int t = 0; t < threads; ++t) { r += nres[t]; c += csum[t]; }
-        std::cout << "{\"build_s\": " << build_s << ", \"search_s\": " << search_s
+        double search_s = 0;
+        for (int pass = 0; pass < warmup + steps; ++pass) {
+            std::atomic<size_t> next(0);
+            std::vector<uint64_t> nres(threads, 0), csum(threads, 0);
+            auto t1 = std::chrono::steady_clock::now();
+            std::vector<std::thread> pool;
+            for (int t = 0; t < threads; ++t) {
+                pool.emplace_back([&, t]() {
+                    size_t q;
+                    while ((q = next.fetch_add(1)) < queries.size()) {
+                        try {
+                            auto res = locate(idx, queries[q]);
+                            for (auto it = res.begin(); it != res.end(); ++it) {
+                                nres[t]++;
+                                csum[t] += *it;  // same checksum as gm_search.cpp:110-114
+                            }
+                        } catch (const std::exception&) {
+                        }
+                    }
+                });
+            }
+            for (auto& th : pool) th.join();
+            double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
+            r = c = 0;
+            for (int t = 0; t < threads; ++t) { r += nres[t]; c += csum[t]; }
+            if (pass >= warmup) { step_s.push_back(dt); search_s += dt; }
+        }
+        search_s /= (double)step_s.size();
+        std::cout << "{\"build_s\": " << build_s << ", \"search_s\": " << search_s << ", \"steps\": " << step_s.size()
                   << ", \"queries\": " << queries.size() << ", \"threads\": " << threads
                   << ", \"text_bytes\": " << idx.text.size()
                   << ", \"num_results\": " << r << ", \"checksum\": " << c << "}" << std::endl;

@@ -59,15 +59,10 @@ def worker(rank, world, port, result_q):
         dist.all_gather(out, t)
         return torch.stack(out).numpy().view(np.uint64)
 
-    def broadcast(arr, src):
-        t = torch.from_numpy(arr.view(np.int64).copy())
-        dist.broadcast(t, src)
-        return t.numpy().view(np.uint64)
-
     def fixup(entry):
         return shard_search(text, queries, lo, hi, end, entry)
 
-    table, refixed = chain_cursors(rank, world, local, all_gather, broadcast, fixup)
+    table, refixed = chain_cursors(rank, world, local, all_gather, fixup)  # decisions: the library's vlgb_chain_plan
     result_q.put((rank, table.tolist(), refixed))
     dist.barrier()
     dist.destroy_process_group()
@@ -111,3 +106,22 @@ def test_shard_bounds_cover_text_once():
     b = shard_bounds(1000, 3, 50)
     assert b[0][0] == 0 and b[-1][1] == 1000 and all(b[i][1] == b[i + 1][0] for i in range(2))
     assert all(e == min(1000, h + 50) for _, h, e in b)
+
+
+def test_chain_plan_equals_numpy_protocol():
+    """vlgb_chain_plan (the host logic inside vlgb_search_sharded) against the numpy statement of the same rule."""
+    from vlg_matching_b200 import capi
+    from vlg_matching_b200.sharded import implied_entries
+    rng = np.random.default_rng(7)
+    for G, Q in ((1, 5), (2, 1), (3, 40), (8, 257)):
+        rows = np.zeros((G, Q, 3), dtype=np.uint64)
+        rows[:, :, 0] = rng.integers(0, 3, (G, Q))
+        rows[:, :, 1] = rng.integers(0, 1000, (G, Q))
+        rows[:, :, 2] = rng.integers(0, 1000, (G, Q))
+        used = rng.integers(0, 3, (G, Q)).astype(np.uint64) * np.uint64(300)
+        entries, redo = capi.chain_plan(rows, used)
+        want = implied_entries(rows)
+        cnt, first = rows[:, :, 0], rows[:, :, 2]
+        moved = want != used
+        harmless = (want > used) & ((cnt == 0) | (want <= first))
+        assert np.array_equal(entries, want) and np.array_equal(redo, (moved & ~harmless).any(axis=1))

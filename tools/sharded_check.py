@@ -1,37 +1,56 @@
 #!/usr/bin/env python
-"""Under torchrun (N >= 2): the sharded search of bench.py's workload (N x 200 MiB, halo overlap, cursor exchange,
-re-entry) must report exactly the counts a single index over the WHOLE text reports on rank 0's GPU."""
-import os, sys
+"""Under torchrun (N >= 2): vlgb_search_sharded over N ranks x SHARDS_PER_RANK shards of SHARD_MIB MiB each (halo
+overlap, NCCL cursor exchange inside the library, re-entry) must report, for EVERY query, exactly the match starts a
+single index over the WHOLE text reports inside each shard's owned range -- checked on every rank for its own shards.
+Used by tests/test_gpu_multi.py (2 GPUs) and by hand at 4 / 8."""
+import os
+import sys
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch, torch.distributed as dist
+import numpy as np
+import torch
+import torch.distributed as dist
+
 import bench
 from vlg_matching_b200 import capi, sharded
+
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-torch.cuda.set_device(local); capi.init(local)
+torch.cuda.set_device(local)
+capi.init(local)
 dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
+sharded.comm_init(rank, world, dist)
 mib = int(os.environ.get("SHARD_MIB", "200"))
+per = int(os.environ.get("SHARDS_PER_RANK", "1"))
+nq = int(os.environ.get("QUERIES", "1000"))
 n = mib << 20
-queries = bench.make_queries(); span = sharded.batch_span(queries)
-own = bench.shard_text(rank, n)
-host = np.concatenate([own, bench.shard_text(rank + 1, span)]) if rank + 1 < world else own
-idx = capi.Index.build(host, global_offset=rank * n, owned_len=n, total_len=n * world)
+S = world * per
+queries = bench.make_queries(nq)
+queries += [([b"e"], []), ([b" "], []), ([b"th"], []), ([b"e", b"t"], [(20, 300)])]  # dense lists: every boundary is crossed
+span = sharded.batch_span(queries)
+pieces = {g: bench.shard_text(g, n) for g in range(S)} if rank == 0 or True else {}
+shards = []
+for j in range(per):
+    g = rank * per + j
+    host = np.concatenate([pieces[g], pieces[g + 1][:span]]) if g + 1 < S else pieces[g]
+    shards.append(capi.Index.build(host, global_offset=g * n, owned_len=n, total_len=n * S))
 batch = capi.PackedBatch(queries)
-S = sharded.ShardedSearcher(idx, rank, world, dist, dev)
-r, gcounts, refixed = S.search(batch, capi.WANT_STARTS)
-local_counts = r.counts().copy()
-starts0 = [r.starts(q).copy() for q in range(0, len(queries), 97)]
-r.free(); idx.free()
-dist.barrier()
-if rank == 0:
-    whole = np.concatenate([bench.shard_text(g, n) for g in range(world)])
-    w = capi.Index.build(whole)
-    rw = w.search(batch, capi.WANT_STARTS)
-    wc = rw.counts().copy()
-    assert np.array_equal(wc, gcounts.astype(np.uint64)), np.nonzero(wc != gcounts)[0][:10]
-    for k, q in enumerate(range(0, len(queries), 97)):  # rank 0's own matches are the whole-text matches below n
+res, gcounts, st = capi.search_sharded(shards, batch, capi.WANT_STARTS)
+whole = np.concatenate([pieces[g] for g in range(S)])
+w = capi.Index.build(whole)
+rw = w.search(batch, capi.WANT_STARTS)
+assert np.array_equal(rw.counts(), gcounts), np.nonzero(rw.counts() != gcounts)[0][:10]
+for j in range(per):
+    lo, hi = (rank * per + j) * n, (rank * per + j + 1) * n
+    for q in range(len(queries)):
         ws = rw.starts(q)
-        assert np.array_equal(ws[ws < n], starts0[k]), q
-    print(f"sharded x{world} ({mib} MiB per shard): {int(wc.sum())} matches, per-query counts equal the single-index search; "
-          f"{refixed} shard re-entries; rank 0 starts equal", flush=True)
-dist.barrier(); dist.destroy_process_group()
+        assert np.array_equal(ws[(ws >= lo) & (ws < hi)], res[j].starts(q)), (rank, j, q)
+ok = torch.ones(1, device=dev)
+dist.all_reduce(ok)
+if rank == 0:
+    print(f"sharded x{world} ranks x{per} shards ({mib} MiB each): {int(gcounts.sum())} matches, starts of all {len(queries)} queries equal "
+          f"the single-index search on every rank; rounds {st['rounds']}, shards re-entered {st['reentered_shards']}, "
+          f"exchange {st['exchange_ms']:.3f} ms", flush=True)
+capi.comm_destroy()
+dist.barrier()
+dist.destroy_process_group()

@@ -33,7 +33,8 @@ SYMBOLS = [
     "vlgb_result_fixup", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
     "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
     "vlgb_parse_batch", "vlgb_parse_lines", "vlgb_index_attach_rank", "vlgb_index_rank_info", "vlgb_index_sa_extract",
-    "vlgb_set_path",
+    "vlgb_set_path", "vlgb_result_device_starts", "vlgb_result_device_tuples", "vlgb_comm_unique_id", "vlgb_comm_init",
+    "vlgb_comm_destroy", "vlgb_search_sharded", "vlgb_chain_plan",
 ]
 
 
@@ -117,6 +118,22 @@ lib.vlgb_index_attach_rank.argtypes = [_P, C.c_uint32]
 lib.vlgb_index_rank_info.argtypes = [_P, C.POINTER(RankInfo)]
 lib.vlgb_index_sa_extract.argtypes = [_P, C.c_uint64, C.c_uint64, _P]
 lib.vlgb_set_path.argtypes = [C.c_int]
+for _f in ("vlgb_result_device_starts", "vlgb_result_device_tuples"):
+    getattr(lib, _f).argtypes = [_P, C.c_uint32]
+    getattr(lib, _f).restype = C.c_void_p
+COMM_ID_BYTES = 128
+
+
+class ShardStats(C.Structure):
+    _fields_ = [("n_ranks", C.c_uint32), ("rounds", C.c_uint32), ("reentered_shards", C.c_uint32),
+                ("reentered_queries", C.c_uint32), ("exchange_ms", C.c_float), ("global_matches", C.c_uint64)]
+
+
+lib.vlgb_comm_unique_id.argtypes = [_P]
+lib.vlgb_comm_init.argtypes = [_P, C.c_int, C.c_int]
+lib.vlgb_search_sharded.argtypes = [C.POINTER(_P), C.c_uint32, C.POINTER(Batch), C.c_uint32, C.POINTER(_P), _P,
+                                    C.POINTER(ShardStats)]
+lib.vlgb_chain_plan.argtypes = [_P, _P, C.c_uint32, C.c_uint32, _P, _P]
 
 
 def check(rc):
@@ -144,6 +161,48 @@ def last_stats() -> dict:
             "segments": int(s.segments), "query_chunks": int(s.query_chunks),
             "total_occurrences": int(s.total_occurrences), "join_slots": int(s.join_slots),
             "list_path": {PATH_SCAN: "scan", PATH_RANK: "rank"}.get(int(s.list_path), "none"), "host_syncs": int(s.host_syncs)}
+
+
+def comm_unique_id() -> bytes:
+    buf = (C.c_uint8 * COMM_ID_BYTES)()
+    check(lib.vlgb_comm_unique_id(buf))
+    return bytes(buf)
+
+
+def comm_init(comm_id: bytes | None, n_ranks: int, rank: int):
+    """ncclCommInitRank on this thread's device (vlgb_init first).  n_ranks = 1 needs no id."""
+    buf = (C.c_uint8 * COMM_ID_BYTES).from_buffer_copy(comm_id) if comm_id else None
+    check(lib.vlgb_comm_init(buf, n_ranks, rank))
+
+
+def comm_destroy():
+    lib.vlgb_comm_destroy()
+
+
+def chain_plan(rows: np.ndarray, used: np.ndarray):
+    """vlgb_chain_plan: rows [G, Q, 3], used [G, Q] -> (entries [G, Q], redo bool [G]).  Pure host logic."""
+    rows = np.ascontiguousarray(rows, dtype=np.uint64)
+    used = np.ascontiguousarray(used, dtype=np.uint64)
+    g, q = used.shape
+    entries = np.zeros((g, q), dtype=np.uint64)
+    redo = np.zeros(max(g, 1), dtype=np.uint8)
+    rc = lib.vlgb_chain_plan(rows.ctypes.data, used.ctypes.data, g, q, entries.ctypes.data, redo.ctypes.data)
+    if rc < 0:
+        check(rc)
+    return entries, redo[:g].astype(bool)
+
+
+def search_sharded(shards, batch, want=WANT_STARTS):
+    """vlgb_search_sharded on this rank's shards (consecutive pieces of the text, left to right).
+    -> (results [one per local shard], global per-query counts over all ranks, stats dict)."""
+    n = len(shards)
+    hs = (_P * n)(*[s.h for s in shards])
+    rs = (_P * n)()
+    gc = np.zeros(max(len(batch), 1), dtype=np.uint64)
+    st = ShardStats()
+    check(lib.vlgb_search_sharded(hs, n, C.byref(batch.c), want, rs, gc.ctypes.data, C.byref(st)))
+    return ([Result(_P(rs[j]), batch, want) for j in range(n)], gc[:len(batch)],
+            {k: getattr(st, k) for k, _ in ShardStats._fields_})
 
 
 def set_path(path: int):
@@ -287,6 +346,13 @@ class Result:
         if not p or c == 0:
             return np.zeros((0, k), dtype=np.uint64)
         return np.ctypeslib.as_array(p, shape=(c * k,)).copy().reshape(c, k)
+
+    def device_starts(self, q) -> int:
+        """Device address of query q's match starts (u64, KEEP_ON_DEVICE results), 0 if none."""
+        return lib.vlgb_result_device_starts(self.h, q) or 0
+
+    def device_tuples(self, q) -> int:
+        return lib.vlgb_result_device_tuples(self.h, q) or 0
 
     def fixup(self, entry_cursor: np.ndarray) -> int:
         e = np.ascontiguousarray(entry_cursor, dtype=np.uint64)

@@ -31,13 +31,20 @@ struct HostBlock {  // pinned result memory
     size_t cap = 0;
 };
 
+struct DeviceBlock {  // device result memory owned by a result (VLGB_KEEP_ON_DEVICE)
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
 struct vlgb_result {
     uint32_t nq = 0;
     uint32_t want = 0;
     std::vector<int32_t> status;
     std::vector<uint64_t> counts, exit_cursor, occ;
-    std::vector<const uint64_t*> starts, tuples;
+    std::vector<const uint64_t*> starts, tuples;          // host (pinned blocks)
+    std::vector<const uint64_t*> dev_starts, dev_tuples;  // device (VLGB_KEEP_ON_DEVICE), nullptr otherwise
     std::vector<HostBlock> blocks;
+    std::vector<DeviceBlock> dev_blocks;
     uint64_t total = 0;
 };
 
@@ -77,6 +84,49 @@ struct PinnedPool {
 PinnedPool& pinned_pool()
 {
     static thread_local PinnedPool p;
+    return p;
+}
+
+// device result blocks are recycled the same way (cudaMalloc / cudaFree synchronise the device)
+struct DevicePool {
+    std::vector<DeviceBlock> free_list;
+    DeviceBlock take(size_t bytes)
+    {
+        size_t best = SIZE_MAX;
+        for (size_t i = 0; i < free_list.size(); i++)
+            if (free_list[i].cap >= bytes && (best == SIZE_MAX || free_list[i].cap < free_list[best].cap)) best = i;
+        if (best != SIZE_MAX && free_list[best].cap <= 4 * bytes + (1u << 20)) {
+            DeviceBlock b = free_list[best];
+            free_list.erase(free_list.begin() + best);
+            return b;
+        }
+        DeviceBlock b;
+        b.cap = bytes + bytes / 4 + 4096;
+        cudaError_t e = cudaMalloc(&b.p, b.cap);
+        if (e != cudaSuccess) {
+            for (auto& f : free_list) cudaFree(f.p);  // give the cached blocks back and try once more
+            free_list.clear();
+            e = cudaMalloc(&b.p, b.cap);
+        }
+        if (e != cudaSuccess) throw CudaError{e, __FILE__, __LINE__};
+        return b;
+    }
+    void give(DeviceBlock b)
+    {
+        if (free_list.size() >= 4) {
+            size_t small = 0;
+            for (size_t i = 1; i < free_list.size(); i++)
+                if (free_list[i].cap < free_list[small].cap) small = i;
+            if (free_list[small].cap < b.cap) std::swap(free_list[small], b);
+            cudaFree(b.p);
+            return;
+        }
+        free_list.push_back(b);
+    }
+};
+DevicePool& device_pool()
+{
+    static thread_local DevicePool p;
     return p;
 }
 
@@ -577,6 +627,8 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
     R.exit_cursor.assign(nq, 0);
     R.starts.assign(nq, nullptr);
     R.tuples.assign(nq, nullptr);
+    R.dev_starts.assign(nq, nullptr);
+    R.dev_tuples.assign(nq, nullptr);
     R.total = 0;
     R.ext.idx = idx;
     R.ext.entry.assign(nq, 0);
@@ -678,6 +730,12 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
                       R.blocks.push_back(hb);
                       return hb.p;
                   },
+                  [&](size_t nbytes) -> void* {
+                      if (!keep_device) return c.out_buf.get(nbytes);
+                      DeviceBlock db = device_pool().take(nbytes);
+                      R.dev_blocks.push_back(db);
+                      return db.p;
+                  },
                   co);
         for (size_t s = 0; s < chunk.size(); s++) {
             uint32_t q = chunk[s].q;
@@ -691,6 +749,8 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
             if (co.counts[s]) {
                 if (co.h_starts) R.starts[q] = co.h_starts + m;
                 if (co.h_tuples) R.tuples[q] = co.h_tuples + co.tuple_off[s];
+                if (keep_device && co.d_starts) R.dev_starts[q] = co.d_starts + m;
+                if (keep_device && co.d_tuples) R.dev_tuples[q] = co.d_tuples + co.tuple_off[s];
             }
             m += co.counts[s];
         }
@@ -733,6 +793,7 @@ extern "C" int vlgb_search_batch(const vlgb_index* idx, const vlgb_batch* batch,
             do_search(c, idx, batch, entry_cursor, want, *R);
         } catch (...) {
             for (auto& b : R->blocks) pinned_pool().give(b);
+            for (auto& b : R->dev_blocks) device_pool().give(b);
             throw;
         }
         copy_batch(batch, R->ext.batch);
@@ -759,10 +820,14 @@ extern "C" const uint64_t* vlgb_result_first_starts(const vlgb_result* r)
 }
 extern "C" uint64_t vlgb_result_occurrences(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->occ[q] : 0; }
 
+extern "C" const uint64_t* vlgb_result_device_starts(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->dev_starts[q] : nullptr; }
+extern "C" const uint64_t* vlgb_result_device_tuples(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->dev_tuples[q] : nullptr; }
+
 extern "C" void vlgb_result_free(vlgb_result* r)
 {
     if (!r) return;
     for (auto& b : r->blocks) pinned_pool().give(b);
+    for (auto& b : r->dev_blocks) device_pool().give(b);
     delete static_cast<ResultImpl*>(r);
 }
 
@@ -814,11 +879,19 @@ extern "C" int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, u
                 }
                 vlgb_stats keep = c.stats;
                 RefixOut ro;
-                run_refix(c, T, rs, re, R.want & 3u, (R.want & VLGB_KEEP_ON_DEVICE) != 0,
+                const bool keep_dev = (R.want & VLGB_KEEP_ON_DEVICE) != 0;
+                static thread_local DeviceBuffer fix_out;
+                run_refix(c, T, rs, re, R.want & 3u, keep_dev,
                           [&](size_t nbytes) {
                               HostBlock hb = pinned_pool().take(nbytes ? nbytes : 8);
                               R.blocks.push_back(hb);
                               return hb.p;
+                          },
+                          [&](size_t nbytes) -> void* {
+                              if (!keep_dev) return fix_out.get(nbytes);
+                              DeviceBlock db = device_pool().take(nbytes);
+                              R.dev_blocks.push_back(db);
+                              return db.p;
                           },
                           ro);
                 c.flush_timers();
@@ -835,6 +908,10 @@ extern "C" int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, u
                     if (host_lists && (R.want & 3u) >= VLGB_WANT_STARTS) R.starts[q] = ro.counts[i] && ro.h_starts ? ro.h_starts + m : EMPTY_LIST;
                     if (host_lists && (R.want & 3u) >= VLGB_WANT_TUPLES)
                         R.tuples[q] = ro.counts[i] && ro.h_tuples ? ro.h_tuples + ro.tuple_off[i] : EMPTY_LIST;
+                    if (keep_dev) {
+                        R.dev_starts[q] = ro.counts[i] && ro.d_starts ? ro.d_starts + m : nullptr;
+                        R.dev_tuples[q] = ro.counts[i] && ro.d_tuples ? ro.d_tuples + ro.tuple_off[i] : nullptr;
+                    }
                     m += ro.counts[i];
                 }
             }
@@ -876,13 +953,212 @@ extern "C" int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, u
         R.exit_cursor[q] = N.exit_cursor[i];
         R.starts[q] = N.starts[i];
         R.tuples[q] = N.tuples[i];
+        R.dev_starts[q] = N.dev_starts[i];
+        R.dev_tuples[q] = N.dev_tuples[i];
         R.status[q] = N.status[i];
         R.ext.entry[q] = entry_cursor[q];
         R.ext.first_start[q] = N.ext.first_start[i];
     }
     for (auto& b : N.blocks) R.blocks.push_back(b);  // the spliced lists live in the new result's blocks
     N.blocks.clear();
+    for (auto& b : N.dev_blocks) R.dev_blocks.push_back(b);
+    N.dev_blocks.clear();
     vlgb_result_free(nr);
     if (n_changed) *n_changed = (uint32_t)redo.size();
+    return VLGB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-GPU: overlap-sharded text, one rank per GPU, ONE small collective per round
+// ---------------------------------------------------------------------------------------------
+#include "comm.hpp"
+
+extern "C" int vlgb_chain_plan(const uint64_t* rows, const uint64_t* used, uint32_t n_shards, uint32_t nq, uint64_t* entries,
+                               uint8_t* redo)
+{
+    if ((!rows || !used || !entries) && n_shards && nq) return fail(VLGB_ERR_ARG, "vlgb_chain_plan: null argument");
+    if (!redo && n_shards) return fail(VLGB_ERR_ARG, "vlgb_chain_plan: null argument");
+    return (int)chain_plan(rows, used, n_shards, nq, entries, redo);
+}
+
+extern "C" int vlgb_comm_unique_id(uint8_t* id)
+{
+    if (!id) return fail(VLGB_ERR_ARG, "vlgb_comm_unique_id: null");
+    NcclApi& api = nccl_api();
+    if (!api.ok) return fail(VLGB_ERR_CUDA, "NCCL is not available (libnccl.so.2 could not be loaded)");
+    static_assert(sizeof(ncclUniqueId) == VLGB_COMM_ID_BYTES, "ncclUniqueId size");
+    ncclUniqueId u;
+    ncclResult_t rc = api.GetUniqueId(&u);
+    if (rc != ncclSuccess) return fail(VLGB_ERR_CUDA, "ncclGetUniqueId: %s", api.GetErrorString(rc));
+    memcpy(id, &u, sizeof u);
+    return VLGB_OK;
+}
+
+extern "C" int vlgb_comm_init(const uint8_t* id, int n_ranks, int rank)
+{
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(VLGB_ERR_ARG, "vlgb_comm_init: rank %d of %d", rank, n_ranks);
+    Comm& cm = comm();
+    if (cm.comm) return fail(VLGB_ERR_ARG, "vlgb_comm_init: this thread already has a communicator");
+    try {
+        ensure_ready();
+        if (n_ranks > 1) {
+            if (!id) return fail(VLGB_ERR_ARG, "vlgb_comm_init: null id");
+            NcclApi& api = nccl_api();
+            if (!api.ok) return fail(VLGB_ERR_CUDA, "NCCL is not available (libnccl.so.2 could not be loaded)");
+            ncclUniqueId u;
+            memcpy(&u, id, sizeof u);
+            ncclResult_t rc = api.CommInitRank(&cm.comm, n_ranks, u, rank);
+            if (rc != ncclSuccess) {
+                cm.comm = nullptr;
+                return fail(VLGB_ERR_CUDA, "ncclCommInitRank: %s", api.GetErrorString(rc));
+            }
+        }
+        cm.n_ranks = n_ranks;
+        cm.rank = rank;
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+extern "C" int vlgb_comm_destroy(void)
+{
+    Comm& cm = comm();
+    if (cm.comm) nccl_api().CommDestroy(cm.comm);
+    cm.comm = nullptr;
+    cm.n_ranks = 1;
+    cm.rank = 0;
+    return VLGB_OK;
+}
+
+namespace {
+
+// row of this rank: its local shards are consecutive in the text and already chained exactly
+void local_row(vlgb_result* const* res, uint32_t n_local, uint32_t nq, uint64_t* row)
+{
+    for (uint32_t q = 0; q < nq; q++) {
+        uint64_t cnt = 0, first = ~uint64_t(0);
+        for (uint32_t j = 0; j < n_local; j++) {
+            const ResultImpl& R = *static_cast<const ResultImpl*>(res[j]);
+            if (R.counts[q] && !cnt) first = R.ext.first_start[q];
+            cnt += R.counts[q];
+        }
+        row[3 * q] = cnt;
+        row[3 * q + 1] = static_cast<const ResultImpl*>(res[n_local - 1])->exit_cursor[q];
+        row[3 * q + 2] = first;
+    }
+}
+
+}  // namespace
+
+extern "C" int vlgb_search_sharded(const vlgb_index* const* shards, uint32_t n_local, const vlgb_batch* batch, uint32_t want,
+                                   vlgb_result** results, uint64_t* global_counts, vlgb_shard_stats* st)
+{
+    if (!shards || !n_local || !results) return fail(VLGB_ERR_ARG, "vlgb_search_sharded: null argument");
+    int rc = batch_check(batch);
+    if (rc) return rc;
+    const uint32_t nq = batch->n_queries;
+    for (uint32_t j = 0; j < n_local; j++) results[j] = nullptr;
+    auto cleanup = [&](int code) {
+        for (uint32_t j = 0; j < n_local; j++) {
+            vlgb_result_free(results[j]);
+            results[j] = nullptr;
+        }
+        return code;
+    };
+    vlgb_shard_stats S;
+    memset(&S, 0, sizeof S);
+    Comm& cm = comm();
+    S.n_ranks = (uint32_t)cm.n_ranks;
+    // ---- the local shards, left to right; shard j enters with the cursors shard j-1 left (exact inside the rank)
+    vlgb_stats acc;
+    memset(&acc, 0, sizeof acc);
+    std::vector<uint64_t> entry(nq, 0);
+    for (uint32_t j = 0; j < n_local; j++) {
+        rc = vlgb_search_batch(shards[j], batch, j ? entry.data() : nullptr, want, &results[j]);
+        if (rc) return cleanup(rc);
+        const ResultImpl& R = *static_cast<const ResultImpl*>(results[j]);
+        entry = R.exit_cursor;
+        if (n_local > 1) {  // stage times of all local shards add up in vlgb_last_stats
+            Context& c = ctx();
+            c.flush_timers();
+            for (uint32_t s = 0; s < ST_COUNT; s++) {
+                acc.ms[s] += c.stats.ms[s];
+                acc.bytes[s] += c.stats.bytes[s];
+                acc.launches[s] += c.stats.launches[s];
+            }
+            acc.h2d_bytes += c.stats.h2d_bytes;
+            acc.d2h_bytes += c.stats.d2h_bytes;
+            acc.distinct_patterns = c.stats.distinct_patterns;
+            acc.scan_passes += c.stats.scan_passes;
+            acc.segments += c.stats.segments;
+            acc.query_chunks += c.stats.query_chunks;
+            acc.total_occurrences += c.stats.total_occurrences;
+            acc.join_slots += c.stats.join_slots;
+            acc.list_path = c.stats.list_path;
+            acc.host_syncs += c.stats.host_syncs;
+        }
+    }
+    if (n_local > 1) ctx().stats = acc;
+    const uint32_t G = (uint32_t)cm.n_ranks;
+    std::vector<uint64_t> table((size_t)G * nq * 3);
+    try {
+        if (G > 1 && nq) {
+            Context& c = ctx();
+            NcclApi& api = nccl_api();
+            const double t0 = HostTrace::now();
+            const size_t row_words = (size_t)nq * 3;
+            uint64_t* d_buf = (uint64_t*)cm.dev.get((G + 1) * row_words * 8);
+            uint64_t* h_buf = (uint64_t*)cm.host.get((G + 1) * row_words * 8);
+            std::vector<uint64_t> used((size_t)G * nq, 0), entries((size_t)G * nq, 0);
+            std::vector<uint8_t> redo(G, 0);
+            for (uint32_t round = 0; round <= G; round++) {
+                local_row(results, n_local, nq, h_buf);
+                VLGB_CUDA(cudaMemcpyAsync(d_buf, h_buf, row_words * 8, cudaMemcpyHostToDevice, c.stream));
+                ncclResult_t nrc = api.AllGather(d_buf, d_buf + row_words, row_words, ncclUint64, cm.comm, c.stream);
+                if (nrc != ncclSuccess) return cleanup(fail(VLGB_ERR_CUDA, "ncclAllGather: %s", api.GetErrorString(nrc)));
+                VLGB_CUDA(cudaMemcpyAsync(h_buf + row_words, d_buf + row_words, G * row_words * 8, cudaMemcpyDeviceToHost, c.stream));
+                VLGB_CUDA(cudaStreamSynchronize(c.stream));
+                memcpy(table.data(), h_buf + row_words, G * row_words * 8);
+                S.rounds++;
+                const uint32_t n_redo = chain_plan(table.data(), used.data(), G, nq, entries.data(), redo.data());
+                // record the cursors on this rank (harmless moves change no match but do change the exit cursor of
+                // queries without one); search again only what can change -- vlgb_result_fixup decides per query
+                const uint64_t* mine = entries.data() + (size_t)cm.rank * nq;
+                if (memcmp(mine, used.data() + (size_t)cm.rank * nq, (size_t)nq * 8) != 0) {
+                    std::vector<uint64_t> e(mine, mine + nq);
+                    for (uint32_t j = 0; j < n_local; j++) {
+                        uint32_t changed = 0;
+                        vlgb_stats keep = c.stats;
+                        rc = vlgb_result_fixup(results[j], e.data(), &changed);
+                        c.stats = keep;
+                        if (rc) return cleanup(rc);
+                        S.reentered_queries += changed;
+                        e = static_cast<const ResultImpl*>(results[j])->exit_cursor;
+                    }
+                }
+                used = entries;
+                if (!n_redo) break;
+                S.reentered_shards += n_redo;
+            }
+            // rows of shards without a match carry the cursor through
+            S.exchange_ms = (float)(HostTrace::now() - t0);
+        } else {
+            local_row(results, n_local, nq, table.data());
+        }
+    } catch (const CudaError& e) {
+        return cleanup(cuda_fail(e));
+    } catch (const std::bad_alloc&) {
+        return cleanup(fail(VLGB_ERR_NOMEM, "out of host memory"));
+    }
+    if (global_counts)
+        for (uint32_t q = 0; q < nq; q++) {
+            uint64_t s = 0;
+            for (uint32_t g = 0; g < G; g++) s += table[((size_t)g * nq + q) * 3];
+            global_counts[q] = s;
+        }
+    for (uint32_t q = 0; q < nq; q++)
+        for (uint32_t g = 0; g < G; g++) S.global_matches += table[((size_t)g * nq + q) * 3];
+    if (st) *st = S;
     return VLGB_OK;
 }

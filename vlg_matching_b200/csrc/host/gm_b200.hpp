@@ -13,9 +13,12 @@
 #pragma once
 #include <sys/stat.h>
 
+#include <pthread.h>
+
 #include <algorithm>
 #include <chrono>
 #include <map>
+#include <thread>
 
 #include "vlg_b200.hpp"
 
@@ -232,6 +235,100 @@ private:
     vlg_b200::vlg_index<> m_keep;  // set by load()
     bool m_symbols = false;
 };
+
+// ---- several GPUs in ONE process: one host thread per GPU drives one rank of vlgb_search_sharded (the
+// other way to drive it is one process per GPU, bench.py).  The text is cut into n_gpus contiguous shards that overlap
+// by the largest span of the pattern file; every rank answers all patterns on its shard; the NCCL exchange of the
+// non-overlap cursors (pull_forward state, vlg_index.hpp:253-264) happens inside the library.
+struct multi_gpu_run {
+    std::vector<gapped_search_result> results;  // per pattern, whole-text positions, ascending
+    double seconds = 0;                         // slowest rank, search only (shards resident)
+    vlgb_shard_stats stats;
+};
+
+inline multi_gpu_run search_batch_multi_gpu(const std::vector<uint8_t>& text, const std::vector<gapped_pattern>& pats, int n_gpus)
+{
+    multi_gpu_run run;
+    memset(&run.stats, 0, sizeof run.stats);
+    run.results.resize(pats.size());
+    if (pats.empty() || n_gpus < 1) return run;
+    if (vlgb_device_count() < n_gpus) throw std::runtime_error("search_batch_multi_gpu: fewer CUDA devices than --gpus");
+    vlg_b200::detail::packed_batch pb;
+    std::vector<char> possible(pats.size(), 1);
+    uint64_t span = 0;
+    for (size_t i = 0; i < pats.size(); i++) {
+        std::vector<std::string> subs;
+        uint64_t sp = 0;
+        for (size_t j = 0; j < pats[i].subpatterns.size(); j++) {
+            const string_type& s = pats[i].subpatterns[j];
+            std::string e(s.size(), '\0');
+            for (size_t c = 0; c < s.size(); c++) {
+                if (s[c] == 0 || s[c] > 255) possible[i] = 0;
+                e[c] = (char)s[c];
+            }
+            sp += s.size() + (j < pats[i].gaps.size() ? pats[i].gaps[j].second : 0);
+            subs.push_back(std::move(e));
+        }
+        if (possible[i]) {
+            pb.add(subs, pats[i].gaps);
+            span = std::max(span, sp);
+        }
+    }
+    vlgb_batch batch = pb.view();
+    const uint64_t n = text.size();
+    uint8_t id[VLGB_COMM_ID_BYTES] = {0};
+    if (n_gpus > 1) vlg_b200::detail::check(vlgb_comm_unique_id(id));
+    pthread_barrier_t bar;
+    pthread_barrier_init(&bar, nullptr, (unsigned)n_gpus);
+    std::vector<std::vector<std::vector<uint64_t>>> part(n_gpus, std::vector<std::vector<uint64_t>>(batch.n_queries));
+    std::vector<double> secs(n_gpus, 0.0);
+    std::vector<std::string> errors(n_gpus);
+    std::vector<vlgb_shard_stats> st(n_gpus);
+    auto worker = [&](int r) {
+        vlgb_index* shard = nullptr;
+        vlgb_result* res = nullptr;
+        bool armed = true;  // every thread reaches every barrier, whatever fails
+        int rc = vlgb_init(r);
+        if (rc == VLGB_OK) rc = vlgb_comm_init(n_gpus > 1 ? id : nullptr, n_gpus, r);
+        const uint64_t lo = n * (uint64_t)r / n_gpus, hi = n * (uint64_t)(r + 1) / n_gpus, end = std::min(n, hi + span);
+        if (rc == VLGB_OK) rc = vlgb_index_build(text.data() + lo, end - lo, lo, hi - lo, n, &shard);
+        if (rc != VLGB_OK) errors[r] = vlgb_last_error();
+        pthread_barrier_wait(&bar);
+        bool all_ok = true;
+        for (int g = 0; g < n_gpus; g++) all_ok = all_ok && errors[g].empty();
+        if (all_ok) {
+            const vlgb_index* one[1] = {shard};
+            auto t0 = std::chrono::high_resolution_clock::now();
+            rc = vlgb_search_sharded(one, 1, &batch, VLGB_WANT_STARTS, &res, nullptr, &st[r]);
+            secs[r] = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - t0).count();
+            if (rc != VLGB_OK) errors[r] = vlgb_last_error();
+            else
+                for (uint32_t q = 0; q < batch.n_queries; q++) {
+                    const uint64_t c = vlgb_result_count(res, q);
+                    const uint64_t* s = vlgb_result_starts(res, q);
+                    if (c && s) part[r][q].assign(s, s + c);
+                }
+        }
+        (void)armed;
+        vlgb_result_free(res);
+        vlgb_index_free(shard);
+        vlgb_comm_destroy();
+    };
+    std::vector<std::thread> pool;
+    for (int r = 0; r < n_gpus; r++) pool.emplace_back(worker, r);
+    for (auto& t : pool) t.join();
+    pthread_barrier_destroy(&bar);
+    for (int r = 0; r < n_gpus; r++)
+        if (!errors[r].empty()) throw std::runtime_error("rank " + std::to_string(r) + ": " + errors[r]);
+    for (size_t i = 0, q = 0; i < pats.size(); i++) {
+        if (!possible[i]) continue;
+        for (int r = 0; r < n_gpus; r++) run.results[i].positions.insert(run.results[i].positions.end(), part[r][q].begin(), part[r][q].end());
+        q++;
+    }
+    run.seconds = *std::max_element(secs.begin(), secs.end());
+    run.stats = st[0];
+    return run;
+}
 
 // timings.hpp:33-62
 struct timing_results {

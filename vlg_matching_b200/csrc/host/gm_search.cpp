@@ -5,6 +5,8 @@
 // *_time_mus, prep_*_time_mus), so outputs diff against the reference harness.
 // -b 1 (extension) answers the whole pattern file in ONE device pass (index_b200::search_batch); the per-pattern
 // TIMING lines then carry the batch time divided by the number of patterns.
+// -g N / --gpus N (extension, implies -b 1, byte texts): the text of the collection is cut into N overlapping shards,
+// one per GPU, one host thread per GPU; the cursor exchange runs over NCCL inside the library (vlgb_search_sharded).
 #include <getopt.h>
 
 #include "gm_b200.hpp"
@@ -31,13 +33,15 @@ int main(int argc, char* const argv[])
 {
     std::string dir, pattern_file;
     bool string_patterns = true, batch = false;
-    int op;
-    while ((op = getopt(argc, argv, "c:p:t:b:")) != -1) {
+    int op, gpus = 1;
+    static const option long_opts[] = {{"gpus", required_argument, nullptr, 'g'}, {nullptr, 0, nullptr, 0}};
+    while ((op = getopt_long(argc, argv, "c:p:t:b:g:", long_opts, nullptr)) != -1) {
         switch (op) {
             case 'c': dir = optarg; break;
             case 'p': pattern_file = optarg; break;
             case 't': string_patterns = std::string(optarg) == "1"; break;
             case 'b': batch = std::string(optarg) == "1"; break;
+            case 'g': gpus = atoi(optarg); break;
         }
     }
     if (dir.empty() || pattern_file.empty()) {
@@ -47,6 +51,34 @@ int main(int argc, char* const argv[])
     try {
         gm_b200::collection col(dir);
         auto patterns = gm_b200::parse_pattern_file(pattern_file, string_patterns);
+        if (gpus > 1) {  // sharded over several GPUs: built from the collection's text, one shard per device
+            const std::vector<uint64_t> sym = vlg_b200::read_sdsl_int_vector(col.file_map["TEXT"]);
+            std::vector<uint8_t> text(sym.size());
+            for (size_t i = 0; i < sym.size(); i++) {
+                if (sym[i] == 0 || sym[i] > 255) throw std::runtime_error("--gpus needs a byte text");
+                text[i] = (uint8_t)sym[i];
+            }
+            gm_b200::multi_gpu_run run = gm_b200::search_batch_multi_gpu(text, patterns, gpus);
+            size_t num_results = 0, checksum = 0;
+            gm_b200::timing_results t_prep, t;
+            for (size_t i = 0; i < patterns.size(); i++) {
+                t_prep.add_timing(nanoseconds(0));
+                t.add_timing(nanoseconds((long long)(run.seconds * 1e9 / patterns.size())));
+                std::cout << "TIMING = " << (long long)(run.seconds * 1e6 / patterns.size()) << std::endl;
+                for (uint64_t pos : run.results[i].positions) {
+                    checksum += pos;
+                    num_results++;
+                }
+            }
+            std::cout << "# gpus = " << gpus << std::endl;
+            std::cout << "# exchange_rounds = " << run.stats.rounds << std::endl;
+            std::cout << "# shards_reentered = " << run.stats.reentered_shards << std::endl;
+            std::cout << "# num_results = " << num_results << std::endl;
+            std::cout << "# checksum = " << checksum << std::endl;
+            print_summary("", t);
+            print_summary("prep_", t_prep);
+            return 0;
+        }
         INDEX_TYPE idx;
         const std::string input_file = col.path + "/index/index-" + idx.name() + "-" + idx.class_hash() + ".sdsl";
         std::ifstream ifs(input_file.c_str(), std::ios::binary);

@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     uint32_t* mrow = a.matrix + (size_t)row * a.s_stride;
 
     const uint32_t lo = row * a.chunk;
-    const uint32_t hi = min(lo + a.chunk, a.valid_len);
+    const uint32_t hi = (uint32_t)min((uint64_t)lo + a.chunk, (uint64_t)a.valid_len);  // 64-bit: lo + chunk may pass 2^32 in the last row
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint32_t qhead = 0, qcount = 0;  // warp-uniform
     uint32_t nh = 0;                 // occurrences recorded in the row's hit stream (pass 1)

@@ -207,7 +207,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         VLGB_CUDA(cudaMemsetAsync(pd[p].matrix, 0, (size_t)rows * pd[p].stride * 4, c.stream));
         if (a.has_short) scan_kernel<false, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
         else scan_kernel<false, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-        c.end(ST_SCAN_COUNT, 1, n + (uint64_t)rows * pd[p].s_act * 4);  // + 4 B per occurrence streamed, added below
+        c.end(ST_SCAN_COUNT, 1, n);  // n read + 4 B per occurrence (added below once the counts are known)
         c.begin(ST_SCAN_OFFSETS);
         dim3 g((pd[p].stride + 127) / 128, nrb);
         scan_colsum_kernel<<<g, 128, 0, c.stream>>>(pd[p].matrix, rows, pd[p].stride, pd[p].part);
@@ -253,7 +253,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         if (pocc && streamed) {  // scatter the recorded occurrences; only overflowed rows are scanned again
             scan_scatter_kernel<<<std::min<uint32_t>(rows, 3u * (uint32_t)c.sm_count), SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
             launches++;
-            bytes += pocc * 8 + (uint64_t)rows * pd[p].s_act * 4;
+            bytes += pocc * 8;  // 4 B per occurrence read from the stream + 4 B written to its list
             c.stats.bytes[ST_SCAN_COUNT] += pocc * 4;
         }
         if (pocc && (!streamed || overflow[p])) {
@@ -261,7 +261,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
             if (a.has_short) scan_kernel<true, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
             else scan_kernel<true, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
             launches++;
-            if (!streamed) bytes += n + (uint64_t)rows * pd[p].s_act * 4 + pocc * 4;
+            if (!streamed) bytes += n + pocc * 4;
         }
         c.end(ST_SCAN_FILL, launches, bytes);
     }
@@ -423,6 +423,8 @@ struct ChunkOut {  // per query of the chunk, chunk order
     uint64_t matches = 0, tuple_words = 0;
     uint64_t* h_starts = nullptr;  // pinned (inside block)
     uint64_t* h_tuples = nullptr;
+    uint64_t* d_starts = nullptr;  // device copies (owned by the result when VLGB_KEEP_ON_DEVICE, else scratch)
+    uint64_t* d_tuples = nullptr;
     std::vector<uint64_t> tuple_off;
 };
 
@@ -478,7 +480,7 @@ struct Retained {
     uint32_t* scratch = nullptr;
     uint64_t* d_counts = nullptr;
     uint64_t* d_tuple_off = nullptr;
-    DeviceBuffer fix_buf, fix_out;
+    DeviceBuffer fix_buf;
 };
 inline Retained& retained()
 {
@@ -488,9 +490,11 @@ inline Retained& retained()
 
 // `qs` sorted by k descending.  Results land in `co`; starts/tuples (if wanted) in the pinned block
 // `hb` (grown by the caller-supplied allocator).
-template <class PinnedAlloc>
+// `device_alloc(bytes)` returns device memory for the starts / tuples of the chunk: a block owned by the result when
+// the caller keeps them on the device, the thread's reusable output buffer otherwise.
+template <class PinnedAlloc, class DeviceAlloc>
 inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuery>& qs, uint32_t want, bool keep_device,
-                      PinnedAlloc&& pinned_alloc, ChunkOut& co)
+                      PinnedAlloc&& pinned_alloc, DeviceAlloc&& device_alloc, ChunkOut& co)
 {
     const uint32_t nq = (uint32_t)qs.size();
     const uint32_t kmax = qs[0].k;
@@ -930,7 +934,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             size_t ob = 0;
             if (want_starts) ob += Arena::padded(co.matches, 8);
             if (want_tuples) ob += Arena::padded(co.tuple_words, 8);
-            uint8_t* o = (uint8_t*)c.out_buf.get(ob + 256);
+            uint8_t* o = (uint8_t*)device_alloc(ob + 256);
             if (want_starts) {
                 d_starts = (uint64_t*)o;
                 o += Arena::padded(co.matches, 8);
@@ -942,6 +946,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             }
             S.starts = d_starts;
             S.tuples = d_tuples;
+            co.d_starts = d_starts;
+            co.d_tuples = d_tuples;
             c.begin(ST_EMIT);
             sel_emit_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
             c.end(ST_EMIT, 1, co.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? co.tuple_words * 12 : 0));
@@ -988,11 +994,13 @@ struct RefixOut {
     uint64_t matches = 0, tuple_words = 0;
     uint64_t* h_starts = nullptr;
     uint64_t* h_tuples = nullptr;
+    uint64_t* d_starts = nullptr;
+    uint64_t* d_tuples = nullptr;
 };
 
-template <class PinnedAlloc>
+template <class PinnedAlloc, class DeviceAlloc>
 inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo, const std::vector<uint64_t>& entry,
-                      uint32_t want, bool keep_device, PinnedAlloc&& pinned_alloc, RefixOut& ro)
+                      uint32_t want, bool keep_device, PinnedAlloc&& pinned_alloc, DeviceAlloc&& device_alloc, RefixOut& ro)
 {
     trace() = HostTrace();
     const uint32_t nr = (uint32_t)redo.size(), nq = T.nq;
@@ -1054,7 +1062,7 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     size_t ob = 256;
     if (want_starts) ob += Arena::padded(ro.matches, 8);
     if (want_tuples) ob += Arena::padded(ro.tuple_words, 8);
-    uint8_t* o = (uint8_t*)T.fix_out.get(ob);
+    uint8_t* o = (uint8_t*)device_alloc(ob);
     uint64_t *d_starts = nullptr, *d_tuples = nullptr;
     if (want_starts) {
         d_starts = (uint64_t*)o;
@@ -1067,6 +1075,8 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     }
     S.starts = d_starts;
     S.tuples = d_tuples;
+    ro.d_starts = d_starts;
+    ro.d_tuples = d_tuples;
     c.begin(ST_EMIT);
     sel_emit_kernel<<<T.ntiles, SEL_TILE, 0, c.stream>>>(S);
     c.end(ST_EMIT, 1, ro.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? ro.tuple_words * 12 : 0));

@@ -1,17 +1,16 @@
-"""Multi-GPU search: contiguous text shards that overlap by the maximum query span, one process per
-GPU, every rank answers the whole query batch on its shard.
+"""Multi-GPU search: contiguous text shards that overlap by the maximum query span, one rank per GPU, every rank
+answers the whole query batch on its shards.
 
-The only exchange is tiny: per (query, shard) the match count, the exit cursor and the first reported
-start (24 B).  One all-gather, then the non-overlap cursor is chained left to right: shard g enters
-with the cursor shard g-1 left (vlg_iterator::pull_forward state, vlg_index.hpp:253-264).  Shards
-whose true entry cursor lies beyond their first speculative match re-enter on the device
-(vlgb_result_fixup), all at once, followed by another all-gather; this repeats until no entry cursor
-moves (chain_cursors).  Every rank derives the same decisions from the gathered data, so the collective
-sequence is identical on all ranks.  A match is owned by the shard that contains its first
-subpattern's start, so no match is reported twice.
+The exchange lives in the library (vlgb_search_sharded, csrc/engine.cu + csrc/comm.hpp): per round ONE NCCL
+all-gather of (match count, exit cursor, first start) per query and rank -- 24 B -- then every rank derives every
+rank's true entry cursor (the pull_forward state handed over the boundary, vlg_index.hpp:253-264) and the ranks whose
+reported set can change re-enter on the device (vlgb_result_fixup).  A match is owned by the shard that contains
+its first subpattern's start, so no match is reported twice and no match data crosses NVLink.
 
-torch.distributed is plumbing only (NCCL on the GPU box, gloo in the CPU tests); `search_fn` /
-`fixup_fn` are injected so the protocol itself can be tested without a GPU.
+This module is the thin Python caller: shard geometry, communicator bootstrap over torch.distributed (plumbing:
+only the 128-byte NCCL id travels through it), and `chain_cursors`, the same round protocol written against
+injected search/all-gather functions so that it can run on CPU over gloo -- its decisions come from the library's
+own host logic (vlgb_chain_plan).
 """
 from __future__ import annotations
 
@@ -21,7 +20,7 @@ NONE = np.uint64(0xFFFFFFFFFFFFFFFF)
 
 
 def shard_bounds(total_len: int, world: int, span: int):
-    """[(lo, hi, end)] per rank: owned [lo, hi), resident [lo, end) with end = min(total, hi + span)."""
+    """[(lo, hi, end)] per shard: owned [lo, hi), resident [lo, end) with end = min(total, hi + span)."""
     cuts = [total_len * g // world for g in range(world + 1)]
     return [(cuts[g], cuts[g + 1], min(total_len, cuts[g + 1] + span)) for g in range(world)]
 
@@ -32,8 +31,8 @@ def batch_span(queries) -> int:
 
 
 def implied_entries(table: np.ndarray):
-    """Entry cursor of every shard implied by the gathered rows: shard g enters with the cursor the nearest
-    shard to its left that reported a match left behind (0 for shard 0)."""
+    """Entry cursor of every shard implied by the gathered rows (numpy statement of vlgb_chain_plan's `entries`,
+    kept for the tests that compare the two)."""
     world, nq = table.shape[0], table.shape[1]
     cursor = np.zeros(nq, dtype=np.uint64)
     entries = np.zeros((world, nq), dtype=np.uint64)
@@ -43,87 +42,59 @@ def implied_entries(table: np.ndarray):
     return entries
 
 
-def chain_cursors(rank: int, world: int, local: np.ndarray, all_gather, broadcast, fixup):
-    """local: uint64 [Q, 3] = (count, exit_cursor, first_start) of this rank's speculative result
-    (entry cursor 0).  all_gather(arr) -> [world, Q, 3]; fixup(entry[Q]) -> new local [Q, 3] (re-enters the
-    shard on the device for the queries that can change, vlgb_result_fixup).  `broadcast` is unused (kept for
-    callers of the earlier sequential protocol).
+def chain_cursors(rank: int, world: int, local: np.ndarray, all_gather, fixup, plan=None):
+    """The round protocol of vlgb_search_sharded with the search injected (CPU tests over gloo).
+    local: uint64 [Q, 3] = (count, exit_cursor, first_start) of this rank's speculative result (entry cursor 0);
+    all_gather(arr) -> [world, Q, 3]; fixup(entry[Q]) -> new local [Q, 3]; plan(rows, used) -> (entries, redo),
+    default the library's vlgb_chain_plan.
     Returns (table [world, Q, 3] with the final values, number of shard re-entries over all rounds).
 
-    Rounds instead of a left-to-right walk: after the first all-gather every shard knows the cursor its left
-    neighbours would hand it.  All shards whose reported set can change under that cursor re-enter AT THE SAME
-    TIME, then one more all-gather.  A re-entered shard almost always leaves the same exit cursor (orbits of the
-    monotone successor coalesce within a few matches), so the second table already is the fixpoint; when an
-    exit cursor did move, the shards to its right go again.  Shard g is final after round g at the latest, so
-    the loop ends after <= world rounds -- typically 1 -- and costs one small collective per round instead of
-    one per shard.  Every rank derives the same decisions from the same table, so the collective sequence is
-    identical on all ranks."""
-    del broadcast
+    After the first all-gather every shard knows the cursor its left neighbours would hand it.  All shards whose
+    reported set can change under that cursor re-enter AT THE SAME TIME, then one more all-gather.  A re-entered
+    shard almost always leaves the same exit cursor (orbits of the monotone successor coalesce within a few
+    matches), so the second table already is the fixpoint; when an exit cursor did move, the shards to its right go
+    again.  Shard g is final after round g at the latest.  Every rank derives the same decisions from the same
+    table, so the collective sequence is identical on all ranks."""
+    if plan is None:
+        from . import capi
+        plan = capi.chain_plan
     table = all_gather(local)
     nq = local.shape[0]
     used = np.zeros((world, nq), dtype=np.uint64)  # entry cursor every shard's current row was computed with
     refixed = 0
-    for _ in range(world):
-        entries = implied_entries(table)
-        cnt, first = table[:, :, 0], table[:, :, 2]
-        # same rule as vlgb_result_fixup: a query is searched again unless the cursor is unchanged, or moved
-        # right without passing the first reported start (no match: nothing to report either way)
-        moved = entries != used
-        harmless = (entries > used) & ((cnt == 0) | (entries <= first))
-        redo = (moved & ~harmless).any(axis=1)
-        if moved[rank].any():
+    for _ in range(world + 1):
+        entries, redo = plan(table, used)
+        if (entries[rank] != used[rank]).any():
             local = fixup(entries[rank].copy())  # records the cursors; searches again only what can change
         used = entries
         if not redo.any():
             # rows of shards without a match carry the cursor through
-            table[:, :, 1] = np.where(cnt > 0, table[:, :, 1], entries)
+            table[:, :, 1] = np.where(table[:, :, 0] > 0, table[:, :, 1], entries)
             break
         refixed += int(redo.sum())
         table = all_gather(local)
     return table, refixed
 
 
+def comm_init(rank: int, world: int, dist=None):
+    """Create the library's NCCL communicator for this rank.  The 128-byte id travels over torch.distributed."""
+    from . import capi
+    if world == 1:
+        capi.comm_init(None, 1, 0)
+        return
+    obj = [capi.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(obj, src=0)
+    capi.comm_init(obj[0], world, rank)
+
+
 class ShardedSearcher:
-    """One instance per rank.  `index` is this rank's capi.Index built over [lo, end) with
-    global_offset=lo, owned_len=hi-lo, total_len=total."""
+    """One instance per rank: `shards` are this rank's capi.Index objects, consecutive pieces of the text, each built
+    over [lo, end) with global_offset=lo, owned_len=hi-lo, total_len=total.  comm_init() must have run."""
 
-    def __init__(self, index, rank: int, world: int, dist=None, device=None):
-        self.index, self.rank, self.world, self.dist, self.device = index, rank, world, dist, device
-
-    def _all_gather(self, arr):
-        if self.world == 1:
-            return arr[None].copy()
-        import torch
-        # persistent pinned host + device buffers: two async copies and one NCCL call, no allocation per step
-        key = arr.shape
-        if getattr(self, "_ag_key", None) != key:
-            n = int(np.prod(arr.shape))
-            self._ag_host_in = torch.empty(n, dtype=torch.int64).pin_memory()
-            self._ag_host_out = torch.empty(self.world * n, dtype=torch.int64).pin_memory()
-            self._ag_dev_in = torch.empty(n, dtype=torch.int64, device=self.device)
-            self._ag_dev_out = torch.empty(self.world * n, dtype=torch.int64, device=self.device)
-            self._ag_key = key
-        self._ag_host_in.numpy()[:] = arr.reshape(-1).view(np.int64)
-        self._ag_dev_in.copy_(self._ag_host_in, non_blocking=True)
-        self.dist.all_gather_into_tensor(self._ag_dev_out, self._ag_dev_in)
-        self._ag_host_out.copy_(self._ag_dev_out, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        return self._ag_host_out.numpy().view(np.uint64).reshape((self.world,) + tuple(arr.shape)).copy()
-
-    def _broadcast(self, arr, src):
-        import torch
-        t = torch.from_numpy(arr.view(np.int64).copy()).to(self.device)
-        self.dist.broadcast(t, src)
-        return t.cpu().numpy().view(np.uint64)
+    def __init__(self, shards):
+        self.shards = list(shards) if isinstance(shards, (list, tuple)) else [shards]
 
     def search(self, batch, want):
-        """-> (local capi.Result holding this shard's owned matches, global counts [Q], shards re-entered)."""
-        r = self.index.search(batch, want)
-        local = np.stack([r.counts(), r.exit_cursors(), r.first_starts()], axis=1).astype(np.uint64)
-
-        def fixup(entry):
-            r.fixup(entry)
-            return np.stack([r.counts(), r.exit_cursors(), r.first_starts()], axis=1).astype(np.uint64)
-
-        table, refixed = chain_cursors(self.rank, self.world, local, self._all_gather, self._broadcast, fixup)
-        return r, table[:, :, 0].sum(axis=0), refixed
+        """-> (results per local shard, global per-query counts over all ranks, stats of the exchange)."""
+        from . import capi
+        return capi.search_sharded(self.shards, batch, want)
