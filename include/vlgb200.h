@@ -145,6 +145,15 @@ int vlgb_index_rank_info(const vlgb_index* idx, vlgb_rank_info* out);
 /* Copy SA[first .. first+count) to the host, read THROUGH the wavelet tree on the device (wt_int::operator[],
  * wt_int.hpp:339-361) -- what a caller of vlg_index::wt[i] gets.  Needs vlgb_index_attach_rank. */
 int vlgb_index_sa_extract(const vlgb_index* idx, uint64_t first, uint64_t count, uint64_t* out);
+/* Pattern generation for the reference's experiment grid (examples/generate-pattern.cpp:1-120, driven by
+ * benchmark/gapped-matching/Makefile:90-106): the `count` most frequent substrings of `length` symbols whose symbols
+ * all belong to `charset` (0 = alpha-numerical + '_', 1 = 0 plus ' ', 2 = any: the tool's human_readable = 0), in the
+ * order the reference prints them, padded by repetition when the text has fewer.  The reference walks a compressed
+ * suffix tree; here the runs of equal `length`-prefixes in the suffix array are counted on the device.
+ * out: count * length bytes; occ (nullable): count occurrence numbers; n_distinct (nullable): phrases before padding.
+ * Needs vlgb_index_attach_rank. */
+int vlgb_index_frequent_phrases(const vlgb_index* idx, uint32_t length, uint32_t count, uint32_t charset, uint8_t* out,
+                                uint64_t* occ, uint32_t* n_distinct);
 /* Which path produces the occurrence lists of the calling thread's searches. */
 #define VLGB_PATH_AUTO 0   /* cost model: rank path when the index has one and the batch is small and rare */
 #define VLGB_PATH_SCAN 1

@@ -178,7 +178,7 @@ def test_shard_near_4gib_limit(V):
     from vlg_matching_b200 import capi
     n = 0xFFFFF000 - 4096
     buf = torch.full((n + 4096,), 0x61, dtype=torch.uint8, device="cuda:0")
-    plants = {n - 5: b"needle", n - 40000: b"needle", 3: b"needle", (1 << 31) + 7: b"needle", n - 65000: b"thread"}
+    plants = {n - 6: b"needle", n - 40000: b"needle", 3: b"needle", (1 << 31) + 7: b"needle", n - 65000: b"thread"}
     for pos, w in plants.items():
         buf[pos:pos + len(w)] = torch.tensor(list(w), dtype=torch.uint8, device="cuda:0")
     buf[n:] = 0
@@ -188,7 +188,7 @@ def test_shard_near_4gib_limit(V):
                    capi.WANT_TUPLES)
     assert r.starts(0).tolist() == sorted(p for p, w in plants.items() if w == b"needle")
     assert r.tuples(1).tolist() == [[n - 65000, n - 40000]]
-    assert r.tuples(2).tolist() == [[n - 40000, n - 5]]
+    assert r.tuples(2).tolist() == [[n - 40000, n - 6]]
     idx.free()
     del buf
     torch.cuda.empty_cache()

@@ -166,3 +166,26 @@ def test_cost_model_and_errors(V, tmp_path):
     sym = capi.Index.build_symbols(np.asarray([300, 5, 300, 7], dtype=np.uint64))
     with pytest.raises(capi.VlgbError):
         sym.attach_rank()
+
+
+@pytest.mark.parametrize("flags", [0, 1])
+def test_frequent_phrases_equal_reference_rule(V, flags):
+    """vlgb_index_frequent_phrases (device: runs of equal prefixes in the suffix array) against the numpy statement of
+    examples/generate-pattern.cpp (synth.frequent_phrases: same heap rule, same output order, same padding)."""
+    from vlg_matching_b200 import synth
+    for text, cases in ((synth.make_text(2, 1 << 20), [(200, 3), (200, 5), (200, 7), (17, 4)]),
+                        (synth.make_text(3, 1 << 18), [(200, 2), (200, 3), (50, 6)]),
+                        (np.frombuffer(b"ab ab ab, cd cd x_y x_y x_y x_y !!!!", dtype=np.uint8), [(5, 2), (40, 3), (3, 9)])):
+        idx = V.Index.build(text)
+        idx.attach_rank(flags)
+        for count, length in cases:
+            got, occ, nd = idx.frequent_phrases(count, length)
+            want = synth.frequent_phrases(text, count, length)
+            assert got == want, (count, length, got[:5], want[:5])
+            tb = text.tobytes()
+            for g, o in list(zip(got, occ))[:nd][-5:]:
+                c, i = 0, tb.find(g)
+                while i >= 0:
+                    c, i = c + 1, tb.find(g, i + 1)
+                assert c == int(o), (g, c, o)
+        idx.free()

@@ -13,7 +13,7 @@ import pytest
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 BIN = os.path.join(ROOT, "vlg_matching_b200", "bin")
-PROGS = ["vlg_matching.x", "gm_index-VLGB200.x", "gm_search-VLGB200.x", "create_collection.x"]
+PROGS = ["vlg_matching.x", "gm_index-VLGB200.x", "gm_search-VLGB200.x", "create_collection.x", "generate-pattern.x"]
 
 
 def run(args, **kw):
@@ -102,3 +102,31 @@ def test_gm_pipeline_matches_reference_checksum(tmp_path, batch):
     for k in ("total_time_mus", "median_time_mus", "prep_total_time_mus"):
         assert k in keys
     assert "Skipped" in r.stderr
+
+
+@pytest.mark.gpu
+def test_generate_pattern_and_grid_pipeline(tmp_path):
+    """The reference's pattern pipeline (benchmark/gapped-matching/Makefile:90-106): generate-pattern -> words file ->
+    `xargs -n k` lines joined by the gap -> gm_search.  Words equal the numpy statement of generate-pattern.cpp;
+    the k = 4 pattern file runs through gm_search -b 1 and its checksum equals the oracle's."""
+    from oracle import pyoracle as O
+    from vlg_matching_b200 import synth
+    text = synth.make_text(2, 2 << 20)
+    raw = tmp_path / "raw.txt"
+    text.tofile(raw)
+    r = run([os.path.join(BIN, "generate-pattern.x"), str(raw), "200", "3", "1"])
+    assert r.returncode == 0, r.stderr
+    words = r.stdout.split("\n")[:-1]
+    assert [w.encode() for w in words] == synth.frequent_phrases(text, 200, 3)
+    queries = synth.grid_queries([w.encode() for w in words], 4, (0, 100), 20)
+    col = tmp_path / "col"
+    assert run([os.path.join(BIN, "create_collection.x"), "-i", str(raw), "-c", str(col)]).returncode == 0
+    assert run([os.path.join(BIN, "gm_index-VLGB200.x"), "-c", str(col)]).returncode == 0
+    pat = col / "patterns" / "grid.txt"
+    pat.write_bytes(b"\n".join(synth.to_benchmark_syntax(q) for q in queries) + b"\n")
+    r = run([os.path.join(BIN, "gm_search-VLGB200.x"), "-c", str(col), "-p", str(pat), "-b", "1"])
+    assert r.returncode == 0, r.stderr
+    keys = dict(line[2:].split(" = ") for line in r.stdout.splitlines() if line.startswith("# ") and " = " in line)
+    ref = O.search(text, queries, want_tuples=False, threads=8)
+    assert int(keys["num_results"]) == sum(len(s) for _, s, _ in ref)
+    assert int(keys["checksum"]) == sum(int(s.sum()) for _, s, _ in ref)

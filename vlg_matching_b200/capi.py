@@ -34,7 +34,7 @@ SYMBOLS = [
     "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
     "vlgb_parse_batch", "vlgb_parse_lines", "vlgb_index_attach_rank", "vlgb_index_rank_info", "vlgb_index_sa_extract",
     "vlgb_set_path", "vlgb_result_device_starts", "vlgb_result_device_tuples", "vlgb_comm_unique_id", "vlgb_comm_init",
-    "vlgb_comm_destroy", "vlgb_search_sharded", "vlgb_chain_plan",
+    "vlgb_comm_destroy", "vlgb_search_sharded", "vlgb_chain_plan", "vlgb_index_frequent_phrases",
 ]
 
 
@@ -118,6 +118,7 @@ lib.vlgb_index_attach_rank.argtypes = [_P, C.c_uint32]
 lib.vlgb_index_rank_info.argtypes = [_P, C.POINTER(RankInfo)]
 lib.vlgb_index_sa_extract.argtypes = [_P, C.c_uint64, C.c_uint64, _P]
 lib.vlgb_set_path.argtypes = [C.c_int]
+lib.vlgb_index_frequent_phrases.argtypes = [_P, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, C.POINTER(C.c_uint32)]
 for _f in ("vlgb_result_device_starts", "vlgb_result_device_tuples"):
     getattr(lib, _f).argtypes = [_P, C.c_uint32]
     getattr(lib, _f).restype = C.c_void_p
@@ -443,6 +444,14 @@ class Index:
         r = RankInfo()
         check(lib.vlgb_index_rank_info(self.h, C.byref(r)))
         return {k: getattr(r, k) for k, _ in RankInfo._fields_}
+
+    def frequent_phrases(self, count: int, length: int, charset: int = 0):
+        """generate-pattern.cpp: -> (list of `count` phrases (bytes), occurrences uint64[count], distinct found)."""
+        out = np.zeros(max(count * length, 1), dtype=np.uint8)
+        occ = np.zeros(max(count, 1), dtype=np.uint64)
+        nd = C.c_uint32(0)
+        check(lib.vlgb_index_frequent_phrases(self.h, length, count, charset, out.ctypes.data, occ.ctypes.data, C.byref(nd)))
+        return [out[i * length:(i + 1) * length].tobytes() for i in range(count)], occ[:count], nd.value
 
     def sa_extract(self, first: int, count: int) -> np.ndarray:
         out = np.zeros(max(count, 1), dtype=np.uint64)

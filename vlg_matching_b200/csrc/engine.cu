@@ -9,6 +9,8 @@
 #include "common.cuh"
 #include "parse.hpp"
 #include "search.cuh"
+#include "phrases.cuh"
+#include <queue>
 
 using namespace vlgb;
 
@@ -546,6 +548,50 @@ extern "C" int vlgb_index_sa_extract(const vlgb_index* idx, uint64_t first, uint
         return VLGB_OK;
     } catch (const CudaError& e) {
         return cuda_fail(e);
+    }
+}
+
+// examples/generate-pattern.cpp:1-120 -- the `count` most frequent `length`-symbol phrases over a charset, in the order
+// the reference prints them (its min-heap popped: ascending (occurrences, phrase)), padded by repetition (:107-114).
+extern "C" int vlgb_index_frequent_phrases(const vlgb_index* idx, uint32_t length, uint32_t count, uint32_t charset, uint8_t* out,
+                                           uint64_t* occ, uint32_t* n_distinct)
+{
+    if (!idx || (!out && count && length)) return fail(VLGB_ERR_ARG, "vlgb_index_frequent_phrases: null argument");
+    if (!idx->rank) return fail(VLGB_ERR_ARG, "vlgb_index_frequent_phrases: the index has no rank structures (vlgb_index_attach_rank)");
+    if (length == 0 || charset > 2) return fail(VLGB_ERR_ARG, "vlgb_index_frequent_phrases: bad length / charset");
+    if (n_distinct) *n_distinct = 0;
+    if (!count) return VLGB_OK;
+    try {
+        ensure_ready();
+        PhraseRuns runs;
+        frequent_runs(ctx(), idx->rank->view, idx->d_text, length, charset, count, runs);
+        // the reference's heap rule, replayed in lexicographic order (generate-pattern.cpp:55-100): a phrase enters while
+        // the heap is not full, or when it occurs MORE often than the heap's minimum (which is then dropped)
+        typedef std::pair<uint32_t, std::string> entry;
+        std::priority_queue<entry, std::vector<entry>, std::greater<entry>> heap;
+        for (size_t r = 0; r < runs.occ.size(); r++) {
+            if (heap.size() == count && runs.occ[r] <= heap.top().first) continue;
+            heap.emplace(runs.occ[r], std::string(reinterpret_cast<const char*>(runs.grams.data()) + r * length, length));
+            if (heap.size() > count) heap.pop();
+        }
+        std::vector<entry> res;
+        while (!heap.empty() && res.size() < count) {
+            res.push_back(heap.top());
+            heap.pop();
+        }
+        if (n_distinct) *n_distinct = (uint32_t)res.size();
+        if (res.empty()) res.emplace_back(0u, std::string(length, 'x'));
+        const size_t si = res.size();
+        while (res.size() < count) res.push_back(res[res.size() % si]);
+        for (uint32_t i = 0; i < count; i++) {
+            memcpy(out + (size_t)i * length, res[i].second.data(), length);
+            if (occ) occ[i] = res[i].first;
+        }
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    } catch (const std::bad_alloc&) {
+        return fail(VLGB_ERR_NOMEM, "out of host memory");
     }
 }
 

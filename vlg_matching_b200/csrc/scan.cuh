@@ -7,7 +7,8 @@
 // Layout / algorithm
 //  * up to SCAN_S patterns per pass; patterns are keyed by (class, first min(len,8) bytes) where
 //    class = min(len, 8).  Class <= 7 keys are exact; class 8 entries (len >= 8) are verified byte by byte.
-//  * shared memory per CTA: open-addressing hash table of the pass (SoA, SCAN_H slots), the prefilter
+//  * shared memory per CTA: two-choice (cuckoo) hash table of the pass (SoA, two halves of SCAN_H / 2 slots, built on
+//    the host so that every key sits in one of its two home slots: a probe is two independent slot reads, no walk), the prefilter
 //    f3 (hashed first 3 bytes -> byte with bit c-1 set for every class c = 3..8 that has a pattern with that
 //    prefix) refined by f4 (hashed first 4 bytes, classes 4..8); f1/f2 bitmaps for 1- and 2-byte patterns;
 //    one work queue per warp.
@@ -51,7 +52,9 @@ constexpr int SCAN_RB = 64;        // rows per row-block in the count-matrix sca
 constexpr uint32_t SCAN_MAX_CHUNK = 65280;  // u16 per-row counters
 
 // Hash slot word: 0 = empty, else  1 << 31 | tag (17 bits) << 14 | (class - 1) << 11 | local pid (11 bits),
-// class = min(len, 8).  A probe reads ONE word per slot; the 8-byte key (by pid) is only compared on a tag hit.
+// class = min(len, 8).  Two-choice (cuckoo) placement: a key lives in slot[h & (H/2-1)] or in
+// slot[H/2 + (h2 & (H/2-1))]; a probe reads both words (independent loads) and compares the 8-byte key (by pid) only
+// on a tag hit.  Patterns of class 8 that share their first 8 bytes are chained through long_next (one table entry).
 constexpr uint32_t SCAN_PID_MASK = 0x7FFu;
 static_assert(SCAN_S <= 2048, "pid field of the slot word is 11 bits");
 
@@ -63,16 +66,25 @@ struct ScanTables {  // one pass; same layout on host, in global memory and in s
     uint8_t f4[SCAN_F4];
     uint32_t f2[SCAN_F2_WORDS];
     uint32_t f1[SCAN_F1_WORDS];
+    uint32_t seed;          // mixed into the hash; the host re-seeds when a cuckoo insertion does not settle
+    uint32_t pad[3];
 };
 
-// 32-bit mix of (key, class): low 13 bits = home slot, next 17 bits = tag
-__host__ __device__ inline uint32_t scan_mix(uint32_t klo, uint32_t khi, uint32_t c)
+// 32-bit mix of (key, class): low 12 bits = first home slot, bits 13..29 = tag
+__host__ __device__ inline uint32_t scan_mix(uint32_t klo, uint32_t khi, uint32_t c, uint32_t seed)
 {
-    uint32_t h = (klo * 0x9E3779B1u) ^ ((khi + c) * 0x85EBCA77u);
+    uint32_t h = (klo * 0x9E3779B1u) ^ ((khi + c + seed) * 0x85EBCA77u);
     h ^= h >> 15;
     h *= 0x2C1B3C6Du;
     h ^= h >> 13;
     return h;
+}
+// second home slot (upper half of the table), from bits the tag does not determine
+__host__ __device__ inline uint32_t scan_slot2(uint32_t h)
+{
+    uint32_t g = h * 0xC2B2AE35u;
+    g ^= g >> 16;
+    return (uint32_t)(SCAN_H / 2) + (g & (uint32_t)(SCAN_H / 2 - 1));
 }
 __host__ __device__ inline uint32_t scan_slot_word(uint32_t h, uint32_t c)  // pid field left 0
 {
@@ -95,6 +107,7 @@ struct ScanArgs {
     const ScanTables* tables;
     const uint32_t* long_len;  // [s_act] full length (class 8 only: len >= 8)
     const uint32_t* long_off;  // [s_act] offset into long_blob
+    const uint32_t* long_next; // [s_act] next pattern of class 8 with the same first 8 bytes (NONE32 = end of chain)
     const uint8_t* long_blob;
     uint32_t* matrix;        // [rows][s_stride]: counts (pass 1, zeroed by the host first) / write cursors inside
                              // each list (pass 2; the re-scan advances them)
@@ -140,23 +153,33 @@ __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTa
         klo = wlo & mlo;
         khi = whi & mhi;
     }
-    const uint32_t h = scan_mix(klo, khi, c);
-    const uint32_t want = scan_slot_word(h, c);
-    uint32_t slot = h & (SCAN_H - 1);
+    // ---- one probe: both home slots (independent loads), the key itself only on a tag hit
+    uint32_t cand = NONE32;
+    if (more) {
+        const uint32_t h = scan_mix(klo, khi, c, T->seed);
+        const uint32_t want = scan_slot_word(h, c);
+        const uint32_t s1 = T->slot[h & (uint32_t)(SCAN_H / 2 - 1)], s2 = T->slot[scan_slot2(h)];
+        if ((s1 & ~SCAN_PID_MASK) == want) {
+            const uint32_t k = s1 & SCAN_PID_MASK;
+            if (T->klo[k] == klo && T->khi[k] == khi) cand = k;
+        }
+        if (cand == NONE32 && (s2 & ~SCAN_PID_MASK) == want) {
+            const uint32_t k = s2 & SCAN_PID_MASK;
+            if (T->klo[k] == klo && T->khi[k] == khi) cand = k;
+        }
+        more = cand != NONE32;
+    }
     for (;;) {
         uint32_t pid = NONE32;
-        while (more) {
-            const uint32_t s = T->slot[slot];
-            slot = (slot + 1) & (SCAN_H - 1);
-            if (s == 0) { more = false; break; }
-            if ((s & ~SCAN_PID_MASK) != want) continue;
-            const uint32_t cand = s & SCAN_PID_MASK;
-            if (T->klo[cand] != klo || T->khi[cand] != khi) continue;
+        if (more) {
             bool ok;
             if (c < 8) {
                 ok = (uint64_t)p + c <= a.valid_len;
-                more = false;  // classes 1..7 have at most one entry per key
+                more = false;  // classes 1..7: the key is the pattern
             } else {
+                // class 8: the patterns that share these 8 bytes are chained; one candidate per emit, hit or miss --
+                // lanes holding the same key walk the same chain, so a pattern is emitted by all its lanes together
+                // and its list stays sorted
                 const uint32_t L = a.long_len[cand];
                 ok = (uint64_t)p + L <= a.valid_len;
                 if (ok) {
@@ -166,10 +189,11 @@ __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTa
                         if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
                 }
             }
-            // class 8: one candidate per emit, hit or miss -- lanes holding the same key walk the same
-            // slot sequence, so a pattern is emitted by all its lanes together and its list stays sorted
             if (ok) pid = cand;
-            break;
+            if (c >= 8) {
+                cand = a.long_next[cand];
+                more = cand != NONE32;
+            }
         }
         // ---- warp-wide emit (all 32 lanes take part)
         const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
@@ -350,6 +374,10 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 constexpr int SCAT_WARPS = 16;
 constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * (SCAN_S / 2) * sizeof(uint32_t);
 
+// PLAIN: the per-slice counters are touched by ONE warp only, so after __match_any_sync has grouped the lanes of a
+// round by pattern the group leader updates its 16-bit counter with a plain load/store (leaders of a round hold
+// distinct patterns) instead of shared-memory atomics (ATOMS: 2 cycles per lane on the LSU, B300_MICROARCH.md).
+template <bool PLAIN>
 __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -370,13 +398,26 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
         for (uint32_t w = 0; w < SCAT_WARPS; w++)
             for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) hist[w * (SCAN_S / 2) + i] = 0u;
         __syncthreads();
-        for (uint32_t i = i0 + lane; i < i1; i += 8 * 32) {  // 8 independent loads in flight per lane
+        uint16_t* cur16 = reinterpret_cast<uint16_t*>(cur);  // counter of pattern p = half p of the packed words
+        for (uint32_t ib = i0; ib < i1; ib += 8 * 32) {  // warp-uniform trip count; 8 independent loads in flight per lane
+            const uint32_t i = ib + lane;
             uint32_t e[8];
 #pragma unroll
             for (int u = 0; u < 8; u++) e[u] = i + u * 32 < i1 ? __ldg(st + i + u * 32) : NONE32;
+            if (!PLAIN) {
 #pragma unroll
-            for (int u = 0; u < 8; u++)
-                if (e[u] != NONE32) atomicAdd(&cur[e[u] >> 17], 1u << ((e[u] >> 12) & 16u));
+                for (int u = 0; u < 8; u++)
+                    if (e[u] != NONE32) atomicAdd(&cur[e[u] >> 17], 1u << ((e[u] >> 12) & 16u));
+            } else {
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    if (ib + u * 32 >= i1) break;  // uniform
+                    const uint32_t pid = e[u] == NONE32 ? NONE32 : e[u] >> 16;
+                    const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+                    if (pid != NONE32 && (int)lane == __ffs(grp) - 1) cur16[pid] = (uint16_t)(cur16[pid] + __popc(grp));
+                    __syncwarp();
+                }
+            }
         }
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
@@ -413,9 +454,15 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
                 const int leader = __ffs(grp) - 1;
                 uint32_t old = 0;
                 if (pid[u] != NONE32 && (int)lane == leader) {
-                    const uint32_t sh = (pid[u] & 1u) * 16;
-                    old = (atomicAdd(&cur[pid[u] >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+                    if (PLAIN) {
+                        old = cur16[pid[u]];
+                        cur16[pid[u]] = (uint16_t)(old + __popc(grp));
+                    } else {
+                        const uint32_t sh = (pid[u] & 1u) * 16;
+                        old = (atomicAdd(&cur[pid[u] >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+                    }
                 }
+                if (PLAIN) __syncwarp();
                 old = __shfl_sync(0xffffffffu, old, leader);
                 if (pid[u] != NONE32) a.out[dst[u] + old + __popc(grp & lt_mask)] = p[u];
             }
@@ -533,9 +580,36 @@ struct PatternDict {
     }
 };
 
+// Places entry `word` (tag | class | pid) of hash h into one of its two home slots, moving earlier entries to their
+// other home when both are taken (cuckoo).  `hs[pid]` = hash of every placed entry.  False if it does not settle.
+inline bool cuckoo_insert(ScanTables& t, std::vector<uint32_t>& hs, uint32_t word, uint32_t h)
+{
+    uint32_t cur_word = word, cur_h = h;
+    uint32_t slot = cur_h & (uint32_t)(SCAN_H / 2 - 1);
+    for (int kicks = 0; kicks < 512; kicks++) {
+        if (!t.slot[slot]) {
+            t.slot[slot] = cur_word;
+            return true;
+        }
+        const uint32_t other = slot < (uint32_t)(SCAN_H / 2) ? scan_slot2(cur_h) : (cur_h & (uint32_t)(SCAN_H / 2 - 1));
+        if (!t.slot[other]) {
+            t.slot[other] = cur_word;
+            return true;
+        }
+        // evict the resident of `slot`, put the current entry there, continue with the evicted one at ITS other home
+        const uint32_t ev = t.slot[slot];
+        t.slot[slot] = cur_word;
+        cur_word = ev;
+        cur_h = hs[ev & SCAN_PID_MASK];
+        const uint32_t home1 = cur_h & (uint32_t)(SCAN_H / 2 - 1);
+        slot = slot == home1 ? scan_slot2(cur_h) : home1;
+    }
+    return false;
+}
+
 struct PassHost {
     ScanTables tables;
-    std::vector<uint32_t> long_len, long_off;
+    std::vector<uint32_t> long_len, long_off, long_next;
     std::string long_blob;
     uint32_t first = 0, count = 0;  // patterns [first, first+count) of the dictionary
     bool has_short = false;
@@ -543,42 +617,65 @@ struct PassHost {
 
 inline void build_pass(const PatternDict& d, uint32_t first, uint32_t count, PassHost& ph)
 {
-    memset(&ph.tables, 0, sizeof ph.tables);
     ph.first = first;
     ph.count = count;
-    ph.long_len.assign(count, 0);
-    ph.long_off.assign(count, 0);
-    ph.long_blob.clear();
-    ph.has_short = false;
-    for (uint32_t i = 0; i < count; i++) {
-        const std::string& s = d.pats[first + i];
-        uint32_t len = (uint32_t)s.size();
-        uint32_t c = len < 8 ? len : 8;
-        uint64_t key = 0;
-        for (uint32_t j = 0; j < len && j < 8; j++) key |= (uint64_t)(uint8_t)s[j] << (8 * j);
-        uint32_t klo = (uint32_t)key, khi = (uint32_t)(key >> 32);
-        const uint32_t h = scan_mix(klo, khi, c);
-        uint32_t slot = h & (SCAN_H - 1);
-        while (ph.tables.slot[slot]) slot = (slot + 1) & (SCAN_H - 1);
-        ph.tables.slot[slot] = scan_slot_word(h, c) | i;
-        ph.tables.klo[i] = klo;
-        ph.tables.khi[i] = khi;
-        uint32_t w32 = klo;
-        if (c <= 2) ph.has_short = true;
-        if (c == 1) {
-            ph.tables.f1[(w32 & 0xFF) >> 5] |= 1u << (w32 & 31);
-        } else if (c == 2) {
-            uint32_t i2 = scan_h2(w32);
-            ph.tables.f2[i2 >> 5] |= 1u << (i2 & 31);
-        } else {
-            ph.tables.f3[scan_h3(w32)] |= (uint8_t)(1u << (c - 1));
-            if (c >= 4) ph.tables.f4[scan_h4(w32)] |= (uint8_t)(1u << (c - 1));
+    std::vector<uint32_t> hs(count, 0);
+    for (uint32_t seed = 0;; seed++) {
+        memset(&ph.tables, 0, sizeof ph.tables);
+        ph.tables.seed = seed * 0x9E3779B9u;
+        ph.long_len.assign(count, 0);
+        ph.long_off.assign(count, 0);
+        ph.long_next.assign(count, NONE32);
+        ph.long_blob.clear();
+        ph.has_short = false;
+        bool settled = true;
+        for (uint32_t i = 0; i < count && settled; i++) {
+            const std::string& s = d.pats[first + i];
+            uint32_t len = (uint32_t)s.size();
+            uint32_t c = len < 8 ? len : 8;
+            uint64_t key = 0;
+            for (uint32_t j = 0; j < len && j < 8; j++) key |= (uint64_t)(uint8_t)s[j] << (8 * j);
+            uint32_t klo = (uint32_t)key, khi = (uint32_t)(key >> 32);
+            const uint32_t h = scan_mix(klo, khi, c, ph.tables.seed);
+            hs[i] = h;
+            ph.tables.klo[i] = klo;
+            ph.tables.khi[i] = khi;
+            uint32_t w32 = klo;
+            if (c <= 2) ph.has_short = true;
+            if (c == 1) {
+                ph.tables.f1[(w32 & 0xFF) >> 5] |= 1u << (w32 & 31);
+            } else if (c == 2) {
+                uint32_t i2 = scan_h2(w32);
+                ph.tables.f2[i2 >> 5] |= 1u << (i2 & 31);
+            } else {
+                ph.tables.f3[scan_h3(w32)] |= (uint8_t)(1u << (c - 1));
+                if (c >= 4) ph.tables.f4[scan_h4(w32)] |= (uint8_t)(1u << (c - 1));
+            }
+            bool chained = false;
+            if (c == 8) {
+                ph.long_len[i] = len;
+                ph.long_off[i] = (uint32_t)ph.long_blob.size();
+                ph.long_blob += s;
+                // patterns with the same first 8 bytes share ONE table entry: append to the chain of the resident
+                const uint32_t want = scan_slot_word(h, c);
+                const uint32_t homes[2] = {h & (uint32_t)(SCAN_H / 2 - 1), scan_slot2(h)};
+                for (uint32_t hm : homes) {
+                    const uint32_t w = ph.tables.slot[hm];
+                    if (w && (w & ~SCAN_PID_MASK) == want) {
+                        uint32_t k = w & SCAN_PID_MASK;
+                        if (ph.tables.klo[k] == klo && ph.tables.khi[k] == khi) {
+                            while (ph.long_next[k] != NONE32) k = ph.long_next[k];
+                            ph.long_next[k] = i;
+                            chained = true;
+                            break;
+                        }
+                    }
+                }
+            }
+            if (!chained) settled = cuckoo_insert(ph.tables, hs, scan_slot_word(h, c) | i, h);
         }
-        if (c == 8) {
-            ph.long_len[i] = len;
-            ph.long_off[i] = (uint32_t)ph.long_blob.size();
-            ph.long_blob += s;
-        }
+        if (settled) return;
+        if (seed > 64) throw CudaError{cudaErrorUnknown, __FILE__, __LINE__};  // 2048 keys in 8192 slots: never
     }
 }
 

@@ -93,13 +93,14 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
         attr_set = true;
     }
 
     struct PassDev {
         uint32_t s_act, stride, has_short;
-        size_t o_tables, o_len, o_off, o_blob, o_base;  // inside the control blob
+        size_t o_tables, o_len, o_off, o_next, o_blob, o_base;  // inside the control blob
         uint32_t *matrix, *part, *total;
         uint32_t *stream = nullptr, *row_hits = nullptr, *overflow = nullptr;  // hit stream of pass 1 (if it fits)
     };
@@ -116,6 +117,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         pd[p].o_tables = ctl.put(&ph->tables, 1);
         pd[p].o_len = ctl.put(ph->long_len);
         pd[p].o_off = ctl.put(ph->long_off);
+        pd[p].o_next = ctl.put(ph->long_next);
         ph->long_blob.append(16, '\0');
         pd[p].o_blob = ctl.put(ph->long_blob.data(), ph->long_blob.size());
         std::vector<uint64_t> zero(cnt, 0);
@@ -187,6 +189,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.tables = dev_at<const ScanTables>(d_ctl, pd[p].o_tables);
         a.long_len = dev_at<const uint32_t>(d_ctl, pd[p].o_len);
         a.long_off = dev_at<const uint32_t>(d_ctl, pd[p].o_off);
+        a.long_next = dev_at<const uint32_t>(d_ctl, pd[p].o_next);
         a.long_blob = dev_at<const uint8_t>(d_ctl, pd[p].o_blob);
         a.matrix = pd[p].matrix;
         a.list_base = dev_at<const uint64_t>(d_ctl, pd[p].o_base);
@@ -251,7 +254,10 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         uint64_t bytes = 0;
         const bool streamed = pd[p].stream != nullptr;
         if (pocc && streamed) {  // scatter the recorded occurrences; only overflowed rows are scanned again
-            scan_scatter_kernel<<<std::min<uint32_t>(rows, 3u * (uint32_t)c.sm_count), SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
+            static const bool scatter_atomics = getenv("VLGB_SCATTER_ATOMICS") != nullptr;  // measurement hook: the ATOMS variant
+            const uint32_t sgrid = std::min<uint32_t>(rows, 3u * (uint32_t)c.sm_count);
+            if (scatter_atomics) scan_scatter_kernel<false><<<sgrid, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
+            else scan_scatter_kernel<true><<<sgrid, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
             launches++;
             bytes += pocc * 8;  // 4 B per occurrence read from the stream + 4 B written to its list
             c.stats.bytes[ST_SCAN_COUNT] += pocc * 4;
