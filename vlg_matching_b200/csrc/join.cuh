@@ -25,9 +25,8 @@
 // Algorithmic bytes per depth: 4 B per slot (x) + 4 B per right-list element read; per VIABLE slot 12 B staged,
 // 12 B read back (+ 4 B gather of the tuple end at depth > 1) and 12 B written.
 #pragma once
-#include <cuda_pipeline.h>
-
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace vlgb {
 
@@ -226,9 +225,15 @@ __device__ __forceinline__ uint32_t clamp_add32(uint32_t x, uint64_t bound)
 // tile_count[tile] records per tile to their final place.
 __global__ void __launch_bounds__(JF_THREADS, 4) join_probe_kernel(DepthDesc d)
 {
-    __shared__ uint32_t s_win[JF_WIN];
+    __shared__ __align__(128) uint32_t s_win_raw[JF_WIN + 8];  // + the elements before / after the window that alignment drags in
     __shared__ uint32_t s_wsum[32];
+    __shared__ __align__(8) uint64_t s_bar;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
     const uint32_t tile = blockIdx.x;
     const uint32_t slot0 = tile * JF_TILE;
     const uint32_t nslots = min((uint32_t)JF_TILE, d.total_slots - slot0);
@@ -251,11 +256,15 @@ __global__ void __launch_bounds__(JF_THREADS, 4) join_probe_kernel(DepthDesc d)
         wlen = j_end - j_first;
     }
     const bool use_win = single && wlen <= (uint32_t)JF_WIN;
-    if (use_win) {
-        // asynchronous global -> shared copies (LDGSTS): all of a thread's up to 16 requests are in flight at once
-        // instead of one load latency per loop trip; the left positions below are fetched while they land
-        for (uint32_t i = tid; i < wlen; i += JF_THREADS) __pipeline_memcpy_async(&s_win[i], R1 + j_first + i, 4);
-        __pipeline_commit();
+    // the window as ONE bulk asynchronous copy (TMA 1-D): source rounded out to 16-byte boundaries, `lead` elements
+    // of slack in front; one thread arms the barrier and issues it, the left positions below are fetched while the
+    // copy engine moves the window (was: up to 32 LDGSTS per thread)
+    const uint32_t lead = use_win ? (uint32_t)((reinterpret_cast<uintptr_t>(R1 + j_first) & 15u) >> 2) : 0u;
+    const uint32_t* s_win = s_win_raw + lead;
+    if (use_win && wlen && tid == 0) {
+        const uint32_t bytes = ((lead + wlen + 3u) & ~3u) * 4u;
+        mbar_expect_tx(&s_bar, bytes);
+        bulk_g2s(s_win_raw, R1 + j_first - lead, bytes, &s_bar);
     }
 
     // ---- probe
@@ -272,8 +281,7 @@ __global__ void __launch_bounds__(JF_THREADS, 4) join_probe_kernel(DepthDesc d)
             segs[i] = seg_lo;
         }
         if (use_win) {
-            __pipeline_wait_prior(0);
-            __syncthreads();  // CTA-uniform branch: the window is complete
+            if (wlen) mbar_wait(&s_bar, 0);  // CTA-uniform branch: the window has landed (visible to every waiting thread)
             // first slot: binary search; the others gallop on from their left neighbour's answer.  Dead slots of
             // the last tile carry x = 0 and are masked out of okbits at the end (no per-slot liveness branches)
             uint32_t at;

@@ -35,6 +35,7 @@
 #include <string>
 
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace vlgb {
 
@@ -123,7 +124,8 @@ struct ScanArgs {
     uint32_t only_overflow;  // FILL kernel: skip the rows the scatter kernel handles
 };
 
-constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t);
+static_assert(sizeof(ScanTables) % 16 == 0 && sizeof(ScanTables) < (1u << 20), "one bulk copy (mbarrier tx count < 2^20)");
+constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t) + 16;
 
 // One drain round: the first n (<= 32) queue entries starting at qhead, one per lane, all lanes converged.
 // Entry = (position - row start) | (class - 1) << 16: ONE probe, so a lane never idles while the warp visits a
@@ -225,18 +227,26 @@ __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTa
 template <bool FILL, bool SHORT>
 __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
+    extern __shared__ __align__(128) uint8_t smem_raw[];
     ScanTables* T = reinterpret_cast<ScanTables*>(smem_raw);
     uint32_t* queues = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t));
 
-    {  // stage the pass tables
-        const uint4* src = reinterpret_cast<const uint4*>(a.tables);
-        uint4* dst = reinterpret_cast<uint4*>(T);
-        for (uint32_t i = threadIdx.x; i < sizeof(ScanTables) / 16; i += blockDim.x) dst[i] = __ldg(src + i);
+    // stage the pass tables (144 KB): ONE bulk asynchronous copy issued by one thread, completion on an mbarrier --
+    // the copy engine moves the bytes while the warps set up (a per-thread load/store loop cost 9 trips of
+    // LDG.128 + STS.128 for every one of the 1024 threads)
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, (uint32_t)sizeof(ScanTables));
+        bulk_g2s(T, a.tables, (uint32_t)sizeof(ScanTables), bar);
     }
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* q = queues + warp * SCAN_QCAP;        // circular queue of (position - row start) | (class - 1) << 16
-    __syncthreads();
+    mbar_wait(bar, 0);
 
     const uint32_t row = blockIdx.x * SCAN_WARPS + warp;
     if (row >= a.rows) return;
@@ -374,13 +384,12 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 constexpr int SCAT_WARPS = 16;
 constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * (SCAN_S / 2) * sizeof(uint32_t);
 
-// PLAIN: the per-slice counters are touched by ONE warp only, so after __match_any_sync has grouped the lanes of a
-// round by pattern the group leader updates its 16-bit counter with a plain load/store (leaders of a round hold
-// distinct patterns) instead of shared-memory atomics (ATOMS: 2 cycles per lane on the LSU, B300_MICROARCH.md).
-template <bool PLAIN>
+// (Measured alternative that lost: group leaders updating warp-private 16-bit counters with plain loads/stores after
+// __match_any_sync instead of the shared-memory atomics -- 0.76 ms against 0.53 ms on BASELINE config 2: the extra
+// match per histogram round costs more than the ATOMS it saves.)
 __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
 {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
+    extern __shared__ __align__(128) uint8_t smem_raw[];
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);  // [SCAT_WARPS][SCAN_S / 2]
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* cur = hist + warp * (SCAN_S / 2);
@@ -398,26 +407,13 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
         for (uint32_t w = 0; w < SCAT_WARPS; w++)
             for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) hist[w * (SCAN_S / 2) + i] = 0u;
         __syncthreads();
-        uint16_t* cur16 = reinterpret_cast<uint16_t*>(cur);  // counter of pattern p = half p of the packed words
-        for (uint32_t ib = i0; ib < i1; ib += 8 * 32) {  // warp-uniform trip count; 8 independent loads in flight per lane
-            const uint32_t i = ib + lane;
+        for (uint32_t i = i0 + lane; i < i1; i += 8 * 32) {  // 8 independent loads in flight per lane
             uint32_t e[8];
 #pragma unroll
             for (int u = 0; u < 8; u++) e[u] = i + u * 32 < i1 ? __ldg(st + i + u * 32) : NONE32;
-            if (!PLAIN) {
 #pragma unroll
-                for (int u = 0; u < 8; u++)
-                    if (e[u] != NONE32) atomicAdd(&cur[e[u] >> 17], 1u << ((e[u] >> 12) & 16u));
-            } else {
-#pragma unroll
-                for (int u = 0; u < 8; u++) {
-                    if (ib + u * 32 >= i1) break;  // uniform
-                    const uint32_t pid = e[u] == NONE32 ? NONE32 : e[u] >> 16;
-                    const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-                    if (pid != NONE32 && (int)lane == __ffs(grp) - 1) cur16[pid] = (uint16_t)(cur16[pid] + __popc(grp));
-                    __syncwarp();
-                }
-            }
+            for (int u = 0; u < 8; u++)
+                if (e[u] != NONE32) atomicAdd(&cur[e[u] >> 17], 1u << ((e[u] >> 12) & 16u));
         }
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
@@ -454,15 +450,9 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
                 const int leader = __ffs(grp) - 1;
                 uint32_t old = 0;
                 if (pid[u] != NONE32 && (int)lane == leader) {
-                    if (PLAIN) {
-                        old = cur16[pid[u]];
-                        cur16[pid[u]] = (uint16_t)(old + __popc(grp));
-                    } else {
-                        const uint32_t sh = (pid[u] & 1u) * 16;
-                        old = (atomicAdd(&cur[pid[u] >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
-                    }
+                    const uint32_t sh = (pid[u] & 1u) * 16;
+                    old = (atomicAdd(&cur[pid[u] >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
                 }
-                if (PLAIN) __syncwarp();
                 old = __shfl_sync(0xffffffffu, old, leader);
                 if (pid[u] != NONE32) a.out[dst[u] + old + __popc(grp & lt_mask)] = p[u];
             }

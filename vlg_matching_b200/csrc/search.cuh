@@ -93,8 +93,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
-        VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
         attr_set = true;
     }
 
@@ -254,10 +253,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         uint64_t bytes = 0;
         const bool streamed = pd[p].stream != nullptr;
         if (pocc && streamed) {  // scatter the recorded occurrences; only overflowed rows are scanned again
-            static const bool scatter_atomics = getenv("VLGB_SCATTER_ATOMICS") != nullptr;  // measurement hook: the ATOMS variant
-            const uint32_t sgrid = std::min<uint32_t>(rows, 3u * (uint32_t)c.sm_count);
-            if (scatter_atomics) scan_scatter_kernel<false><<<sgrid, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
-            else scan_scatter_kernel<true><<<sgrid, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
+            scan_scatter_kernel<<<std::min<uint32_t>(rows, 3u * (uint32_t)c.sm_count), SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
             launches++;
             bytes += pocc * 8;  // 4 B per occurrence read from the stream + 4 B written to its list
             c.stats.bytes[ST_SCAN_COUNT] += pocc * 4;
