@@ -110,8 +110,10 @@ struct ScanArgs {
     const uint32_t* long_off;  // [s_act] offset into long_blob
     const uint32_t* long_next; // [s_act] next pattern of class 8 with the same first 8 bytes (NONE32 = end of chain)
     const uint8_t* long_blob;
-    uint32_t* matrix;        // [rows][s_stride]: counts (pass 1, zeroed by the host first) / write cursors inside
-                             // each list (pass 2; the re-scan advances them)
+    uint32_t* matrix;        // LEGACY passes only: [rows][s_stride] counts (zeroed by the host first) / write cursors
+                             // inside each list (the re-scan advances them)
+    uint32_t* gmatrix;       // [groups][s_stride], one row per GROUP of SCAN_GROUP_ROWS consecutive rows: occurrence
+                             // counts (stream pass out), then the group's write cursor inside each list
     const uint64_t* list_base;  // pass 2: [s_act] first word of every list inside `out`
     uint32_t* out;           // pass 2: positions (u32, shard-local)
     // hit stream: pass 1 records every occurrence of a row as (position - row start) | pid << 16, in the order
@@ -125,7 +127,15 @@ struct ScanArgs {
 };
 
 static_assert(sizeof(ScanTables) % 16 == 0 && sizeof(ScanTables) < (1u << 20), "one bulk copy (mbarrier tx count < 2^20)");
-constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t) + 16;
+constexpr int SCAN_GROUP_ROWS = 16;  // rows (= warps) that share one line of the count matrix: half a scan CTA
+constexpr int SCAN_CTA_GROUPS = SCAN_WARPS / SCAN_GROUP_ROWS;
+constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t) + 16 +
+                             (size_t)SCAN_CTA_GROUPS * SCAN_S * sizeof(uint32_t);
+static_assert(SCAN_SMEM <= 227 * 1024, "scan CTA: tables + queues + group counters must fit the 227 KB of an SM");
+// what a scan pass does with an occurrence
+constexpr int SCAN_STREAM = 0;  // default: count it in the group's shared-memory counters, append it to the row's hit stream
+constexpr int SCAN_COUNT = 1;   // legacy pass 1: count it in the per-row matrix (global reduction), no stream
+constexpr int SCAN_FILL = 2;    // legacy pass 2: write it at the row's cursor
 
 // One drain round: the first n (<= 32) queue entries starting at qhead, one per lane, all lanes converged.
 // Entry = (position - row start) | (class - 1) << 16: ONE probe, so a lane never idles while the warp visits a
@@ -134,7 +144,7 @@ constexpr size_t SCAN_SMEM = sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP
 // 4-byte slot word per probe; the key itself is compared only on a tag hit).  Hits are ranked among equal
 // patterns in lane order = (position, class) order.  A pattern belongs to exactly one class and the queue is
 // FIFO per class, so every list receives its positions in ascending order.
-template <bool FILL>
+template <int MODE>
 __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, const uint32_t* q,
                                                  uint32_t qhead, uint32_t n, uint32_t row_lo, uint32_t* mrow,
                                                  uint32_t lane, uint32_t lt_mask, uint32_t* stream_row, uint32_t& nh)
@@ -200,15 +210,17 @@ __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTa
         // ---- warp-wide emit (all 32 lanes take part)
         const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
         if (hits) {
-            if (!FILL) {
-                // pass 1: bump the (row, pattern) count in the matrix (fire-and-forget L2 reduction) and append
-                // the hit to the row's stream at its place in lane = (position, class) order
+            if (MODE == SCAN_STREAM) {
+                // bump the (group, pattern) count -- a shared-memory atomic: ~1 cycle of the SM's load/store pipe per
+                // warp instruction, where the global reduction of the legacy pass costs ~1.2 cycles per LANE
+                // (tools/microbench, profiles/) -- and append the hit to the row's stream at its place in
+                // lane = (position, class) order
                 if (pid != NONE32) atomicAdd(mrow + pid, 1u);
-                if (stream_row) {
-                    const uint32_t at = nh + __popc(hits & lt_mask);
-                    if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
-                    nh += __popc(hits);
-                }
+                const uint32_t at = nh + __popc(hits & lt_mask);
+                if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
+                nh += __popc(hits);
+            } else if (MODE == SCAN_COUNT) {
+                if (pid != NONE32) atomicAdd(mrow + pid, 1u);  // fire-and-forget L2 reduction
             } else {
                 // pass 2 (rows without a usable stream): the matrix entry is the row's write cursor inside the
                 // list; rank among equal patterns of the round = lane order = position order
@@ -224,13 +236,14 @@ __device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTa
     }
 }
 
-template <bool FILL, bool SHORT>
+template <int MODE, bool SHORT>
 __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     ScanTables* T = reinterpret_cast<ScanTables*>(smem_raw);
     uint32_t* queues = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables));
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t));
+    uint32_t* gcnt = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t) + 16);
 
     // stage the pass tables (144 KB): ONE bulk asynchronous copy issued by one thread, completion on an mbarrier --
     // the copy engine moves the bytes while the warps set up (a per-thread load/store loop cost 9 trips of
@@ -239,6 +252,8 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         mbar_init(bar, 1);
         mbar_fence_init();
     }
+    if (MODE == SCAN_STREAM)
+        for (uint32_t i = threadIdx.x; i < (uint32_t)SCAN_CTA_GROUPS * SCAN_S; i += SCAN_WARPS * 32) gcnt[i] = 0u;
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_expect_tx(bar, (uint32_t)sizeof(ScanTables));
@@ -249,16 +264,18 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     mbar_wait(bar, 0);
 
     const uint32_t row = blockIdx.x * SCAN_WARPS + warp;
-    if (row >= a.rows) return;
-    uint32_t* mrow = a.matrix + (size_t)row * a.s_stride;
+    bool live = row < a.rows;
+    if (MODE == SCAN_FILL && live && a.only_overflow && a.row_hits[row] <= a.stream_cap) live = false;  // scattered from the stream instead
+    if (MODE != SCAN_STREAM && !live) return;  // the stream pass meets again at the barrier before the counter flush
+    // where an occurrence is counted: the group's shared-memory counters (stream pass) / the row's line of the matrix
+    uint32_t* mrow = MODE == SCAN_STREAM ? gcnt + (warp / SCAN_GROUP_ROWS) * SCAN_S : a.matrix + (size_t)row * a.s_stride;
 
-    const uint32_t lo = row * a.chunk;
-    const uint32_t hi = (uint32_t)min((uint64_t)lo + a.chunk, (uint64_t)a.valid_len);  // 64-bit: lo + chunk may pass 2^32 in the last row
+    const uint32_t lo = live ? row * a.chunk : 0u;
+    const uint32_t hi = live ? (uint32_t)min((uint64_t)lo + a.chunk, (uint64_t)a.valid_len) : 0u;  // 64-bit: lo + chunk may pass 2^32 in the last row
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint32_t qhead = 0, qcount = 0;  // warp-uniform
-    uint32_t nh = 0;                 // occurrences recorded in the row's hit stream (pass 1)
-    uint32_t* stream_row = (!FILL && a.stream) ? a.stream + (size_t)row * a.stream_cap : nullptr;
-    if (FILL && a.only_overflow && a.row_hits[row] <= a.stream_cap) return;  // scattered from the stream instead
+    uint32_t nh = 0;                 // occurrences recorded in the row's hit stream (stream pass)
+    uint32_t* stream_row = (MODE == SCAN_STREAM && live) ? a.stream + (size_t)row * a.stream_cap : nullptr;
 
     for (uint32_t base = lo; base < hi; base += SCAN_STEP) {
         // ---- 16 bytes per lane: own 8 + the next lane's 8
@@ -329,7 +346,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             qcount += total;
             __syncwarp();
             while (qcount >= 32) {  // drain full rounds; fewer than 32 leftovers wait for the next step
-                scan_drain_round<FILL>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
+                scan_drain_round<MODE>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
                 qhead = (qhead + 32) & (SCAN_QCAP - 1);
                 qcount -= 32;
             }
@@ -354,7 +371,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
                 qcount += __shfl_sync(0xffffffffu, inc2, 31);
                 __syncwarp();
                 while (qcount >= 32) {
-                    scan_drain_round<FILL>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
+                    scan_drain_round<MODE>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
                     qhead = (qhead + 32) & (SCAN_QCAP - 1);
                     qcount -= 32;
                 }
@@ -362,99 +379,125 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             }
         }
     }
-    if (qcount) scan_drain_round<FILL>(a, T, q, qhead, qcount, lo, mrow, lane, lt_mask, stream_row, nh);
-    if (!FILL) {
-        if (stream_row && lane == 0) {
+    if (qcount) scan_drain_round<MODE>(a, T, q, qhead, qcount, lo, mrow, lane, lt_mask, stream_row, nh);
+    if (MODE == SCAN_STREAM) {
+        if (live && lane == 0) {
             a.row_hits[row] = nh;
             if (nh > a.stream_cap) atomicAdd(a.overflow, 1u);
+        }
+        // the CTA's groups publish their counts: one line of the group matrix each, plain coalesced stores
+        __syncthreads();
+        for (uint32_t g = 0; g < (uint32_t)SCAN_CTA_GROUPS; g++) {
+            const uint32_t grp = blockIdx.x * SCAN_CTA_GROUPS + g;
+            if (grp * SCAN_GROUP_ROWS >= a.rows) break;
+            for (uint32_t i = threadIdx.x; i < a.s_stride; i += SCAN_WARPS * 32) a.gmatrix[(size_t)grp * a.s_stride + i] = gcnt[g * SCAN_S + i];
         }
     }
 }
 
-// Pass 2 for the rows whose occurrences fit the hit stream: no text, no tables -- every position of the row's
-// stream goes to  list_base[pid] + row cursor[pid] + (hits of pid earlier in the row).
-// A whole CTA works on ONE row at a time and CTAs take consecutive rows, so all writes into a 32-byte sector of
-// a list (the segments of neighbouring rows) happen within microseconds of each other and merge in L2.  (One
-// warp per row, 4736 rows in flight for the whole kernel, left every sector partially written for ~1 ms:
-// 4x the algorithmic DRAM traffic -- profiles/r01b.)  The row's stream is cut into one slice per warp:
-//   1. every warp histograms its slice by pattern (u16 counters, two per word),
-//   2. the counters become exclusive prefixes over the slices (packed adds, one word = two patterns),
-//   3. every warp scatters its slice: rank among equal patterns of a round in lane order (= the order pass 1
-//      found them = ascending position) on top of the running counter.
+// Pass 2 of the stream path: no text, no tables -- every recorded occurrence goes to
+//     list_base[pid] + group cursor[pid] + (occurrences of pid earlier in the group).
+// One CTA per GROUP of SCAN_GROUP_ROWS consecutive rows, rows taken in order, so the cursors of all patterns stay in
+// shared memory (base[]) for the whole group and every list receives the group's positions as one ascending run:
+// all writes into a 32-byte sector happen within microseconds of each other and merge in L2.  (One warp per row with
+// 4736 rows in flight left every sector partially written for ~1 ms: 4x the algorithmic DRAM traffic, profiles/r01b.)
+//
+// A row's stream is taken in blocks of SCAT_WARPS x 32 x SCAT_ROUNDS hits, one slice of whole rounds per warp:
+//   1. histogram: every warp counts its slice per pattern in its PRIVATE 16-bit counters (shared-memory atomics
+//      without return value; measured ~1 cycle of the load/store pipe per warp instruction, tools/microbench),
+//   2. the counters become exclusive prefixes over the slices; base[pid] advances by the block total,
+//   3. scatter: rank among equal patterns = atomic fetch-add on the private counter.  The hardware serialises the
+//      lanes of one instruction that hit the same counter, but in an order the ISA does not define, and positions
+//      must land in lane (= text) order.  So after the fetch-add every lane re-reads its counter: a lane whose counter
+//      moved by more than its own increment shares the pattern with other lanes of the round.  Those lanes raise a
+//      marker bit in the counter (that also tells the one lane of the group that saw a difference of exactly 1),
+//      and only they run MATCH.ANY to rank themselves in lane order -- MATCH costs ~2 cycles per DISTINCT value among
+//      the participating lanes, so it is kept to the few repeated (frequent) patterns of a round.
 constexpr int SCAT_WARPS = 16;
-constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * (SCAN_S / 2) * sizeof(uint32_t);
+constexpr int SCAT_ROUNDS = 16;
+constexpr int SCAT_BLOCK = SCAT_WARPS * 32 * SCAT_ROUNDS;  // hits per block: every counter stays below 2^15 (marker bit)
+constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * SCAN_S * sizeof(uint16_t) + (size_t)SCAN_S * sizeof(uint64_t);
+static_assert(SCAT_BLOCK < (1 << 15), "counter halves carry a marker in bit 15");
 
-// (Measured alternative that lost: group leaders updating warp-private 16-bit counters with plain loads/stores after
-// __match_any_sync instead of the shared-memory atomics -- 0.76 ms against 0.53 ms on BASELINE config 2: the extra
-// match per histogram round costs more than the ATOMS it saves.)
 __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw);  // [SCAT_WARPS][SCAN_S / 2]
+    uint64_t* base = reinterpret_cast<uint64_t*>(smem_raw);  // [SCAN_S] next free word of pid's list for this group
+    uint32_t* cnt32 = reinterpret_cast<uint32_t*>(smem_raw + (size_t)SCAN_S * sizeof(uint64_t));  // [SCAT_WARPS][SCAN_S / 2], two patterns per word
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* cur = hist + warp * (SCAN_S / 2);
+    uint32_t* cur = cnt32 + warp * (SCAN_S / 2);
+    const volatile uint32_t* vcur = cur;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t words = (a.s_act + 1) >> 1;  // counter words in use
-    for (uint32_t row = blockIdx.x; row < a.rows; row += gridDim.x) {
+    const uint32_t grp = blockIdx.x;
+    const uint32_t* gm = a.gmatrix + (size_t)grp * a.s_stride;
+    for (uint32_t i = threadIdx.x; i < a.s_act; i += SCAT_WARPS * 32) base[i] = __ldg(a.list_base + i) + __ldg(gm + i);
+    for (uint32_t i = threadIdx.x; i < (uint32_t)SCAT_WARPS * (SCAN_S / 2); i += SCAT_WARPS * 32) cnt32[i] = 0u;
+    const uint32_t row_end = min(a.rows, (grp + 1) * (uint32_t)SCAN_GROUP_ROWS);
+    for (uint32_t row = grp * SCAN_GROUP_ROWS; row < row_end; row++) {
         const uint32_t nh = a.row_hits[row];
-        if (nh == 0 || nh > a.stream_cap) continue;  // uniform: nothing to do / re-scanned by the FILL kernel
         const uint32_t* st = a.stream + (size_t)row * a.stream_cap;
-        const uint32_t* mrow = a.matrix + (size_t)row * a.s_stride;
         const uint32_t lo = row * a.chunk;
-        const uint32_t per = ((nh + SCAT_WARPS - 1) / SCAT_WARPS + 31) & ~31u;
-        const uint32_t i0 = min(nh, warp * per), i1 = min(nh, i0 + per);
-        __syncthreads();  // the previous row's counters are no longer in use
-        for (uint32_t w = 0; w < SCAT_WARPS; w++)
-            for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) hist[w * (SCAN_S / 2) + i] = 0u;
-        __syncthreads();
-        for (uint32_t i = i0 + lane; i < i1; i += 8 * 32) {  // 8 independent loads in flight per lane
-            uint32_t e[8];
+        for (uint32_t b0 = 0; b0 < nh; b0 += SCAT_BLOCK) {
+            const uint32_t nb = min((uint32_t)SCAT_BLOCK, nh - b0);
+            const uint32_t per = ((nb + SCAT_WARPS - 1) / SCAT_WARPS + 31) & ~31u;  // hits per slice, whole rounds
+            const uint32_t i0 = b0 + min(nb, warp * per), i1 = b0 + min(nb, (warp + 1) * per);
+            uint32_t e[SCAT_ROUNDS];
 #pragma unroll
-            for (int u = 0; u < 8; u++) e[u] = i + u * 32 < i1 ? __ldg(st + i + u * 32) : NONE32;
+            for (int r = 0; r < SCAT_ROUNDS; r++) e[r] = i0 + r * 32 + lane < i1 ? __ldg(st + i0 + r * 32 + lane) : NONE32;
+            __syncthreads();  // the previous block is scattered (first block: base[] and the counters are set up)
+            // the last slice's counters now hold the previous block's totals: the group cursors advance; then all
+            // slices start from zero (one thread per counter word, the same thread for all slices)
+            for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
+                const uint32_t t = cnt32[(SCAT_WARPS - 1) * (SCAN_S / 2) + i];
+                base[2 * i] += t & 0x7FFFu;
+                base[2 * i + 1] += (t >> 16) & 0x7FFFu;
 #pragma unroll
-            for (int u = 0; u < 8; u++)
-                if (e[u] != NONE32) atomicAdd(&cur[e[u] >> 17], 1u << ((e[u] >> 12) & 16u));
-        }
-        __syncthreads();
-        for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
-            uint32_t run = 0;  // both halves stay below 65536: a pattern occurs at most once per position of the row
-#pragma unroll
-            for (uint32_t w = 0; w < SCAT_WARPS; w++) {
-                const uint32_t v = hist[w * (SCAN_S / 2) + i];
-                hist[w * (SCAN_S / 2) + i] = run;
-                run += v;
+                for (int w = 0; w < SCAT_WARPS; w++) cnt32[w * (SCAN_S / 2) + i] = 0u;
             }
-        }
-        __syncthreads();
-        for (uint32_t i = i0; i < i1; i += 4 * 32) {  // 4 rounds per trip: their loads and gathers overlap
-            uint32_t pid[4], p[4];
-            uint64_t dst[4];
+            __syncthreads();
+            // ---- 1. histogram of the slice
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                pid[u] = NONE32;
-                p[u] = 0;
-                dst[u] = 0;
-                if (i + u * 32 + lane < i1) {
-                    const uint32_t e = __ldg(st + i + u * 32 + lane);
-                    pid[u] = e >> 16;
-                    p[u] = lo + (e & 0xFFFFu);
+            for (int r = 0; r < SCAT_ROUNDS; r++)
+                if (e[r] != NONE32) atomicAdd(&cur[e[r] >> 17], 1u << ((e[r] >> 12) & 16u));
+            __syncthreads();
+            // ---- 2. exclusive prefix over the slices
+            for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
+                uint32_t run = 0;
+#pragma unroll
+                for (int w = 0; w < SCAT_WARPS; w++) {
+                    const uint32_t v = cnt32[w * (SCAN_S / 2) + i];
+                    cnt32[w * (SCAN_S / 2) + i] = run;
+                    run += v;
                 }
             }
+            __syncthreads();
+            // ---- 3. scatter: rank = fetch-add on the slice's counter, put into lane order where lanes share a pattern
 #pragma unroll
-            for (int u = 0; u < 4; u++)
-                if (pid[u] != NONE32) dst[u] = __ldg(a.list_base + pid[u]) + __ldg(mrow + pid[u]);
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                if (i + u * 32 >= i1) break;  // uniform
-                const uint32_t grp = __match_any_sync(0xffffffffu, pid[u]);
-                const int leader = __ffs(grp) - 1;
-                uint32_t old = 0;
-                if (pid[u] != NONE32 && (int)lane == leader) {
-                    const uint32_t sh = (pid[u] & 1u) * 16;
-                    old = (atomicAdd(&cur[pid[u] >> 1], (uint32_t)__popc(grp) << sh) >> sh) & 0xFFFFu;
+            for (int r = 0; r < SCAT_ROUNDS; r++) {
+                if (i0 + r * 32 >= i1) break;  // uniform
+                const bool valid = e[r] != NONE32;
+                const uint32_t pid = e[r] >> 16, w = (e[r] >> 17) & (SCAN_S / 2 - 1), sh = (e[r] >> 12) & 16u;
+                uint32_t rk = 0, now = 0;
+                if (valid) rk = (atomicAdd(&cur[w], 1u << sh) >> sh) & 0x7FFFu;
+                __syncwarp();
+                if (valid) now = (vcur[w] >> sh) & 0x7FFFu;
+                bool dup = valid && now - rk > 1u;
+                if (__any_sync(0xffffffffu, dup)) {
+                    if (dup) atomicOr(&cur[w], 0x8000u << sh);
+                    __syncwarp();
+                    const bool last = valid && !dup && ((vcur[w] >> sh) & 0x8000u);
+                    __syncwarp();
+                    if (dup) atomicAnd(&cur[w], ~(0x8000u << sh));
+                    dup |= last;
+                    const uint32_t m = __ballot_sync(0xffffffffu, dup);
+                    if (dup) {
+                        const uint32_t g = __match_any_sync(m, pid);
+                        rk = now - __popc(g) + __popc(g & lt_mask);
+                    }
+                    __syncwarp();
                 }
-                old = __shfl_sync(0xffffffffu, old, leader);
-                if (pid[u] != NONE32) a.out[dst[u] + old + __popc(grp & lt_mask)] = p[u];
+                if (valid) a.out[base[pid] + rk] = lo + (e[r] & 0xFFFFu);
             }
         }
     }

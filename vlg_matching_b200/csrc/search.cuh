@@ -86,13 +86,16 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     const uint32_t chunk = scan_chunk_for(n, c.sm_count);
     const uint32_t rows = (uint32_t)((n + chunk - 1) / chunk);
     const uint32_t nrb = (rows + SCAN_RB - 1) / SCAN_RB;
+    const uint32_t ngroups = (rows + SCAN_GROUP_ROWS - 1) / SCAN_GROUP_ROWS;
     const size_t smem = SCAN_SMEM;
     static thread_local bool attr_set = false;
     if (!attr_set) {
-        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<SCAN_STREAM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<SCAN_STREAM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<SCAN_COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<SCAN_COUNT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<SCAN_FILL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VLGB_CUDA(cudaFuncSetAttribute(scan_kernel<SCAN_FILL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VLGB_CUDA(cudaFuncSetAttribute(scan_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAT_SMEM));
         attr_set = true;
     }
@@ -100,8 +103,9 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     struct PassDev {
         uint32_t s_act, stride, has_short;
         size_t o_tables, o_len, o_off, o_next, o_blob, o_base;  // inside the control blob
-        uint32_t *matrix, *part, *total;
-        uint32_t *stream = nullptr, *row_hits = nullptr, *overflow = nullptr;  // hit stream of pass 1 (if it fits)
+        uint32_t *gmatrix, *total;                 // stream path: [groups][stride] counts -> group cursors
+        uint32_t *matrix = nullptr, *part = nullptr;  // legacy path: [rows][stride] counts -> row cursors, row-block sums
+        uint32_t *stream = nullptr, *row_hits = nullptr, *overflow = nullptr;  // hit stream (if the budget allows one)
     };
     std::vector<PassDev> pd(npass);
     Packer ctl;
@@ -121,13 +125,12 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         pd[p].o_blob = ctl.put(ph->long_blob.data(), ph->long_blob.size());
         std::vector<uint64_t> zero(cnt, 0);
         pd[p].o_base = ctl.put(zero);
-        work_bytes += Arena::padded((size_t)rows * pd[p].stride, 4) + Arena::padded((size_t)nrb * pd[p].stride, 4) +
-                      Arena::padded(pd[p].stride, 4);
+        work_bytes += Arena::padded((size_t)ngroups * pd[p].stride, 4) + Arena::padded(pd[p].stride, 4);
     }
     const size_t o_allbase = ctl.put(so.base);  // P+1 u64, filled later (owned kernel)
     work_bytes += 2 * Arena::padded(P, 4);      // owned[], totals[]
     // hit streams: stream_cap entries per row (2 per text position, else 1), for as many passes as the budget
-    // (a third of the free device memory, at most 24 GiB) allows; the other passes re-scan in pass 2
+    // (a third of the free device memory, at most 24 GiB) allows; the other passes take the legacy two-scan path
     uint32_t stream_cap = 0, stream_passes = 0;
     {
         // free device memory is asked for once per thread and whenever the arena has to grow: cudaMemGetInfo costs
@@ -152,14 +155,17 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         }
         work_bytes += stream_passes * (Arena::padded((size_t)rows * stream_cap, 4) + Arena::padded(rows, 4)) + Arena::padded(npass, 4);
     }
+    // legacy state: one per pass without a stream, plus ONE spare shared by the passes whose stream overflows
+    // (they are redone one after the other)
+    const size_t legacy_bytes = Arena::padded((size_t)rows * SCAN_S, 4) + Arena::padded((size_t)nrb * SCAN_S, 4);
+    work_bytes += (size_t)(npass - stream_passes + 1) * legacy_bytes;
     trace().mark("scan: tables built");
     c.scan_arena.reserve(ctl.size() + work_bytes + 4096);
     uint8_t* d_ctl = c.scan_arena.take<uint8_t>(ctl.size());
     h2d(c, d_ctl, ctl.host.data(), ctl.host.size());
     c.stats.h2d_bytes += ctl.host.size();
     for (uint32_t p = 0; p < npass; p++) {
-        pd[p].matrix = c.scan_arena.take<uint32_t>((size_t)rows * pd[p].stride);
-        pd[p].part = c.scan_arena.take<uint32_t>((size_t)nrb * pd[p].stride);
+        pd[p].gmatrix = c.scan_arena.take<uint32_t>((size_t)ngroups * pd[p].stride);
         pd[p].total = c.scan_arena.take<uint32_t>(pd[p].stride);
     }
     uint32_t* d_owned = c.scan_arena.take<uint32_t>(P);
@@ -170,6 +176,12 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         pd[p].row_hits = c.scan_arena.take<uint32_t>(rows);
         pd[p].overflow = d_overflow + p;
     }
+    for (uint32_t p = stream_passes; p < npass; p++) {
+        pd[p].matrix = c.scan_arena.take<uint32_t>((size_t)rows * SCAN_S);
+        pd[p].part = c.scan_arena.take<uint32_t>((size_t)nrb * SCAN_S);
+    }
+    uint32_t* spare_matrix = c.scan_arena.take<uint32_t>((size_t)rows * SCAN_S);
+    uint32_t* spare_part = c.scan_arena.take<uint32_t>((size_t)nrb * SCAN_S);
     std::vector<uint32_t> overflow(npass, 0);
 
     auto args_for = [&](uint32_t p) {
@@ -191,6 +203,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.long_next = dev_at<const uint32_t>(d_ctl, pd[p].o_next);
         a.long_blob = dev_at<const uint8_t>(d_ctl, pd[p].o_blob);
         a.matrix = pd[p].matrix;
+        a.gmatrix = pd[p].gmatrix;
         a.list_base = dev_at<const uint64_t>(d_ctl, pd[p].o_base);
         a.out = nullptr;
         a.stream = pd[p].stream;
@@ -201,21 +214,38 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         return a;
     };
     const uint32_t grid = (rows + SCAN_WARPS - 1) / SCAN_WARPS;
-
-    // pass 1: counts, then per-row write cursors
-    for (uint32_t p = 0; p < npass; p++) {
+    // legacy pass 1 of pass p into (matrix, part): per-row counts by global reductions, then per-row write cursors
+    auto legacy_count = [&](uint32_t p, uint32_t* matrix, uint32_t* part, uint32_t* total) {
         ScanArgs a = args_for(p);
+        a.matrix = matrix;
         c.begin(ST_SCAN_COUNT);
-        VLGB_CUDA(cudaMemsetAsync(pd[p].matrix, 0, (size_t)rows * pd[p].stride * 4, c.stream));
-        if (a.has_short) scan_kernel<false, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-        else scan_kernel<false, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-        c.end(ST_SCAN_COUNT, 1, n);  // n read + 4 B per occurrence (added below once the counts are known)
+        VLGB_CUDA(cudaMemsetAsync(matrix, 0, (size_t)rows * pd[p].stride * 4, c.stream));
+        if (a.has_short) scan_kernel<SCAN_COUNT, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        else scan_kernel<SCAN_COUNT, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        c.end(ST_SCAN_COUNT, 1, n);
         c.begin(ST_SCAN_OFFSETS);
         dim3 g((pd[p].stride + 127) / 128, nrb);
-        scan_colsum_kernel<<<g, 128, 0, c.stream>>>(pd[p].matrix, rows, pd[p].stride, pd[p].part);
-        scan_colbase_kernel<<<(pd[p].stride + 127) / 128, 128, 0, c.stream>>>(pd[p].part, nrb, pd[p].stride, pd[p].total);
-        scan_rowoff_kernel<<<g, 128, 0, c.stream>>>(pd[p].matrix, rows, pd[p].stride, pd[p].part);
+        scan_colsum_kernel<<<g, 128, 0, c.stream>>>(matrix, rows, pd[p].stride, part);
+        scan_colbase_kernel<<<(pd[p].stride + 127) / 128, 128, 0, c.stream>>>(part, nrb, pd[p].stride, total);
+        scan_rowoff_kernel<<<g, 128, 0, c.stream>>>(matrix, rows, pd[p].stride, part);
         c.end(ST_SCAN_OFFSETS, 3, (uint64_t)rows * pd[p].stride * 12);
+    };
+
+    // pass 1: occurrences counted (and recorded in the hit streams), then the write cursors
+    for (uint32_t p = 0; p < npass; p++) {
+        if (pd[p].stream) {
+            ScanArgs a = args_for(p);
+            c.begin(ST_SCAN_COUNT);
+            if (a.has_short) scan_kernel<SCAN_STREAM, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+            else scan_kernel<SCAN_STREAM, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+            c.end(ST_SCAN_COUNT, 1, n);  // n read + 4 B per occurrence (added below once the counts are known)
+            c.begin(ST_SCAN_OFFSETS);
+            // group counts -> exclusive prefix over the groups (in place) = every group's cursor; totals = list lengths
+            scan_colbase_kernel<<<(pd[p].stride + 127) / 128, 128, 0, c.stream>>>(pd[p].gmatrix, ngroups, pd[p].stride, pd[p].total);
+            c.end(ST_SCAN_OFFSETS, 1, (uint64_t)ngroups * pd[p].stride * 8);
+        } else {
+            legacy_count(p, pd[p].matrix, pd[p].part, pd[p].total);
+        }
         d2h(c, so.tot.data() + p * SCAN_S, pd[p].total, pd[p].s_act * 4);
         c.stats.d2h_bytes += pd[p].s_act * 4;
     }
@@ -246,26 +276,26 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     for (uint32_t p = 0; p < npass; p++) {
         uint64_t pocc = 0;
         for (uint32_t i = 0; i < pd[p].s_act; i++) pocc += so.tot[p * SCAN_S + i];
+        if (!pocc) continue;
         ScanArgs a = args_for(p);
         a.out = so.d_lists;
-        c.begin(ST_SCAN_FILL);
-        uint32_t launches = 0;
-        uint64_t bytes = 0;
-        const bool streamed = pd[p].stream != nullptr;
-        if (pocc && streamed) {  // scatter the recorded occurrences; only overflowed rows are scanned again
-            scan_scatter_kernel<<<std::min<uint32_t>(rows, 3u * (uint32_t)c.sm_count), SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
-            launches++;
-            bytes += pocc * 8;  // 4 B per occurrence read from the stream + 4 B written to its list
+        if (pd[p].stream && !overflow[p]) {  // scatter the recorded occurrences
+            c.begin(ST_SCAN_FILL);
+            scan_scatter_kernel<<<ngroups, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
+            c.end(ST_SCAN_FILL, 1, pocc * 8);  // 4 B per occurrence read from the stream + 4 B written to its list
             c.stats.bytes[ST_SCAN_COUNT] += pocc * 4;
+            continue;
         }
-        if (pocc && (!streamed || overflow[p])) {
-            a.only_overflow = streamed ? 1u : 0u;
-            if (a.has_short) scan_kernel<true, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-            else scan_kernel<true, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
-            launches++;
-            if (!streamed) bytes += n + pocc * 4;
+        // legacy two-scan path: no stream memory for this pass, or some row found more occurrences than its stream
+        // holds (> 2 per text position) -- count per row, then scan again and write at the row cursors
+        if (pd[p].stream) {
+            legacy_count(p, spare_matrix, spare_part, pd[p].total);
+            a.matrix = spare_matrix;
         }
-        c.end(ST_SCAN_FILL, launches, bytes);
+        c.begin(ST_SCAN_FILL);
+        if (a.has_short) scan_kernel<SCAN_FILL, true><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        else scan_kernel<SCAN_FILL, false><<<grid, SCAN_WARPS * 32, smem, c.stream>>>(a);
+        c.end(ST_SCAN_FILL, 1, n + pocc * 4);
     }
     trace().mark("scan: pass 2 launched");
     c.stats.scan_passes += npass;
