@@ -5,94 +5,96 @@
 // positions where the subpattern occurs.
 //
 // Layout / algorithm
-//  * up to SCAN_S patterns per pass; patterns are keyed by (class, first min(len,8) bytes) where
-//    class = min(len, 8).  Class <= 7 keys are exact; class 8 entries (len >= 8) are verified byte by byte.
-//  * shared memory per CTA: two-choice (cuckoo) hash table of the pass (SoA, two halves of SCAN_H / 2 slots, built on
-//    the host so that every key sits in one of its two home slots: a probe is two independent slot reads, no walk), the prefilter
-//    f3 (hashed first 3 bytes -> byte with bit c-1 set for every class c = 3..8 that has a pattern with that
-//    prefix) refined by f4 (hashed first 4 bytes, classes 4..8); f1/f2 bitmaps for 1- and 2-byte patterns;
-//    one work queue per warp.
-//  * every warp owns one contiguous chunk of the shard ("row") and walks it 256 positions per step:
-//    lane l holds bytes [8l, 8l+12) of the step in registers (one coalesced 8-byte load + a shuffle), looks
-//    up the class-mask byte of its 8 positions and packs them into 64 bits.  A warp prefix sum of the
-//    popcounts gives every lane its place in (POSITION, CLASS) ORDER; one short loop over the set bits
-//    appends 4-byte items (position in row | (class - 1) << 16), one per probe, to the warp's circular queue.
-//  * the queue is drained only in full rounds of 32 items (leftovers wait for the next step), all lanes
-//    busy with one probe each: re-read the item's 8-byte window from the text (L1), mask it to the lane's
-//    class length, one hash probe, then a warp-wide emit.
-//  * pass 1 counts occurrences per (row, pattern) with fire-and-forget reductions into the (L2-resident)
-//    count matrix and records every hit in the row's stream; the column-wise exclusive scan of the matrix
-//    gives every row its write cursor per pattern; pass 2 scatters the stream (scan_scatter_kernel) -- or, for
-//    rows whose stream overflowed, repeats the walk -- writing positions at cursor + rank (rank among equal
-//    patterns of the round by __match_any_sync), which makes every list sorted and the result deterministic.
-//  * measured alternatives that lost: per-position queue entries with a class loop in the drain (idle lanes in
-//    every class visit), shared-memory row counters (16 warps/SM instead of 32), one warp per row in the scatter
-//    (4x DRAM traffic), and probing every lane's candidates in place without a queue (lane imbalance: 1.44 ms
-//    against 0.87 ms for the queue on BASELINE config 2).
-//  * algorithmic bytes per pass: 2 x shard bytes read + 4 B per occurrence written (+ count matrix).
+//  * the patterns of a pass (<= SCAN_S, <= SCAN_NODES trie nodes) form a trie over their first min(len, 8) bytes.
+//    Nodes exist from depth 3 on (depth = bytes matched); a node knows whether a pattern ends there (its id) and whether
+//    it has children.  Patterns longer than 8 bytes hang off their depth-8 node as a chain and are verified byte by byte.
+//  * shared memory per CTA (one bulk copy, ScanTables):
+//      root[16384]  u32, indexed by a 14-bit hash of the first THREE bytes; the entry holds the other 10 bits of the
+//                   (bijective) hash and the id of the depth-3 node, so one load decides EXACTLY whether a position can
+//                   start an occurrence.  Two pattern prefixes that hash to the same entry make it "ambiguous": such
+//                   positions resolve their prefix through the edge table instead (a few percent of the prefixes).
+//      edge[16384]  u32, two-choice (cuckoo) hash of (parent node, next byte) -> child node; the key is 25 bits, the
+//                   hash a bijection on 25 bits, so (slot, 12-bit check) identifies the key: a lookup is two independent
+//                   loads and two compares, never a walk and never a verify.  Also holds the pseudo keys of ambiguous
+//                   prefixes and of 1- and 2-byte patterns.
+//      info[8192]   u32 per node: depth, "a pattern ends here", "has children", pattern id.
+//    plus one work queue per warp and the count lines of the CTA's two row groups.
+//  * every warp owns one contiguous chunk of the shard ("row") and walks it 256 positions per step: lane l holds bytes
+//    [8l, 8l+12) of the step in registers (one coalesced 8-byte load + a shuffle) and looks its 8 positions up in
+//    root[] -- ~9 instructions and one shared-memory load per position.  Positions that hit become work ITEMS
+//    (position | node), appended to the warp's queue in position order by a prefix sum, no divergent loop.
+//  * the queue is drained in rounds of 32 items, every lane busy with ONE item: read the node, emit an occurrence if
+//    a pattern ends there, look up the child for the next text byte and append the child as a new item.  Every item
+//    costs one emit and one lookup whatever the pattern lengths are; there is no per-class loop with idle lanes and
+//    no re-hash of a whole window per (position, length) pair.  Items of one depth stay in position order (FIFO, lane
+//    order), a pattern ends at exactly one depth, so every list receives its positions ascending.
+//  * an occurrence is counted in the group's shared-memory counters and appended to the row's hit stream
+//    (SCAN_STREAM); the stream is later scattered into the lists by scan_scatter_kernel.  The legacy modes
+//    (SCAN_COUNT / SCAN_FILL: per-row count matrix by global reductions, second scan writing at the row cursors) serve
+//    passes without stream memory and rows that find more occurrences than their stream holds.
+//  * measured alternatives that lost (profiles/): one queue entry per (position, length class) pair probed
+//    in a hash table of whole keys (3.4 warp instructions per text byte, 0.81 ms for BASELINE config 2), per-position
+//    entries with a class loop in the drain (idle lanes), probing in place without a queue (lane imbalance),
+//    global reductions into a per-row count matrix (1.2 cycles of the load/store pipe per LANE).
+//  * algorithmic bytes per pass: shard bytes read + 4 B per occurrence written.
 #pragma once
 #include <algorithm>
 #include <string>
+#include <unordered_map>
 
 #include "common.cuh"
 #include "tma.cuh"
 
 namespace vlgb {
 
-constexpr int SCAN_S = 2048;       // patterns per pass
-constexpr int SCAN_H = 8192;       // hash slots (4 B each; load factor <= 25%)
-constexpr int SCAN_WARPS = 32;     // warps per CTA (one CTA per SM: the pass tables take half its shared memory)
+constexpr int SCAN_S = 2048;       // patterns per pass (11-bit ids)
+constexpr int SCAN_NODES = 8192;   // trie nodes per pass (13-bit ids)
+constexpr int SCAN_ROOT = 16384;   // root entries
+constexpr int SCAN_EDGE = 16384;   // edge slots, two halves of 8192
+constexpr int SCAN_EDGE_MAX = 6600;  // entries the host puts into the edge table (40 % load: cuckoo settles)
+constexpr int SCAN_WARPS = 32;     // warps per CTA (one CTA per SM)
 constexpr int SCAN_PPL = 8;        // positions per lane per step
 constexpr int SCAN_STEP = 32 * SCAN_PPL;
-constexpr int SCAN_F3 = 65536;     // 3-byte prefilter entries (u8: bit c-1 set = class c present, c = 3..8)
-constexpr int SCAN_F4 = 32768;     // 4-byte prefilter entries (u8: bit c-1 set = class c present, c = 4..8)
 constexpr int SCAN_F2_WORDS = 64;  // 2048 bits
 constexpr int SCAN_F1_WORDS = 8;   // 256 bits
-constexpr int SCAN_QCAP = 512;     // entries (u32) of a warp's circular work queue
-constexpr int SCAN_RB = 64;        // rows per row-block in the count-matrix scan
-constexpr uint32_t SCAN_MAX_CHUNK = 65280;  // u16 per-row counters
+constexpr int SCAN_QCAP = 256;     // items (u32) of a warp's circular work queue
+constexpr int SCAN_RB = 64;        // rows per row-block in the legacy count-matrix scan
+constexpr uint32_t SCAN_MAX_CHUNK = 65280;  // positions per row: an item keeps its position in 16 bits
+static_assert(SCAN_S <= 2048, "pattern ids are 11 bits");
 
-// Hash slot word: 0 = empty, else  1 << 31 | tag (17 bits) << 14 | (class - 1) << 11 | local pid (11 bits),
-// class = min(len, 8).  Two-choice (cuckoo) placement: a key lives in slot[h & (H/2-1)] or in
-// slot[H/2 + (h2 & (H/2-1))]; a probe reads both words (independent loads) and compares the 8-byte key (by pid) only
-// on a tag hit.  Patterns of class 8 that share their first 8 bytes are chained through long_next (one table entry).
-constexpr uint32_t SCAN_PID_MASK = 0x7FFu;
-static_assert(SCAN_S <= 2048, "pid field of the slot word is 11 bits");
+// root entry: bit 31 valid, bit 30 ambiguous (several prefixes: resolve through the edge table), bits 13..22 the
+//             10 check bits of the prefix hash, bits 0..12 node id
+// edge entry: bit 31 valid, bits 13..24 the 12 check bits of the key hash, bits 0..12 child node id
+// node info : bits 0..10 pattern id, bit 11 a pattern ends here (depth 8: head of the chain of patterns that share
+//             these 8 bytes), bit 12 has children, bits 13..16 depth
+constexpr uint32_t ROOT_VALID = 0x80000000u, ROOT_AMB = 0x40000000u;
+constexpr uint32_t NODE_TERM = 1u << 11, NODE_CHILD = 1u << 12;
+// edge keys (25 bits): (node << 8 | byte) for real edges; pseudo keys for what the root table cannot resolve
+constexpr uint32_t KEY_SHORT1 = 1u << 21;  // | b0            -> node of the 1-byte pattern
+constexpr uint32_t KEY_SHORT2 = 1u << 22;  // | b0 | b1 << 8  -> node of the 2-byte pattern
+constexpr uint32_t KEY_PREFIX3 = 1u << 24; // | 24-bit prefix -> depth-3 node of an ambiguous prefix
+constexpr uint32_t KEY_MASK = (1u << 25) - 1u;
+// work item: bits 0..15 position - row start, bits 16..28 node id, bits 29..30 type
+constexpr uint32_t ITEM_NODE = 0, ITEM_PREFIX3 = 1, ITEM_SHORT1 = 2, ITEM_SHORT2 = 3;
 
 struct ScanTables {  // one pass; same layout on host, in global memory and in shared memory
-    uint32_t slot[SCAN_H];
-    uint32_t klo[SCAN_S];   // first min(len, 8) bytes of pattern pid, zero padded
-    uint32_t khi[SCAN_S];
-    uint8_t f3[SCAN_F3];
-    uint8_t f4[SCAN_F4];
-    uint32_t f2[SCAN_F2_WORDS];
-    uint32_t f1[SCAN_F1_WORDS];
-    uint32_t seed;          // mixed into the hash; the host re-seeds when a cuckoo insertion does not settle
-    uint32_t pad[3];
+    uint32_t root[SCAN_ROOT];
+    uint32_t edge[SCAN_EDGE];
+    uint32_t info[SCAN_NODES];
+    uint32_t f2[SCAN_F2_WORDS];  // 2-byte patterns: bitmap over an 11-bit hash of the two bytes (candidates only)
+    uint32_t f1[SCAN_F1_WORDS];  // 1-byte patterns: bitmap over the byte
+    uint32_t mul_root, mul_e1, mul_e2;  // odd multipliers of the three bijective hashes (the host re-seeds when the
+    uint32_t pad;                       // cuckoo placement does not settle)
 };
 
-// 32-bit mix of (key, class): low 12 bits = first home slot, bits 13..29 = tag
-__host__ __device__ inline uint32_t scan_mix(uint32_t klo, uint32_t khi, uint32_t c, uint32_t seed)
-{
-    uint32_t h = (klo * 0x9E3779B1u) ^ ((khi + c + seed) * 0x85EBCA77u);
-    h ^= h >> 15;
-    h *= 0x2C1B3C6Du;
-    h ^= h >> 13;
-    return h;
-}
-// second home slot (upper half of the table), from bits the tag does not determine
-__host__ __device__ inline uint32_t scan_slot2(uint32_t h)
-{
-    uint32_t g = h * 0xC2B2AE35u;
-    g ^= g >> 16;
-    return (uint32_t)(SCAN_H / 2) + (g & (uint32_t)(SCAN_H / 2 - 1));
-}
-__host__ __device__ inline uint32_t scan_slot_word(uint32_t h, uint32_t c)  // pid field left 0
-{
-    return 0x80000000u | (((h >> 13) & 0x1FFFFu) << 14) | ((c - 1u) << 11);
-}
-__host__ __device__ inline uint32_t scan_h3(uint32_t w) { return ((w & 0xFFFFFFu) * 0x9E3779B1u) >> 16; }
-__host__ __device__ inline uint32_t scan_h4(uint32_t w) { return (w * 0x85EBCA77u) >> 17; }
+// root: (prefix24 << 8) * mul is (prefix24 * mul mod 2^24) << 8: slot = top 14 bits, check = the next 10
+__host__ __device__ inline uint32_t root_hash(uint32_t w, uint32_t mul) { return (w << 8) * mul; }
+__host__ __device__ inline uint32_t root_slot(uint32_t h) { return h >> 18; }
+__host__ __device__ inline uint32_t root_check(uint32_t h) { return (h >> 8) & 0x3FFu; }
+// edge: key * mul mod 2^25: slot = top 13 bits (inside one half of the table), check = low 12 bits
+__host__ __device__ inline uint32_t edge_hash(uint32_t key, uint32_t mul) { return (key * mul) & KEY_MASK; }
+__host__ __device__ inline uint32_t edge_slot(uint32_t h) { return h >> 12; }
+__host__ __device__ inline uint32_t edge_word(uint32_t h, uint32_t child) { return 0x80000000u | ((h & 0xFFFu) << 13) | child; }
 __host__ __device__ inline uint32_t scan_h2(uint32_t w) { return ((w & 0xFFFFu) * 0x9E3779B1u) >> 21; }
 
 struct ScanArgs {
@@ -103,12 +105,12 @@ struct ScanArgs {
     uint32_t s_act;          // patterns in this pass
     uint32_t s_stride;       // row stride of the count matrix (multiple of 32)
     uint32_t has_short;      // the pass holds 1- or 2-byte patterns
-    uint32_t align0, align1; // byte masks of the positions j = 0..3 / 4..7 of a lane that are symbol-aligned
-                             // (all ones for byte texts; W-byte symbols start at multiples of W)
+    uint32_t align;          // bit j set = position j of a lane's eight is symbol-aligned (all ones for byte texts;
+                             // W-byte symbols start at multiples of W)
     const ScanTables* tables;
-    const uint32_t* long_len;  // [s_act] full length (class 8 only: len >= 8)
+    const uint32_t* long_len;  // [s_act] full length (patterns of >= 8 bytes only)
     const uint32_t* long_off;  // [s_act] offset into long_blob
-    const uint32_t* long_next; // [s_act] next pattern of class 8 with the same first 8 bytes (NONE32 = end of chain)
+    const uint32_t* long_next; // [s_act] next pattern with the same first 8 bytes (NONE32 = end of chain)
     const uint8_t* long_blob;
     uint32_t* matrix;        // LEGACY passes only: [rows][s_stride] counts (zeroed by the host first) / write cursors
                              // inside each list (the re-scan advances them)
@@ -116,14 +118,13 @@ struct ScanArgs {
                              // counts (stream pass out), then the group's write cursor inside each list
     const uint64_t* list_base;  // pass 2: [s_act] first word of every list inside `out`
     uint32_t* out;           // pass 2: positions (u32, shard-local)
-    // hit stream: pass 1 records every occurrence of a row as (position - row start) | pid << 16, in the order
-    // it was found (ascending per pattern), so that pass 2 only has to scatter it (scan_scatter_kernel).  A row
-    // with more than stream_cap occurrences is re-scanned by the FILL kernel instead.
+    // hit stream: the stream pass records every occurrence of a row as (position - row start) | pid << 16, in the
+    // order it was found (ascending per pattern), so that pass 2 only has to scatter it (scan_scatter_kernel).
     uint32_t* stream;        // [rows][stream_cap] or nullptr
     uint32_t stream_cap;
-    uint32_t* row_hits;      // [rows] occurrences found in the row (pass 1 out)
-    uint32_t* overflow;      // number of rows with row_hits > stream_cap (pass 1 out)
-    uint32_t only_overflow;  // FILL kernel: skip the rows the scatter kernel handles
+    uint32_t* row_hits;      // [rows] occurrences found in the row (stream pass out)
+    uint32_t* overflow;      // number of rows with row_hits > stream_cap (stream pass out)
+    uint32_t only_overflow;  // unused (kept for the ABI of the args block)
 };
 
 static_assert(sizeof(ScanTables) % 16 == 0 && sizeof(ScanTables) < (1u << 20), "one bulk copy (mbarrier tx count < 2^20)");
@@ -137,103 +138,114 @@ constexpr int SCAN_STREAM = 0;  // default: count it in the group's shared-memor
 constexpr int SCAN_COUNT = 1;   // legacy pass 1: count it in the per-row matrix (global reduction), no stream
 constexpr int SCAN_FILL = 2;    // legacy pass 2: write it at the row's cursor
 
-// One drain round: the first n (<= 32) queue entries starting at qhead, one per lane, all lanes converged.
-// Entry = (position - row start) | (class - 1) << 16: ONE probe, so a lane never idles while the warp visits a
-// class it does not carry.  The 8-byte window of the position is re-read from the text (L1-resident: the
-// warp loaded that line moments ago), masked to the lane's class length and looked up in the hash table (one
-// 4-byte slot word per probe; the key itself is compared only on a tag hit).  Hits are ranked among equal
-// patterns in lane order = (position, class) order.  A pattern belongs to exactly one class and the queue is
-// FIFO per class, so every list receives its positions in ascending order.
-template <int MODE>
-__device__ __forceinline__ void scan_drain_round(const ScanArgs& a, const ScanTables* T, const uint32_t* q,
-                                                 uint32_t qhead, uint32_t n, uint32_t row_lo, uint32_t* mrow,
-                                                 uint32_t lane, uint32_t lt_mask, uint32_t* stream_row, uint32_t& nh)
+// four text bytes at an arbitrary position (two aligned words, one funnel shift)
+__device__ __forceinline__ uint32_t text_u32(const uint8_t* text, uint32_t p)
 {
-    uint32_t p = 0, c = 1, klo = 0, khi = 0;
-    bool more = lane < n;
-    if (more) {
-        const uint32_t e = q[(qhead + lane) & (SCAN_QCAP - 1)];
+    const uint32_t* t32 = reinterpret_cast<const uint32_t*>(text + (p & ~3u));
+    return __funnelshift_r(__ldg(t32), __ldg(t32 + 1), (p & 3u) * 8u);
+}
+
+// two-choice lookup of a 25-bit key: child node id or NONE32
+__device__ __forceinline__ uint32_t edge_lookup(const ScanTables* T, uint32_t key)
+{
+    const uint32_t h1 = edge_hash(key, T->mul_e1), h2 = edge_hash(key, T->mul_e2);
+    const uint32_t e1 = T->edge[edge_slot(h1)], e2 = T->edge[SCAN_EDGE / 2 + edge_slot(h2)];
+    uint32_t r = NONE32;
+    if ((e2 >> 13) == (0x40000u | (h2 & 0xFFFu))) r = e2 & 0x1FFFu;
+    if ((e1 >> 13) == (0x40000u | (h1 & 0xFFFu))) r = e1 & 0x1FFFu;
+    return r;
+}
+
+// One drain round: the first n (<= 32) queue items starting at qhead, one per lane, all lanes converged.
+//   A. node items read their node; if a pattern ends there the occurrence is emitted (warp-wide, in lane order: items
+//      of one depth sit in the queue in position order, and a pattern ends at exactly one depth).  Depth-8 nodes carry
+//      the chain of patterns that share their 8 bytes: every member is verified against the text, one per emit round.
+//   B. one lookup per item: the child for the next text byte (node items with children), or the pseudo key of an
+//      ambiguous prefix / a short pattern.  Lanes that find a node append it to the queue as a new item.
+// Returns the number of items appended.
+template <int MODE>
+__device__ __forceinline__ uint32_t scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* q, uint32_t qhead, uint32_t n,
+                                                     uint32_t qtail, uint32_t row_lo, uint32_t* mrow, uint32_t lane, uint32_t lt_mask,
+                                                     uint32_t* stream_row, uint32_t& nh)
+{
+    const bool active = lane < n;
+    uint32_t e = 0, p = 0, type = 0, info = 0;
+    if (active) {
+        e = q[(qhead + lane) & (SCAN_QCAP - 1)];
         p = row_lo + (e & 0xFFFFu);
-        c = ((e >> 16) & 7u) + 1u;
-        const uint32_t* t32 = reinterpret_cast<const uint32_t*>(a.text + (p & ~3u));
-        const uint32_t w0 = __ldg(t32), w1 = __ldg(t32 + 1), w2 = __ldg(t32 + 2);
-        const uint32_t sh = (p & 3u) * 8u;
-        const uint32_t wlo = __funnelshift_r(w0, w1, sh), whi = __funnelshift_r(w1, w2, sh);
-        // bytes [0, c) of the window: 64-bit mask 2^(8c) - 1 split in two words (c = 8: all ones)
-        const uint32_t mlo = c >= 4 ? 0xFFFFFFFFu : ((1u << (8 * c)) - 1u);
-        const uint32_t mhi = c >= 8 ? 0xFFFFFFFFu : (c > 4 ? ((1u << (8 * (c - 4))) - 1u) : 0u);
-        klo = wlo & mlo;
-        khi = whi & mhi;
+        type = e >> 29;
+        if (type == ITEM_NODE) info = T->info[(e >> 16) & 0x1FFFu];
     }
-    // ---- one probe: both home slots (independent loads), the key itself only on a tag hit
-    uint32_t cand = NONE32;
-    if (more) {
-        const uint32_t h = scan_mix(klo, khi, c, T->seed);
-        const uint32_t want = scan_slot_word(h, c);
-        const uint32_t s1 = T->slot[h & (uint32_t)(SCAN_H / 2 - 1)], s2 = T->slot[scan_slot2(h)];
-        if ((s1 & ~SCAN_PID_MASK) == want) {
-            const uint32_t k = s1 & SCAN_PID_MASK;
-            if (T->klo[k] == klo && T->khi[k] == khi) cand = k;
-        }
-        if (cand == NONE32 && (s2 & ~SCAN_PID_MASK) == want) {
-            const uint32_t k = s2 & SCAN_PID_MASK;
-            if (T->klo[k] == klo && T->khi[k] == khi) cand = k;
-        }
-        more = cand != NONE32;
-    }
-    for (;;) {
-        uint32_t pid = NONE32;
-        if (more) {
-            bool ok;
-            if (c < 8) {
-                ok = (uint64_t)p + c <= a.valid_len;
-                more = false;  // classes 1..7: the key is the pattern
-            } else {
-                // class 8: the patterns that share these 8 bytes are chained; one candidate per emit, hit or miss --
-                // lanes holding the same key walk the same chain, so a pattern is emitted by all its lanes together
-                // and its list stays sorted
-                const uint32_t L = a.long_len[cand];
-                ok = (uint64_t)p + L <= a.valid_len;
-                if (ok) {
-                    const uint8_t* pat = a.long_blob + a.long_off[cand];
-                    const uint8_t* txt = a.text + p;
-                    for (uint32_t j = 8; j < L; j++)
-                        if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
+    const uint32_t depth = (info >> 13) & 15u;
+    // ---- A. emit
+    uint32_t cand = (info & NODE_TERM) ? (info & 0x7FFu) : NONE32;
+    if (__any_sync(0xffffffffu, cand != NONE32)) {
+        for (;;) {
+            uint32_t pid = NONE32;
+            if (cand != NONE32) {
+                bool ok;
+                if (depth < 8) {
+                    ok = (uint64_t)p + depth <= a.valid_len;
+                    if (ok) pid = cand;
+                    cand = NONE32;
+                } else {
+                    // patterns of >= 8 bytes that share these 8 bytes: one candidate per emit round, hit or miss -- lanes
+                    // on the same node walk the same chain, so a pattern is emitted by all its lanes together and its
+                    // list stays sorted
+                    const uint32_t L = a.long_len[cand];
+                    ok = (uint64_t)p + L <= a.valid_len;
+                    if (ok) {
+                        const uint8_t* pat = a.long_blob + a.long_off[cand];
+                        const uint8_t* txt = a.text + p;
+                        for (uint32_t j = 8; j < L; j++)
+                            if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
+                    }
+                    if (ok) pid = cand;
+                    cand = a.long_next[cand];
                 }
             }
-            if (ok) pid = cand;
-            if (c >= 8) {
-                cand = a.long_next[cand];
-                more = cand != NONE32;
+            const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
+            if (hits) {
+                if (MODE == SCAN_STREAM) {
+                    // bump the (group, pattern) count -- a shared-memory atomic, where the global reduction of the legacy
+                    // pass costs ~1.2 cycles of the load/store pipe per LANE (tools/microbench) -- and append the hit to
+                    // the row's stream at its place in lane order
+                    if (pid != NONE32) atomicAdd(mrow + pid, 1u);
+                    const uint32_t at = nh + __popc(hits & lt_mask);
+                    if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
+                    nh += __popc(hits);
+                } else if (MODE == SCAN_COUNT) {
+                    if (pid != NONE32) atomicAdd(mrow + pid, 1u);  // fire-and-forget L2 reduction
+                } else {
+                    // legacy pass 2: the matrix entry is the row's write cursor inside the list; rank among equal
+                    // patterns of the round = lane order = position order
+                    const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+                    const int leader = __ffs(grp) - 1;
+                    uint32_t old = 0;
+                    if (pid != NONE32 && (int)lane == leader) old = atomicAdd(mrow + pid, (uint32_t)__popc(grp));
+                    old = __shfl_sync(0xffffffffu, old, leader);
+                    if (pid != NONE32) a.out[__ldg(a.list_base + pid) + old + __popc(grp & lt_mask)] = p;
+                }
             }
+            if (!__any_sync(0xffffffffu, cand != NONE32)) break;  // only depth-8 lanes can still have candidates
         }
-        // ---- warp-wide emit (all 32 lanes take part)
-        const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
-        if (hits) {
-            if (MODE == SCAN_STREAM) {
-                // bump the (group, pattern) count -- a shared-memory atomic: ~1 cycle of the SM's load/store pipe per
-                // warp instruction, where the global reduction of the legacy pass costs ~1.2 cycles per LANE
-                // (tools/microbench, profiles/) -- and append the hit to the row's stream at its place in
-                // lane = (position, class) order
-                if (pid != NONE32) atomicAdd(mrow + pid, 1u);
-                const uint32_t at = nh + __popc(hits & lt_mask);
-                if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
-                nh += __popc(hits);
-            } else if (MODE == SCAN_COUNT) {
-                if (pid != NONE32) atomicAdd(mrow + pid, 1u);  // fire-and-forget L2 reduction
-            } else {
-                // pass 2 (rows without a usable stream): the matrix entry is the row's write cursor inside the
-                // list; rank among equal patterns of the round = lane order = position order
-                const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-                const int leader = __ffs(grp) - 1;
-                uint32_t old = 0;
-                if (pid != NONE32 && (int)lane == leader) old = atomicAdd(mrow + pid, (uint32_t)__popc(grp));
-                old = __shfl_sync(0xffffffffu, old, leader);
-                if (pid != NONE32) a.out[__ldg(a.list_base + pid) + old + __popc(grp & lt_mask)] = p;
-            }
-        }
-        if (!__any_sync(0xffffffffu, more)) break;  // only class-8 lanes can still have candidates
     }
+    // ---- B. one lookup per item
+    uint32_t child = NONE32;
+    if (active && (type != ITEM_NODE || (info & NODE_CHILD))) {
+        uint32_t key;
+        if (type == ITEM_NODE) {
+            key = (((e >> 16) & 0x1FFFu) << 8) | __ldg(a.text + p + depth);
+        } else {
+            const uint32_t w = text_u32(a.text, p);
+            key = type == ITEM_PREFIX3 ? (KEY_PREFIX3 | (w & 0xFFFFFFu)) : type == ITEM_SHORT1 ? (KEY_SHORT1 | (w & 0xFFu)) : (KEY_SHORT2 | (w & 0xFFFFu));
+        }
+        child = edge_lookup(T, key);
+    }
+    const uint32_t found = __ballot_sync(0xffffffffu, child != NONE32);
+    if (child != NONE32) q[(qtail + __popc(found & lt_mask)) & (SCAN_QCAP - 1)] = (e & 0xFFFFu) | (child << 16);
+    __syncwarp();
+    return __popc(found);
 }
 
 template <int MODE, bool SHORT>
@@ -245,9 +257,8 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t));
     uint32_t* gcnt = reinterpret_cast<uint32_t*>(smem_raw + sizeof(ScanTables) + (size_t)SCAN_WARPS * SCAN_QCAP * sizeof(uint32_t) + 16);
 
-    // stage the pass tables (144 KB): ONE bulk asynchronous copy issued by one thread, completion on an mbarrier --
-    // the copy engine moves the bytes while the warps set up (a per-thread load/store loop cost 9 trips of
-    // LDG.128 + STS.128 for every one of the 1024 threads)
+    // stage the pass tables (160 KB): ONE bulk asynchronous copy issued by one thread, completion on an mbarrier --
+    // the copy engine moves the bytes while the warps set up
     if (threadIdx.x == 0) {
         mbar_init(bar, 1);
         mbar_fence_init();
@@ -260,12 +271,11 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         bulk_g2s(T, a.tables, (uint32_t)sizeof(ScanTables), bar);
     }
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* q = queues + warp * SCAN_QCAP;        // circular queue of (position - row start) | (class - 1) << 16
+    uint32_t* q = queues + warp * SCAN_QCAP;  // circular queue of work items
     mbar_wait(bar, 0);
 
     const uint32_t row = blockIdx.x * SCAN_WARPS + warp;
-    bool live = row < a.rows;
-    if (MODE == SCAN_FILL && live && a.only_overflow && a.row_hits[row] <= a.stream_cap) live = false;  // scattered from the stream instead
+    const bool live = row < a.rows;
     if (MODE != SCAN_STREAM && !live) return;  // the stream pass meets again at the barrier before the counter flush
     // where an occurrence is counted: the group's shared-memory counters (stream pass) / the row's line of the matrix
     uint32_t* mrow = MODE == SCAN_STREAM ? gcnt + (warp / SCAN_GROUP_ROWS) * SCAN_S : a.matrix + (size_t)row * a.s_stride;
@@ -273,9 +283,59 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     const uint32_t lo = live ? row * a.chunk : 0u;
     const uint32_t hi = live ? (uint32_t)min((uint64_t)lo + a.chunk, (uint64_t)a.valid_len) : 0u;  // 64-bit: lo + chunk may pass 2^32 in the last row
     const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t mul_root = T->mul_root;
     uint32_t qhead = 0, qcount = 0;  // warp-uniform
     uint32_t nh = 0;                 // occurrences recorded in the row's hit stream (stream pass)
     uint32_t* stream_row = (MODE == SCAN_STREAM && live) ? a.stream + (size_t)row * a.stream_cap : nullptr;
+
+    auto drain_full_rounds = [&]() {
+        while (qcount >= 32) {
+            const uint32_t added = scan_drain_round<MODE>(a, T, q, qhead, 32u, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh);
+            qhead = (qhead + 32) & (SCAN_QCAP - 1);
+            qcount += added - 32;
+        }
+    };
+    // appends one item per set bit of `m` (bit j = position j of this lane) in (lane, j) = position order; item j is
+    // rel0 + j | hi[j].  At most SCAN_QCAP - 32 items go in at once: a denser step is taken in two halves (of the lanes).
+    auto enqueue = [&](uint32_t m, uint32_t rel0, const uint32_t (&hi16)[SCAN_PPL]) {
+        const uint32_t all = __popc(m);
+        uint32_t incl = all;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= (uint32_t)d) incl += o;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+        if (total == 0) return;
+        if (total <= SCAN_QCAP - 32) {
+            uint32_t idx = qhead + qcount + incl - all;
+#pragma unroll
+            for (int j = 0; j < SCAN_PPL; j++)
+                if ((m >> j) & 1u) q[idx++ & (SCAN_QCAP - 1)] = (rel0 + j) | hi16[j];
+            qcount += total;
+            __syncwarp();
+            drain_full_rounds();
+        } else {
+            // lanes 0..15 first, then lanes 16..31: queue order stays position order
+            for (uint32_t half = 0; half < 2; half++) {
+                const uint32_t mh = (lane >> 4) == half ? m : 0u;
+                const uint32_t mine = __popc(mh);
+                uint32_t inc2 = mine;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xffffffffu, inc2, d);
+                    if (lane >= (uint32_t)d) inc2 += o;
+                }
+                uint32_t idx = qhead + qcount + inc2 - mine;
+#pragma unroll
+                for (int j = 0; j < SCAN_PPL; j++)
+                    if ((mh >> j) & 1u) q[idx++ & (SCAN_QCAP - 1)] = (rel0 + j) | hi16[j];
+                qcount += __shfl_sync(0xffffffffu, inc2, 31);
+                __syncwarp();
+                drain_full_rounds();
+            }
+        }
+    };
 
     for (uint32_t base = lo; base < hi; base += SCAN_STEP) {
         // ---- 16 bytes per lane: own 8 + the next lane's 8
@@ -287,7 +347,6 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             nx = 0u;
             if (base + SCAN_STEP < a.valid_len) nx = __ldg(reinterpret_cast<const uint32_t*>(a.text + base + SCAN_STEP));
         }
-        // ---- prefilter: one class-mask byte per position (bit c-1 = a pattern of class c may start here)
         uint32_t wl[SCAN_PPL];  // low 32 bits of the window at position j
         wl[0] = own.x;
         wl[1] = __funnelshift_r(own.x, own.y, 8);
@@ -297,89 +356,51 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         wl[5] = __funnelshift_r(own.y, nx, 8);
         wl[6] = __funnelshift_r(own.y, nx, 16);
         wl[7] = __funnelshift_r(own.y, nx, 24);
-        uint32_t s0 = 0, s1 = 0;
+        // positions of this lane that may start an occurrence: symbol-aligned and, in the last step of the row, < hi
+        // (the others belong to the next row or to nobody)
+        uint32_t okpos = a.align;
+        if (base + SCAN_STEP > hi) {
+            const uint32_t left = off < hi ? min(hi - off, 8u) : 0u;
+            okpos &= (1u << left) - 1u;
+        }
+        // ---- root lookup: exact on the first three bytes
+        uint32_t m = 0, hi16[SCAN_PPL];
 #pragma unroll
         for (int j = 0; j < SCAN_PPL; j++) {
-            // classes >= 4 must also pass the 4-byte filter: most 3-byte prefixes of frequent words are shared by
-            // longer patterns that do not occur here, and every miss costs a full probe sequence
-            uint32_t mj = T->f3[scan_h3(wl[j])] & (T->f4[scan_h4(wl[j])] | 0x07u);
-            if (SHORT) {
-                const uint32_t b0 = wl[j] & 0xFFu;
-                mj |= (T->f1[b0 >> 5] >> (b0 & 31)) & 1u;
-                const uint32_t i2 = scan_h2(wl[j]);
-                mj |= ((T->f2[i2 >> 5] >> (i2 & 31)) & 1u) << 1;
-            }
-            if (j < 4) s0 |= mj << (8 * j); else s1 |= mj << (8 * (j - 4));
+            const uint32_t h = root_hash(wl[j], mul_root);
+            const uint32_t v = T->root[root_slot(h)];
+            // valid entry with my check bits, or an ambiguous entry (its prefix is resolved through the edge table)
+            const bool hit = ((v >> 13) & 0x5FFFFu) == (0x40000u | root_check(h));
+            const bool amb = v >= (ROOT_VALID | ROOT_AMB);
+            hi16[j] = amb ? (ITEM_PREFIX3 << 29) : ((v & 0x1FFFu) << 16);
+            m |= (uint32_t)(hit || amb) << j;
         }
-        s0 &= a.align0;
-        s1 &= a.align1;
-        if (base + SCAN_STEP > hi) {  // last step of the row: positions >= hi belong to the next row (or nobody)
-            const uint32_t left = off < hi ? hi - off : 0u;  // my positions j < left are inside
-            if (left < 4) { s1 = 0u; s0 &= left ? (0xFFFFFFFFu >> (8 * (4 - left))) : 0u; }
-            else if (left < 8) s1 &= left > 4 ? (0xFFFFFFFFu >> (8 * (8 - left))) : 0u;
-        }
-        // ---- one queue entry per set mask bit = one (position, class) probe, in (position, class) order.  The
-        // queue starts a step with fewer than 32 leftovers, so up to SCAN_QCAP - 32 new entries go in at once
-        // (the common case); a step with more probes (small alphabets: every position carries several
-        // classes) is enqueued class by class, at most 256 entries at a time.  Entries of one class stay in
-        // FIFO = position order either way.
         const uint32_t rel0 = off - lo;
-        const uint32_t all = __popc(s0) + __popc(s1);
-        uint32_t incl = all;
+        enqueue(m & okpos, rel0, hi16);
+        if (SHORT) {
+            uint32_t m1 = 0, m2 = 0;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= (uint32_t)d) incl += o;
-        }
-        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-        if (total == 0) continue;
-        if (total <= SCAN_QCAP - 32) {
-            uint32_t idx = qhead + qcount + incl - all;
-            for (uint32_t m = s0; m; m &= m - 1) {
-                const uint32_t b = __ffs(m) - 1;
-                q[idx++ & (SCAN_QCAP - 1)] = (rel0 + (b >> 3)) | ((b & 7u) << 16);
+            for (int j = 0; j < SCAN_PPL; j++) {
+                const uint32_t b0 = wl[j] & 0xFFu;
+                m1 |= ((T->f1[b0 >> 5] >> (b0 & 31)) & 1u) << j;
+                const uint32_t i2 = scan_h2(wl[j]);
+                m2 |= ((T->f2[i2 >> 5] >> (i2 & 31)) & 1u) << j;
             }
-            for (uint32_t m = s1; m; m &= m - 1) {
-                const uint32_t b = __ffs(m) - 1;
-                q[idx++ & (SCAN_QCAP - 1)] = (rel0 + 4 + (b >> 3)) | ((b & 7u) << 16);
-            }
-            qcount += total;
-            __syncwarp();
-            while (qcount >= 32) {  // drain full rounds; fewer than 32 leftovers wait for the next step
-                scan_drain_round<MODE>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
-                qhead = (qhead + 32) & (SCAN_QCAP - 1);
-                qcount -= 32;
-            }
-            __syncwarp();
-        } else {
-            const uint32_t present = __reduce_or_sync(0xffffffffu, s0 | s1);
-            uint32_t classes = (present | (present >> 8) | (present >> 16) | (present >> 24)) & 0xFFu;
-            while (classes) {
-                const uint32_t cb = __ffs(classes) - 1;  // class - 1, warp-uniform
-                classes &= classes - 1;
-                const uint32_t t0 = (s0 >> cb) & 0x01010101u, t1 = (s1 >> cb) & 0x01010101u;
-                const uint32_t mine = __popc(t0) + __popc(t1);
-                uint32_t inc2 = mine;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const uint32_t o = __shfl_up_sync(0xffffffffu, inc2, d);
-                    if (lane >= (uint32_t)d) inc2 += o;
-                }
-                uint32_t idx = qhead + qcount + inc2 - mine;
-                for (uint32_t m = t0; m; m &= m - 1) q[idx++ & (SCAN_QCAP - 1)] = (rel0 + ((__ffs(m) - 1) >> 3)) | (cb << 16);
-                for (uint32_t m = t1; m; m &= m - 1) q[idx++ & (SCAN_QCAP - 1)] = (rel0 + 4 + ((__ffs(m) - 1) >> 3)) | (cb << 16);
-                qcount += __shfl_sync(0xffffffffu, inc2, 31);
-                __syncwarp();
-                while (qcount >= 32) {
-                    scan_drain_round<MODE>(a, T, q, qhead, 32u, lo, mrow, lane, lt_mask, stream_row, nh);
-                    qhead = (qhead + 32) & (SCAN_QCAP - 1);
-                    qcount -= 32;
-                }
-                __syncwarp();
-            }
+            for (int j = 0; j < SCAN_PPL; j++) hi16[j] = ITEM_SHORT1 << 29;
+            enqueue(m1 & okpos, rel0, hi16);
+#pragma unroll
+            for (int j = 0; j < SCAN_PPL; j++) hi16[j] = ITEM_SHORT2 << 29;
+            enqueue(m2 & okpos, rel0, hi16);
         }
     }
-    if (qcount) scan_drain_round<MODE>(a, T, q, qhead, qcount, lo, mrow, lane, lt_mask, stream_row, nh);
+    // the tail: rounds until the queue runs dry (a round can append what it finds)
+    while (qcount) {
+        const uint32_t n = min(qcount, 32u);
+        const uint32_t added = scan_drain_round<MODE>(a, T, q, qhead, n, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh);
+        qhead = (qhead + n) & (SCAN_QCAP - 1);
+        qcount += added - n;
+    }
     if (MODE == SCAN_STREAM) {
         if (live && lane == 0) {
             a.row_hits[row] = nh;
@@ -613,33 +634,7 @@ struct PatternDict {
     }
 };
 
-// Places entry `word` (tag | class | pid) of hash h into one of its two home slots, moving earlier entries to their
-// other home when both are taken (cuckoo).  `hs[pid]` = hash of every placed entry.  False if it does not settle.
-inline bool cuckoo_insert(ScanTables& t, std::vector<uint32_t>& hs, uint32_t word, uint32_t h)
-{
-    uint32_t cur_word = word, cur_h = h;
-    uint32_t slot = cur_h & (uint32_t)(SCAN_H / 2 - 1);
-    for (int kicks = 0; kicks < 512; kicks++) {
-        if (!t.slot[slot]) {
-            t.slot[slot] = cur_word;
-            return true;
-        }
-        const uint32_t other = slot < (uint32_t)(SCAN_H / 2) ? scan_slot2(cur_h) : (cur_h & (uint32_t)(SCAN_H / 2 - 1));
-        if (!t.slot[other]) {
-            t.slot[other] = cur_word;
-            return true;
-        }
-        // evict the resident of `slot`, put the current entry there, continue with the evicted one at ITS other home
-        const uint32_t ev = t.slot[slot];
-        t.slot[slot] = cur_word;
-        cur_word = ev;
-        cur_h = hs[ev & SCAN_PID_MASK];
-        const uint32_t home1 = cur_h & (uint32_t)(SCAN_H / 2 - 1);
-        slot = slot == home1 ? scan_slot2(cur_h) : home1;
-    }
-    return false;
-}
-
+// ---- host side: the trie of a pass and its tables ------------------------------------------------
 struct PassHost {
     ScanTables tables;
     std::vector<uint32_t> long_len, long_off, long_next;
@@ -648,68 +643,193 @@ struct PassHost {
     bool has_short = false;
 };
 
-inline void build_pass(const PatternDict& d, uint32_t first, uint32_t count, PassHost& ph)
+// two-choice placement of (key -> child) in the edge table, moving earlier entries to their other home when both
+// homes are taken.  keys[] / childs[] hold every entry placed so far, where[] the slot of each.  False = did not settle.
+struct EdgeBuilder {
+    std::vector<uint32_t> keys, childs;
+    std::vector<int32_t> owner;  // per slot: index into keys, -1 = empty
+    uint32_t m1 = 0, m2 = 0;
+    void reset(uint32_t mul1, uint32_t mul2)
+    {
+        owner.assign(SCAN_EDGE, -1);
+        m1 = mul1;
+        m2 = mul2;
+    }
+    uint32_t home(uint32_t k, int which) const
+    {
+        return which == 0 ? edge_slot(edge_hash(keys[k], m1)) : (uint32_t)(SCAN_EDGE / 2) + edge_slot(edge_hash(keys[k], m2));
+    }
+    bool place(uint32_t k)
+    {
+        uint32_t cur = k;
+        int which = 0;
+        for (int kicks = 0; kicks < 256; kicks++) {
+            const uint32_t s0 = home(cur, which);
+            if (owner[s0] < 0) { owner[s0] = (int32_t)cur; return true; }
+            const uint32_t s1 = home(cur, which ^ 1);
+            if (owner[s1] < 0) { owner[s1] = (int32_t)cur; return true; }
+            // evict the resident of s0; it moves to ITS other home
+            const uint32_t ev = (uint32_t)owner[s0];
+            owner[s0] = (int32_t)cur;
+            cur = ev;
+            which = s0 < (uint32_t)(SCAN_EDGE / 2) ? 1 : 0;
+        }
+        return false;
+    }
+    bool settle()
+    {
+        for (uint32_t k = 0; k < keys.size(); k++)
+            if (!place(k)) return false;
+        return true;
+    }
+    void write(ScanTables& t) const
+    {
+        for (uint32_t s = 0; s < (uint32_t)SCAN_EDGE; s++) {
+            if (owner[s] < 0) continue;
+            const uint32_t k = (uint32_t)owner[s];
+            const uint32_t h = edge_hash(keys[k], s < (uint32_t)(SCAN_EDGE / 2) ? m1 : m2);
+            t.edge[s] = edge_word(h, childs[k]);
+        }
+    }
+};
+
+// Builds the tables of the pass that starts at dictionary pattern `first`: as many of the next patterns (<= SCAN_S) as
+// fit SCAN_NODES trie nodes and SCAN_EDGE_MAX edge-table entries.  Returns how many patterns it took (>= 1).
+inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_count, PassHost& ph)
 {
     ph.first = first;
-    ph.count = count;
-    std::vector<uint32_t> hs(count, 0);
-    for (uint32_t seed = 0;; seed++) {
-        memset(&ph.tables, 0, sizeof ph.tables);
-        ph.tables.seed = seed * 0x9E3779B9u;
-        ph.long_len.assign(count, 0);
-        ph.long_off.assign(count, 0);
-        ph.long_next.assign(count, NONE32);
-        ph.long_blob.clear();
-        ph.has_short = false;
-        bool settled = true;
-        for (uint32_t i = 0; i < count && settled; i++) {
-            const std::string& s = d.pats[first + i];
-            uint32_t len = (uint32_t)s.size();
-            uint32_t c = len < 8 ? len : 8;
-            uint64_t key = 0;
-            for (uint32_t j = 0; j < len && j < 8; j++) key |= (uint64_t)(uint8_t)s[j] << (8 * j);
-            uint32_t klo = (uint32_t)key, khi = (uint32_t)(key >> 32);
-            const uint32_t h = scan_mix(klo, khi, c, ph.tables.seed);
-            hs[i] = h;
-            ph.tables.klo[i] = klo;
-            ph.tables.khi[i] = khi;
-            uint32_t w32 = klo;
-            if (c <= 2) ph.has_short = true;
-            if (c == 1) {
-                ph.tables.f1[(w32 & 0xFF) >> 5] |= 1u << (w32 & 31);
-            } else if (c == 2) {
-                uint32_t i2 = scan_h2(w32);
-                ph.tables.f2[i2 >> 5] |= 1u << (i2 & 31);
+    ph.long_len.clear();
+    ph.long_off.clear();
+    ph.long_next.clear();
+    ph.long_blob.clear();
+    ph.has_short = false;
+    std::vector<uint32_t> info;                       // per node
+    std::unordered_map<uint64_t, uint32_t> node_of;  // (kind, parent / prefix, byte) -> node id
+    std::vector<std::pair<uint32_t, uint32_t>> prefix3;  // (24-bit prefix, node) of every depth-3 node
+    EdgeBuilder eb;
+    auto new_node = [&](uint32_t depth) {
+        info.push_back(depth << 13);
+        return (uint32_t)info.size() - 1;
+    };
+    uint32_t count = 0;
+    for (; count < max_count && count < (uint32_t)SCAN_S; count++) {
+        const std::string& s = d.pats[first + count];
+        const uint32_t len = (uint32_t)s.size();
+        // worst case this pattern adds 6 nodes and 6 edge entries (+ its prefix, should the root entry turn ambiguous)
+        if (count && (info.size() + 6 > (size_t)SCAN_NODES || eb.keys.size() + prefix3.size() / 8 + 8 > (size_t)SCAN_EDGE_MAX)) break;
+        auto b = [&](uint32_t j) { return (uint32_t)(uint8_t)s[j]; };
+        uint32_t node;
+        if (len <= 2) {
+            ph.has_short = true;
+            const uint32_t key = len == 1 ? (KEY_SHORT1 | b(0)) : (KEY_SHORT2 | b(0) | (b(1) << 8));
+            node = new_node(len);  // distinct patterns: always a new node
+            eb.keys.push_back(key);
+            eb.childs.push_back(node);
+        } else {
+            const uint32_t p24 = b(0) | (b(1) << 8) | (b(2) << 16);
+            auto it = node_of.find((uint64_t)1 << 40 | p24);
+            if (it == node_of.end()) {
+                node = new_node(3);
+                node_of.emplace((uint64_t)1 << 40 | p24, node);
+                prefix3.emplace_back(p24, node);
             } else {
-                ph.tables.f3[scan_h3(w32)] |= (uint8_t)(1u << (c - 1));
-                if (c >= 4) ph.tables.f4[scan_h4(w32)] |= (uint8_t)(1u << (c - 1));
+                node = it->second;
             }
-            bool chained = false;
-            if (c == 8) {
-                ph.long_len[i] = len;
-                ph.long_off[i] = (uint32_t)ph.long_blob.size();
-                ph.long_blob += s;
-                // patterns with the same first 8 bytes share ONE table entry: append to the chain of the resident
-                const uint32_t want = scan_slot_word(h, c);
-                const uint32_t homes[2] = {h & (uint32_t)(SCAN_H / 2 - 1), scan_slot2(h)};
-                for (uint32_t hm : homes) {
-                    const uint32_t w = ph.tables.slot[hm];
-                    if (w && (w & ~SCAN_PID_MASK) == want) {
-                        uint32_t k = w & SCAN_PID_MASK;
-                        if (ph.tables.klo[k] == klo && ph.tables.khi[k] == khi) {
-                            while (ph.long_next[k] != NONE32) k = ph.long_next[k];
-                            ph.long_next[k] = i;
-                            chained = true;
-                            break;
-                        }
-                    }
+            for (uint32_t dpt = 4; dpt <= std::min<uint32_t>(len, 8); dpt++) {
+                const uint32_t key = (node << 8) | b(dpt - 1);
+                auto ic = node_of.find((uint64_t)key);
+                if (ic == node_of.end()) {
+                    const uint32_t child = new_node(dpt);
+                    node_of.emplace((uint64_t)key, child);
+                    eb.keys.push_back(key);
+                    eb.childs.push_back(child);
+                    info[node] |= NODE_CHILD;
+                    node = child;
+                } else {
+                    node = ic->second;
                 }
             }
-            if (!chained) settled = cuckoo_insert(ph.tables, hs, scan_slot_word(h, c) | i, h);
         }
-        if (settled) return;
-        if (seed > 64) throw CudaError{cudaErrorUnknown, __FILE__, __LINE__};  // 2048 keys in 8192 slots: never
+        ph.long_len.push_back(0);
+        ph.long_off.push_back(0);
+        ph.long_next.push_back(NONE32);
+        if (len >= 8) {
+            ph.long_len[count] = len;
+            ph.long_off[count] = (uint32_t)ph.long_blob.size();
+            ph.long_blob += s;
+            if (info[node] & NODE_TERM) {  // append to the chain of the patterns that share these 8 bytes
+                uint32_t k = info[node] & 0x7FFu;
+                while (ph.long_next[k] != NONE32) k = ph.long_next[k];
+                ph.long_next[k] = count;
+            } else {
+                info[node] |= NODE_TERM | count;
+            }
+        } else {
+            info[node] |= NODE_TERM | count;  // a shorter pattern owns its node alone
+        }
     }
+    ph.count = count;
+    // ---- root table: the multiplier (of a few) that leaves the fewest prefixes ambiguous
+    static const uint32_t muls[8] = {0x9E3779B1u, 0x85EBCA77u, 0xC2B2AE3Du, 0x27D4EB2Fu, 0x165667B1u, 0xD3A2646Du, 0xFD7046C5u, 0xB55A4F09u};
+    uint32_t best_mul = muls[0], best_amb = ~0u;
+    std::vector<uint16_t> fill(SCAN_ROOT);
+    for (uint32_t mul : muls) {
+        std::fill(fill.begin(), fill.end(), 0);
+        uint32_t amb = 0;
+        for (auto& pr : prefix3) {
+            uint16_t& f = fill[root_slot(root_hash(pr.first, mul))];
+            if (f == 1) amb += 2; else if (f > 1) amb += 1;
+            if (f < 3) f++;
+        }
+        if (amb < best_amb) { best_amb = amb; best_mul = mul; }
+        if (!amb) break;
+    }
+    memset(&ph.tables, 0, sizeof ph.tables);
+    ph.tables.mul_root = best_mul;
+    std::fill(fill.begin(), fill.end(), 0);
+    for (auto& pr : prefix3) {
+        uint16_t& f = fill[root_slot(root_hash(pr.first, best_mul))];
+        if (f < 3) f++;
+    }
+    const size_t real_edges = eb.keys.size();
+    for (auto& pr : prefix3) {
+        const uint32_t h = root_hash(pr.first, best_mul);
+        if (fill[root_slot(h)] == 1) {
+            ph.tables.root[root_slot(h)] = ROOT_VALID | (root_check(h) << 13) | pr.second;
+        } else {
+            ph.tables.root[root_slot(h)] = ROOT_VALID | ROOT_AMB;
+            eb.keys.push_back(KEY_PREFIX3 | pr.first);
+            eb.childs.push_back(pr.second);
+        }
+    }
+    (void)real_edges;
+    for (uint32_t i = 0; i < (uint32_t)info.size(); i++) ph.tables.info[i] = info[i];
+    for (uint32_t i = 0; i < count; i++) {
+        const std::string& s = d.pats[first + i];
+        if (s.size() == 1) {
+            const uint32_t b0 = (uint8_t)s[0];
+            ph.tables.f1[b0 >> 5] |= 1u << (b0 & 31);
+        } else if (s.size() == 2) {
+            const uint32_t i2 = scan_h2((uint32_t)(uint8_t)s[0] | ((uint32_t)(uint8_t)s[1] << 8));
+            ph.tables.f2[i2 >> 5] |= 1u << (i2 & 31);
+        }
+    }
+    // ---- edge table
+    for (uint32_t seed = 0;; seed++) {
+        const uint32_t m1 = (0x9E3779B1u + seed * 0x7F4A7C15u * 2u) | 1u, m2 = (0x85EBCA77u + seed * 0x3C6EF372u) | 1u;
+        eb.reset(m1, m2);
+        if (eb.settle()) {
+            ph.tables.mul_e1 = m1;
+            ph.tables.mul_e2 = m2;
+            eb.write(ph.tables);
+            break;
+        }
+        if (seed > 16) {  // 40 % load, two choices: practically never; take fewer patterns rather than fail
+            if (count <= 1) throw CudaError{cudaErrorUnknown, __FILE__, __LINE__};
+            return build_pass(d, first, count * 3 / 4, ph);
+        }
+    }
+    return count;
 }
 
 }  // namespace vlgb

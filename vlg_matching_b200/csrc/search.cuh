@@ -82,7 +82,6 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     so.total_words = 0;
     if (P == 0 || n == 0) return;
 
-    const uint32_t npass = (P + SCAN_S - 1) / SCAN_S;
     const uint32_t chunk = scan_chunk_for(n, c.sm_count);
     const uint32_t rows = (uint32_t)((n + chunk - 1) / chunk);
     const uint32_t nrb = (rows + SCAN_RB - 1) / SCAN_RB;
@@ -101,32 +100,37 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     }
 
     struct PassDev {
-        uint32_t s_act, stride, has_short;
+        uint32_t first, s_act, stride, has_short;  // dictionary patterns [first, first + s_act)
         size_t o_tables, o_len, o_off, o_next, o_blob, o_base;  // inside the control blob
         uint32_t *gmatrix, *total;                 // stream path: [groups][stride] counts -> group cursors
         uint32_t *matrix = nullptr, *part = nullptr;  // legacy path: [rows][stride] counts -> row cursors, row-block sums
         uint32_t *stream = nullptr, *row_hits = nullptr, *overflow = nullptr;  // hit stream (if the budget allows one)
     };
-    std::vector<PassDev> pd(npass);
+    // passes: as many patterns each as fit the ids (SCAN_S) and the trie tables of one pass (build_pass decides)
+    std::vector<PassDev> pd;
     Packer ctl;
     std::unique_ptr<PassHost> ph(new PassHost());
     size_t work_bytes = 0;
-    for (uint32_t p = 0; p < npass; p++) {
-        uint32_t first = p * SCAN_S, cnt = std::min<uint32_t>(SCAN_S, P - first);
-        build_pass(dict, first, cnt, *ph);
-        pd[p].s_act = cnt;
-        pd[p].stride = (cnt + 31) & ~31u;
-        pd[p].has_short = ph->has_short;
-        pd[p].o_tables = ctl.put(&ph->tables, 1);
-        pd[p].o_len = ctl.put(ph->long_len);
-        pd[p].o_off = ctl.put(ph->long_off);
-        pd[p].o_next = ctl.put(ph->long_next);
+    for (uint32_t first = 0; first < P;) {
+        const uint32_t cnt = build_pass(dict, first, P - first, *ph);
+        PassDev d;
+        d.first = first;
+        d.s_act = cnt;
+        d.stride = (cnt + 31) & ~31u;
+        d.has_short = ph->has_short;
+        d.o_tables = ctl.put(&ph->tables, 1);
+        d.o_len = ctl.put(ph->long_len);
+        d.o_off = ctl.put(ph->long_off);
+        d.o_next = ctl.put(ph->long_next);
         ph->long_blob.append(16, '\0');
-        pd[p].o_blob = ctl.put(ph->long_blob.data(), ph->long_blob.size());
+        d.o_blob = ctl.put(ph->long_blob.data(), ph->long_blob.size());
         std::vector<uint64_t> zero(cnt, 0);
-        pd[p].o_base = ctl.put(zero);
-        work_bytes += Arena::padded((size_t)ngroups * pd[p].stride, 4) + Arena::padded(pd[p].stride, 4);
+        d.o_base = ctl.put(zero);
+        work_bytes += Arena::padded((size_t)ngroups * d.stride, 4) + Arena::padded(d.stride, 4);
+        pd.push_back(d);
+        first += cnt;
     }
+    const uint32_t npass = (uint32_t)pd.size();
     const size_t o_allbase = ctl.put(so.base);  // P+1 u64, filled later (owned kernel)
     work_bytes += 2 * Arena::padded(P, 4);      // owned[], totals[]
     // hit streams: stream_cap entries per row (2 per text position, else 1), for as many passes as the budget
@@ -193,10 +197,8 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.s_act = pd[p].s_act;
         a.s_stride = pd[p].stride;
         a.has_short = pd[p].has_short;
-        static const uint32_t al0[4] = {0xFFFFFFFFu, 0x00FF00FFu, 0x000000FFu, 0x000000FFu};
-        static const uint32_t al1[4] = {0xFFFFFFFFu, 0x00FF00FFu, 0x000000FFu, 0u};
-        a.align0 = al0[sym_shift];
-        a.align1 = al1[sym_shift];
+        static const uint32_t al[4] = {0xFFu, 0x55u, 0x11u, 0x01u};
+        a.align = al[sym_shift];
         a.tables = dev_at<const ScanTables>(d_ctl, pd[p].o_tables);
         a.long_len = dev_at<const uint32_t>(d_ctl, pd[p].o_len);
         a.long_off = dev_at<const uint32_t>(d_ctl, pd[p].o_off);
@@ -246,7 +248,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         } else {
             legacy_count(p, pd[p].matrix, pd[p].part, pd[p].total);
         }
-        d2h(c, so.tot.data() + p * SCAN_S, pd[p].total, pd[p].s_act * 4);
+        d2h(c, so.tot.data() + pd[p].first, pd[p].total, pd[p].s_act * 4);
         c.stats.d2h_bytes += pd[p].s_act * 4;
     }
     d2h(c, overflow.data(), d_overflow, (size_t)npass * 4);
@@ -265,7 +267,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     c.list_arena.reserve(words * 4 + 4096);
     so.d_lists = c.list_arena.take<uint32_t>(words + 16);
     for (uint32_t p = 0; p < npass; p++)
-        h2d(c, d_ctl + pd[p].o_base, so.base.data() + p * SCAN_S, pd[p].s_act * 8);
+        h2d(c, d_ctl + pd[p].o_base, so.base.data() + pd[p].first, pd[p].s_act * 8);
     h2d(c, d_ctl + o_allbase, so.base.data(), (P + 1) * 8);
     c.stats.h2d_bytes += (uint64_t)P * 16 + 8;
 
@@ -275,7 +277,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     c.stats.total_occurrences += occ;
     for (uint32_t p = 0; p < npass; p++) {
         uint64_t pocc = 0;
-        for (uint32_t i = 0; i < pd[p].s_act; i++) pocc += so.tot[p * SCAN_S + i];
+        for (uint32_t i = 0; i < pd[p].s_act; i++) pocc += so.tot[pd[p].first + i];
         if (!pocc) continue;
         ScanArgs a = args_for(p);
         a.out = so.d_lists;
