@@ -40,7 +40,6 @@
 #pragma once
 #include <algorithm>
 #include <string>
-#include <unordered_map>
 
 #include "common.cuh"
 #include "tma.cuh"
@@ -62,20 +61,23 @@ constexpr int SCAN_RB = 64;        // rows per row-block in the legacy count-mat
 constexpr uint32_t SCAN_MAX_CHUNK = 65280;  // positions per row: an item keeps its position in 16 bits
 static_assert(SCAN_S <= 2048, "pattern ids are 11 bits");
 
-// root entry: bit 31 valid, bit 30 ambiguous (several prefixes: resolve through the edge table), bits 13..22 the
-//             10 check bits of the prefix hash, bits 0..12 node id
-// edge entry: bit 31 valid, bits 13..24 the 12 check bits of the key hash, bits 0..12 child node id
+// All three tables are laid out so that a lookup is "multiply, shift, load, xor-and, compare":
+// root entry: bits 19..31 node id | bit 18 ambiguous (several prefixes share the entry: resolve through the edge
+//             table) | bits 8..17 the 10 check bits of the prefix hash | bits 0..7 zero (0xFF = empty, 0xAA = ambiguous:
+//             the hash has zeros there, so neither ever compares equal)
+// edge entry: bits 19..31 child node id | bits 7..18 the 12 check bits of the key hash | bits 0..6 zero (0x7F = empty)
 // node info : bits 0..10 pattern id, bit 11 a pattern ends here (depth 8: head of the chain of patterns that share
 //             these 8 bytes), bit 12 has children, bits 13..16 depth
-constexpr uint32_t ROOT_VALID = 0x80000000u, ROOT_AMB = 0x40000000u;
+// work item : bits 0..15 position - row start | bits 16..17 kind (0 node / prefix, 1 one-byte, 2 two-byte pattern)
+//             | bit 18 ambiguous prefix | bits 19..31 node id   -- (root entry & 0xFFFC0000) | position is an item,
+//             and so is (edge entry & 0xFFF80000) | position
+constexpr uint32_t ROOT_EMPTY = 0xFFu, ROOT_AMB = 0x400AAu, ROOT_AMB_BIT = 1u << 18, EDGE_EMPTY = 0x7Fu;
 constexpr uint32_t NODE_TERM = 1u << 11, NODE_CHILD = 1u << 12;
 // edge keys (25 bits): (node << 8 | byte) for real edges; pseudo keys for what the root table cannot resolve
 constexpr uint32_t KEY_SHORT1 = 1u << 21;  // | b0            -> node of the 1-byte pattern
 constexpr uint32_t KEY_SHORT2 = 1u << 22;  // | b0 | b1 << 8  -> node of the 2-byte pattern
 constexpr uint32_t KEY_PREFIX3 = 1u << 24; // | 24-bit prefix -> depth-3 node of an ambiguous prefix
-constexpr uint32_t KEY_MASK = (1u << 25) - 1u;
-// work item: bits 0..15 position - row start, bits 16..28 node id, bits 29..30 type
-constexpr uint32_t ITEM_NODE = 0, ITEM_PREFIX3 = 1, ITEM_SHORT1 = 2, ITEM_SHORT2 = 3;
+constexpr uint32_t ITEM_SHORT1 = 1u << 16, ITEM_SHORT2 = 2u << 16, ITEM_SPECIAL = 7u << 16;
 
 struct ScanTables {  // one pass; same layout on host, in global memory and in shared memory
     uint32_t root[SCAN_ROOT];
@@ -83,18 +85,19 @@ struct ScanTables {  // one pass; same layout on host, in global memory and in s
     uint32_t info[SCAN_NODES];
     uint32_t f2[SCAN_F2_WORDS];  // 2-byte patterns: bitmap over an 11-bit hash of the two bytes (candidates only)
     uint32_t f1[SCAN_F1_WORDS];  // 1-byte patterns: bitmap over the byte
-    uint32_t mul_root, mul_e1, mul_e2;  // odd multipliers of the three bijective hashes (the host re-seeds when the
-    uint32_t pad;                       // cuckoo placement does not settle)
+    // multipliers of the three bijective hashes, pre-shifted (the host re-seeds when the cuckoo placement does not settle)
+    uint32_t mul_root;  // odd << 8: (prefix24 * mul_root) has the 24-bit bijection in bits 8..31
+    uint32_t mul_e1;    // odd << 7: (key25 * mul_e)  has the 25-bit bijection in bits 7..31
+    uint32_t mul_e2;
+    uint32_t pad;
 };
 
-// root: (prefix24 << 8) * mul is (prefix24 * mul mod 2^24) << 8: slot = top 14 bits, check = the next 10
-__host__ __device__ inline uint32_t root_hash(uint32_t w, uint32_t mul) { return (w << 8) * mul; }
+// root: h = w * mul_root -- slot = top 14 bits, check = the next 10, low 8 bits zero (w's top byte falls out)
 __host__ __device__ inline uint32_t root_slot(uint32_t h) { return h >> 18; }
-__host__ __device__ inline uint32_t root_check(uint32_t h) { return (h >> 8) & 0x3FFu; }
-// edge: key * mul mod 2^25: slot = top 13 bits (inside one half of the table), check = low 12 bits
-__host__ __device__ inline uint32_t edge_hash(uint32_t key, uint32_t mul) { return (key * mul) & KEY_MASK; }
-__host__ __device__ inline uint32_t edge_slot(uint32_t h) { return h >> 12; }
-__host__ __device__ inline uint32_t edge_word(uint32_t h, uint32_t child) { return 0x80000000u | ((h & 0xFFFu) << 13) | child; }
+__host__ __device__ inline uint32_t root_word(uint32_t h, uint32_t node) { return (node << 19) | (h & 0x3FF00u); }
+// edge: h = key * mul_e -- slot = top 13 bits (inside one half of the table), check = the next 12, low 7 bits zero
+__host__ __device__ inline uint32_t edge_slot(uint32_t h) { return h >> 19; }
+__host__ __device__ inline uint32_t edge_word(uint32_t h, uint32_t child) { return (child << 19) | (h & 0x7FF80u); }
 __host__ __device__ inline uint32_t scan_h2(uint32_t w) { return ((w & 0xFFFFu) * 0x9E3779B1u) >> 21; }
 
 struct ScanArgs {
@@ -145,15 +148,44 @@ __device__ __forceinline__ uint32_t text_u32(const uint8_t* text, uint32_t p)
     return __funnelshift_r(__ldg(t32), __ldg(t32 + 1), (p & 3u) * 8u);
 }
 
-// two-choice lookup of a 25-bit key: child node id or NONE32
-__device__ __forceinline__ uint32_t edge_lookup(const ScanTables* T, uint32_t key)
+// two-choice lookup of a 25-bit key: the matching edge entry (child node in bits 19..31) or 0
+__device__ __forceinline__ uint32_t edge_lookup(const ScanTables* T, uint32_t key, uint32_t m1, uint32_t m2)
 {
-    const uint32_t h1 = edge_hash(key, T->mul_e1), h2 = edge_hash(key, T->mul_e2);
+    const uint32_t h1 = key * m1, h2 = key * m2;
     const uint32_t e1 = T->edge[edge_slot(h1)], e2 = T->edge[SCAN_EDGE / 2 + edge_slot(h2)];
-    uint32_t r = NONE32;
-    if ((e2 >> 13) == (0x40000u | (h2 & 0xFFFu))) r = e2 & 0x1FFFu;
-    if ((e1 >> 13) == (0x40000u | (h1 & 0xFFFu))) r = e1 & 0x1FFFu;
+    uint32_t r = 0;
+    if (((e2 ^ h2) & 0x7FFFFu) == 0u) r = e2;
+    if (((e1 ^ h1) & 0x7FFFFu) == 0u) r = e1;
     return r;
+}
+
+// what happens to the occurrences a round found: pid != NONE32 on the lanes that hold one, p = its position
+template <int MODE>
+__device__ __forceinline__ void scan_emit(const ScanArgs& a, uint32_t hits, uint32_t pid, uint32_t p, uint32_t rel, uint32_t* mrow,
+                                          uint32_t lane, uint32_t lt_mask, uint32_t* stream_row, uint32_t& nh)
+{
+    if (MODE == SCAN_STREAM) {
+        // bump the (group, pattern) count -- a shared-memory atomic, where the global reduction of the legacy pass
+        // costs ~1.2 cycles of the load/store pipe per LANE (tools/microbench) -- and append the hit to the row's
+        // stream at its place in lane order
+        const uint32_t at = nh + __popc(hits & lt_mask);
+        if (pid != NONE32) {
+            atomicAdd(mrow + pid, 1u);
+            if (at < a.stream_cap) stream_row[at] = rel | (pid << 16);
+        }
+        nh += __popc(hits);
+    } else if (MODE == SCAN_COUNT) {
+        if (pid != NONE32) atomicAdd(mrow + pid, 1u);  // fire-and-forget L2 reduction
+    } else {
+        // legacy pass 2: the matrix entry is the row's write cursor inside the list; rank among equal patterns of
+        // the round = lane order = position order
+        const uint32_t grp = __match_any_sync(0xffffffffu, pid);
+        const int leader = __ffs(grp) - 1;
+        uint32_t old = 0;
+        if (pid != NONE32 && (int)lane == leader) old = atomicAdd(mrow + pid, (uint32_t)__popc(grp));
+        old = __shfl_sync(0xffffffffu, old, leader);
+        if (pid != NONE32) a.out[__ldg(a.list_base + pid) + old + __popc(grp & lt_mask)] = p;
+    }
 }
 
 // One drain round: the first n (<= 32) queue items starting at qhead, one per lane, all lanes converged.
@@ -162,88 +194,67 @@ __device__ __forceinline__ uint32_t edge_lookup(const ScanTables* T, uint32_t ke
 //      the chain of patterns that share their 8 bytes: every member is verified against the text, one per emit round.
 //   B. one lookup per item: the child for the next text byte (node items with children), or the pseudo key of an
 //      ambiguous prefix / a short pattern.  Lanes that find a node append it to the queue as a new item.
+// `careful` (warp-uniform): the row ends within 8 bytes of the text's end, so occurrences are checked against it.
 // Returns the number of items appended.
-template <int MODE>
+template <int MODE, bool FULL>
 __device__ __forceinline__ uint32_t scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* q, uint32_t qhead, uint32_t n,
                                                      uint32_t qtail, uint32_t row_lo, uint32_t* mrow, uint32_t lane, uint32_t lt_mask,
-                                                     uint32_t* stream_row, uint32_t& nh)
+                                                     uint32_t* stream_row, uint32_t& nh, uint32_t m1, uint32_t m2, bool careful)
 {
-    const bool active = lane < n;
-    uint32_t e = 0, p = 0, type = 0, info = 0;
-    if (active) {
-        e = q[(qhead + lane) & (SCAN_QCAP - 1)];
-        p = row_lo + (e & 0xFFFFu);
-        type = e >> 29;
-        if (type == ITEM_NODE) info = T->info[(e >> 16) & 0x1FFFu];
-    }
+    const bool active = FULL || lane < n;
+    const uint32_t e = active ? q[(qhead + lane) & (SCAN_QCAP - 1)] : ITEM_SPECIAL;
+    const uint32_t rel = e & 0xFFFFu, p = row_lo + rel;
+    const bool special = (e & ITEM_SPECIAL) != 0u;
+    const uint32_t info = special ? 0u : T->info[e >> 19];
     const uint32_t depth = (info >> 13) & 15u;
     // ---- A. emit
-    uint32_t cand = (info & NODE_TERM) ? (info & 0x7FFu) : NONE32;
-    if (__any_sync(0xffffffffu, cand != NONE32)) {
-        for (;;) {
-            uint32_t pid = NONE32;
-            if (cand != NONE32) {
-                bool ok;
-                if (depth < 8) {
-                    ok = (uint64_t)p + depth <= a.valid_len;
-                    if (ok) pid = cand;
-                    cand = NONE32;
-                } else {
-                    // patterns of >= 8 bytes that share these 8 bytes: one candidate per emit round, hit or miss -- lanes
-                    // on the same node walk the same chain, so a pattern is emitted by all its lanes together and its
-                    // list stays sorted
-                    const uint32_t L = a.long_len[cand];
-                    ok = (uint64_t)p + L <= a.valid_len;
-                    if (ok) {
-                        const uint8_t* pat = a.long_blob + a.long_off[cand];
-                        const uint8_t* txt = a.text + p;
-                        for (uint32_t j = 8; j < L; j++)
-                            if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
+    const bool term = (info & NODE_TERM) != 0u;
+    const uint32_t terms = __ballot_sync(0xffffffffu, term);
+    if (terms) {
+        if (!careful && !__any_sync(0xffffffffu, term && depth >= 8u)) {
+            scan_emit<MODE>(a, terms, term ? (info & 0x7FFu) : NONE32, p, rel, mrow, lane, lt_mask, stream_row, nh);
+        } else {
+            uint32_t cand = term ? (info & 0x7FFu) : NONE32;
+            for (;;) {
+                uint32_t pid = NONE32;
+                if (cand != NONE32) {
+                    if (depth < 8u) {
+                        if ((uint64_t)p + depth <= a.valid_len) pid = cand;
+                        cand = NONE32;
+                    } else {
+                        // patterns of >= 8 bytes that share these 8 bytes: one candidate per emit round, hit or miss --
+                        // lanes on the same node walk the same chain, so a pattern is emitted by all its lanes
+                        // together and its list stays sorted
+                        const uint32_t L = a.long_len[cand];
+                        bool ok = (uint64_t)p + L <= a.valid_len;
+                        if (ok) {
+                            const uint8_t* pat = a.long_blob + a.long_off[cand];
+                            const uint8_t* txt = a.text + p;
+                            for (uint32_t j = 8; j < L; j++)
+                                if (__ldg(txt + j) != __ldg(pat + j)) { ok = false; break; }
+                        }
+                        if (ok) pid = cand;
+                        cand = a.long_next[cand];
                     }
-                    if (ok) pid = cand;
-                    cand = a.long_next[cand];
                 }
+                const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
+                if (hits) scan_emit<MODE>(a, hits, pid, p, rel, mrow, lane, lt_mask, stream_row, nh);
+                if (!__any_sync(0xffffffffu, cand != NONE32)) break;  // only depth-8 lanes can still have candidates
             }
-            const uint32_t hits = __ballot_sync(0xffffffffu, pid != NONE32);
-            if (hits) {
-                if (MODE == SCAN_STREAM) {
-                    // bump the (group, pattern) count -- a shared-memory atomic, where the global reduction of the legacy
-                    // pass costs ~1.2 cycles of the load/store pipe per LANE (tools/microbench) -- and append the hit to
-                    // the row's stream at its place in lane order
-                    if (pid != NONE32) atomicAdd(mrow + pid, 1u);
-                    const uint32_t at = nh + __popc(hits & lt_mask);
-                    if (pid != NONE32 && at < a.stream_cap) stream_row[at] = (p - row_lo) | (pid << 16);
-                    nh += __popc(hits);
-                } else if (MODE == SCAN_COUNT) {
-                    if (pid != NONE32) atomicAdd(mrow + pid, 1u);  // fire-and-forget L2 reduction
-                } else {
-                    // legacy pass 2: the matrix entry is the row's write cursor inside the list; rank among equal
-                    // patterns of the round = lane order = position order
-                    const uint32_t grp = __match_any_sync(0xffffffffu, pid);
-                    const int leader = __ffs(grp) - 1;
-                    uint32_t old = 0;
-                    if (pid != NONE32 && (int)lane == leader) old = atomicAdd(mrow + pid, (uint32_t)__popc(grp));
-                    old = __shfl_sync(0xffffffffu, old, leader);
-                    if (pid != NONE32) a.out[__ldg(a.list_base + pid) + old + __popc(grp & lt_mask)] = p;
-                }
-            }
-            if (!__any_sync(0xffffffffu, cand != NONE32)) break;  // only depth-8 lanes can still have candidates
         }
     }
     // ---- B. one lookup per item
-    uint32_t child = NONE32;
-    if (active && (type != ITEM_NODE || (info & NODE_CHILD))) {
-        uint32_t key;
-        if (type == ITEM_NODE) {
-            key = (((e >> 16) & 0x1FFFu) << 8) | __ldg(a.text + p + depth);
-        } else {
-            const uint32_t w = text_u32(a.text, p);
-            key = type == ITEM_PREFIX3 ? (KEY_PREFIX3 | (w & 0xFFFFFFu)) : type == ITEM_SHORT1 ? (KEY_SHORT1 | (w & 0xFFu)) : (KEY_SHORT2 | (w & 0xFFFFu));
-        }
-        child = edge_lookup(T, key);
+    uint32_t child = 0;
+    if (info & NODE_CHILD) {
+        const uint32_t key = ((e >> 11) & 0x1FFF00u) | __ldg(a.text + p + depth);
+        child = edge_lookup(T, key, m1, m2);
+    } else if (special && active) {  // rare kinds
+        const uint32_t w = text_u32(a.text, p);
+        const uint32_t key = (e & ROOT_AMB_BIT) ? (KEY_PREFIX3 | (w & 0xFFFFFFu)) : (e & ITEM_SHORT1) ? (KEY_SHORT1 | (w & 0xFFu)) : (KEY_SHORT2 | (w & 0xFFFFu));
+        child = edge_lookup(T, key, m1, m2);
     }
-    const uint32_t found = __ballot_sync(0xffffffffu, child != NONE32);
-    if (child != NONE32) q[(qtail + __popc(found & lt_mask)) & (SCAN_QCAP - 1)] = (e & 0xFFFFu) | (child << 16);
+    const uint32_t found = __ballot_sync(0xffffffffu, child != 0u);
+    if (child) q[(qtail + __popc(found & lt_mask)) & (SCAN_QCAP - 1)] = (child & 0xFFF80000u) | rel;
     __syncwarp();
     return __popc(found);
 }
@@ -282,21 +293,22 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 
     const uint32_t lo = live ? row * a.chunk : 0u;
     const uint32_t hi = live ? (uint32_t)min((uint64_t)lo + a.chunk, (uint64_t)a.valid_len) : 0u;  // 64-bit: lo + chunk may pass 2^32 in the last row
+    const bool careful = (uint64_t)hi + 8u > a.valid_len;  // an occurrence that starts in this row can reach past the text
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t mul_root = T->mul_root;
+    const uint32_t mul_root = T->mul_root, m1 = T->mul_e1, m2 = T->mul_e2;
     uint32_t qhead = 0, qcount = 0;  // warp-uniform
     uint32_t nh = 0;                 // occurrences recorded in the row's hit stream (stream pass)
     uint32_t* stream_row = (MODE == SCAN_STREAM && live) ? a.stream + (size_t)row * a.stream_cap : nullptr;
 
     auto drain_full_rounds = [&]() {
         while (qcount >= 32) {
-            const uint32_t added = scan_drain_round<MODE>(a, T, q, qhead, 32u, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh);
+            const uint32_t added = scan_drain_round<MODE, true>(a, T, q, qhead, 32u, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh, m1, m2, careful);
             qhead = (qhead + 32) & (SCAN_QCAP - 1);
             qcount += added - 32;
         }
     };
     // appends one item per set bit of `m` (bit j = position j of this lane) in (lane, j) = position order; item j is
-    // rel0 + j | hi[j].  At most SCAN_QCAP - 32 items go in at once: a denser step is taken in two halves (of the lanes).
+    // (rel0 + j) | hi[j].  At most SCAN_QCAP - 32 items go in at once: a denser step is taken in two halves (of the lanes).
     auto enqueue = [&](uint32_t m, uint32_t rel0, const uint32_t (&hi16)[SCAN_PPL]) {
         const uint32_t all = __popc(m);
         uint32_t incl = all;
@@ -337,16 +349,20 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
         }
     };
 
+    // the text is read one step ahead: a step's 8 bytes per lane are in flight while the previous step is matched
+    auto load8 = [&](uint32_t at) {
+        uint2 v = make_uint2(0u, 0u);
+        if (at < a.valid_len) v = __ldg(reinterpret_cast<const uint2*>(a.text + at));
+        return v;
+    };
+    uint2 own = load8(lo + 8 * lane);
     for (uint32_t base = lo; base < hi; base += SCAN_STEP) {
-        // ---- 16 bytes per lane: own 8 + the next lane's 8
         const uint32_t off = base + 8 * lane;
-        uint2 own = make_uint2(0u, 0u);
-        if (off < a.valid_len) own = __ldg(reinterpret_cast<const uint2*>(a.text + off));
+        const uint2 ahead = load8(off + SCAN_STEP);  // the next step (the row's last step: look-ahead bytes only)
+        // ---- 12 bytes per lane: own 8 + the next lane's first 4 (lane 31: the next step's first 4)
         uint32_t nx = __shfl_down_sync(0xffffffffu, own.x, 1);
-        if (lane == 31) {
-            nx = 0u;
-            if (base + SCAN_STEP < a.valid_len) nx = __ldg(reinterpret_cast<const uint32_t*>(a.text + base + SCAN_STEP));
-        }
+        const uint32_t nx31 = __shfl_sync(0xffffffffu, ahead.x, 0);
+        if (lane == 31) nx = nx31;
         uint32_t wl[SCAN_PPL];  // low 32 bits of the window at position j
         wl[0] = own.x;
         wl[1] = __funnelshift_r(own.x, own.y, 8);
@@ -363,41 +379,40 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
             const uint32_t left = off < hi ? min(hi - off, 8u) : 0u;
             okpos &= (1u << left) - 1u;
         }
-        // ---- root lookup: exact on the first three bytes
+        // ---- root lookup: exact on the first three bytes (the window's fourth byte falls out of the product)
         uint32_t m = 0, hi16[SCAN_PPL];
 #pragma unroll
         for (int j = 0; j < SCAN_PPL; j++) {
-            const uint32_t h = root_hash(wl[j], mul_root);
+            const uint32_t h = wl[j] * mul_root;
             const uint32_t v = T->root[root_slot(h)];
-            // valid entry with my check bits, or an ambiguous entry (its prefix is resolved through the edge table)
-            const bool hit = ((v >> 13) & 0x5FFFFu) == (0x40000u | root_check(h));
-            const bool amb = v >= (ROOT_VALID | ROOT_AMB);
-            hi16[j] = amb ? (ITEM_PREFIX3 << 29) : ((v & 0x1FFFu) << 16);
-            m |= (uint32_t)(hit || amb) << j;
+            if (((v ^ h) & 0x3FFFFu) == 0u) m |= 1u << j;   // a valid entry with my check bits
+            if (v & ROOT_AMB_BIT) m |= 1u << j;             // several prefixes share the entry: resolved through the edge table
+            hi16[j] = v & 0xFFFC0000u;
         }
         const uint32_t rel0 = off - lo;
         enqueue(m & okpos, rel0, hi16);
         if (SHORT) {
-            uint32_t m1 = 0, m2 = 0;
+            uint32_t mm1 = 0, mm2 = 0;
 #pragma unroll
             for (int j = 0; j < SCAN_PPL; j++) {
                 const uint32_t b0 = wl[j] & 0xFFu;
-                m1 |= ((T->f1[b0 >> 5] >> (b0 & 31)) & 1u) << j;
+                mm1 |= ((T->f1[b0 >> 5] >> (b0 & 31)) & 1u) << j;
                 const uint32_t i2 = scan_h2(wl[j]);
-                m2 |= ((T->f2[i2 >> 5] >> (i2 & 31)) & 1u) << j;
+                mm2 |= ((T->f2[i2 >> 5] >> (i2 & 31)) & 1u) << j;
             }
 #pragma unroll
-            for (int j = 0; j < SCAN_PPL; j++) hi16[j] = ITEM_SHORT1 << 29;
-            enqueue(m1 & okpos, rel0, hi16);
+            for (int j = 0; j < SCAN_PPL; j++) hi16[j] = ITEM_SHORT1;
+            enqueue(mm1 & okpos, rel0, hi16);
 #pragma unroll
-            for (int j = 0; j < SCAN_PPL; j++) hi16[j] = ITEM_SHORT2 << 29;
-            enqueue(m2 & okpos, rel0, hi16);
+            for (int j = 0; j < SCAN_PPL; j++) hi16[j] = ITEM_SHORT2;
+            enqueue(mm2 & okpos, rel0, hi16);
         }
+        own = ahead;
     }
     // the tail: rounds until the queue runs dry (a round can append what it finds)
     while (qcount) {
         const uint32_t n = min(qcount, 32u);
-        const uint32_t added = scan_drain_round<MODE>(a, T, q, qhead, n, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh);
+        const uint32_t added = scan_drain_round<MODE, false>(a, T, q, qhead, n, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh, m1, m2, careful);
         qhead = (qhead + n) & (SCAN_QCAP - 1);
         qcount += added - n;
     }
@@ -657,7 +672,7 @@ struct EdgeBuilder {
     }
     uint32_t home(uint32_t k, int which) const
     {
-        return which == 0 ? edge_slot(edge_hash(keys[k], m1)) : (uint32_t)(SCAN_EDGE / 2) + edge_slot(edge_hash(keys[k], m2));
+        return which == 0 ? edge_slot(keys[k] * m1) : (uint32_t)(SCAN_EDGE / 2) + edge_slot(keys[k] * m2);
     }
     bool place(uint32_t k)
     {
@@ -685,10 +700,12 @@ struct EdgeBuilder {
     void write(ScanTables& t) const
     {
         for (uint32_t s = 0; s < (uint32_t)SCAN_EDGE; s++) {
-            if (owner[s] < 0) continue;
+            if (owner[s] < 0) {
+                t.edge[s] = EDGE_EMPTY;
+                continue;
+            }
             const uint32_t k = (uint32_t)owner[s];
-            const uint32_t h = edge_hash(keys[k], s < (uint32_t)(SCAN_EDGE / 2) ? m1 : m2);
-            t.edge[s] = edge_word(h, childs[k]);
+            t.edge[s] = edge_word(keys[k] * (s < (uint32_t)(SCAN_EDGE / 2) ? m1 : m2), childs[k]);
         }
     }
 };
@@ -703,14 +720,42 @@ inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_co
     ph.long_next.clear();
     ph.long_blob.clear();
     ph.has_short = false;
-    std::vector<uint32_t> info;                       // per node
-    std::unordered_map<uint64_t, uint32_t> node_of;  // (kind, parent / prefix, byte) -> node id
+    std::vector<uint32_t> info;  // per node
+    info.reserve(SCAN_NODES);
+    // (kind, parent / prefix, byte) -> node id: open addressing in a table that is reused from pass to pass
+    struct NodeMap {
+        std::vector<uint64_t> key;  // key + 1, 0 = empty
+        std::vector<uint32_t> val;
+        std::vector<uint32_t> used;
+        NodeMap() : key(1u << 15, 0), val(1u << 15, 0) {}
+        void clear()
+        {
+            for (uint32_t i : used) key[i] = 0;
+            used.clear();
+        }
+        // slot of k: the entry if present, else the empty slot where it belongs
+        uint32_t slot(uint64_t k) const
+        {
+            uint32_t at = (uint32_t)((k * 0x9E3779B97F4A7C15ull) >> 49);
+            while (key[at] && key[at] != k + 1) at = (at + 1) & ((1u << 15) - 1u);
+            return at;
+        }
+        void put(uint32_t at, uint64_t k, uint32_t v)
+        {
+            key[at] = k + 1;
+            val[at] = v;
+            used.push_back(at);
+        }
+    };
+    static thread_local NodeMap node_of;
+    node_of.clear();
     std::vector<std::pair<uint32_t, uint32_t>> prefix3;  // (24-bit prefix, node) of every depth-3 node
     EdgeBuilder eb;
     auto new_node = [&](uint32_t depth) {
         info.push_back(depth << 13);
         return (uint32_t)info.size() - 1;
     };
+    new_node(0);  // node 0 is never a child: an all-zero edge entry means "not found"
     uint32_t count = 0;
     for (; count < max_count && count < (uint32_t)SCAN_S; count++) {
         const std::string& s = d.pats[first + count];
@@ -727,26 +772,27 @@ inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_co
             eb.childs.push_back(node);
         } else {
             const uint32_t p24 = b(0) | (b(1) << 8) | (b(2) << 16);
-            auto it = node_of.find((uint64_t)1 << 40 | p24);
-            if (it == node_of.end()) {
+            const uint64_t k3 = (uint64_t)1 << 40 | p24;
+            const uint32_t at3 = node_of.slot(k3);
+            if (!node_of.key[at3]) {
                 node = new_node(3);
-                node_of.emplace((uint64_t)1 << 40 | p24, node);
+                node_of.put(at3, k3, node);
                 prefix3.emplace_back(p24, node);
             } else {
-                node = it->second;
+                node = node_of.val[at3];
             }
             for (uint32_t dpt = 4; dpt <= std::min<uint32_t>(len, 8); dpt++) {
                 const uint32_t key = (node << 8) | b(dpt - 1);
-                auto ic = node_of.find((uint64_t)key);
-                if (ic == node_of.end()) {
+                const uint32_t atc = node_of.slot(key);
+                if (!node_of.key[atc]) {
                     const uint32_t child = new_node(dpt);
-                    node_of.emplace((uint64_t)key, child);
+                    node_of.put(atc, key, child);
                     eb.keys.push_back(key);
                     eb.childs.push_back(child);
                     info[node] |= NODE_CHILD;
                     node = child;
                 } else {
-                    node = ic->second;
+                    node = node_of.val[atc];
                 }
             }
         }
@@ -777,7 +823,7 @@ inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_co
         std::fill(fill.begin(), fill.end(), 0);
         uint32_t amb = 0;
         for (auto& pr : prefix3) {
-            uint16_t& f = fill[root_slot(root_hash(pr.first, mul))];
+            uint16_t& f = fill[root_slot(pr.first * (mul << 8))];
             if (f == 1) amb += 2; else if (f > 1) amb += 1;
             if (f < 3) f++;
         }
@@ -785,24 +831,23 @@ inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_co
         if (!amb) break;
     }
     memset(&ph.tables, 0, sizeof ph.tables);
-    ph.tables.mul_root = best_mul;
+    ph.tables.mul_root = best_mul << 8;
     std::fill(fill.begin(), fill.end(), 0);
     for (auto& pr : prefix3) {
-        uint16_t& f = fill[root_slot(root_hash(pr.first, best_mul))];
+        uint16_t& f = fill[root_slot(pr.first * ph.tables.mul_root)];
         if (f < 3) f++;
     }
-    const size_t real_edges = eb.keys.size();
+    for (uint32_t i = 0; i < (uint32_t)SCAN_ROOT; i++) ph.tables.root[i] = ROOT_EMPTY;
     for (auto& pr : prefix3) {
-        const uint32_t h = root_hash(pr.first, best_mul);
+        const uint32_t h = pr.first * ph.tables.mul_root;
         if (fill[root_slot(h)] == 1) {
-            ph.tables.root[root_slot(h)] = ROOT_VALID | (root_check(h) << 13) | pr.second;
+            ph.tables.root[root_slot(h)] = root_word(h, pr.second);
         } else {
-            ph.tables.root[root_slot(h)] = ROOT_VALID | ROOT_AMB;
+            ph.tables.root[root_slot(h)] = ROOT_AMB;
             eb.keys.push_back(KEY_PREFIX3 | pr.first);
             eb.childs.push_back(pr.second);
         }
     }
-    (void)real_edges;
     for (uint32_t i = 0; i < (uint32_t)info.size(); i++) ph.tables.info[i] = info[i];
     for (uint32_t i = 0; i < count; i++) {
         const std::string& s = d.pats[first + i];
@@ -816,7 +861,8 @@ inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_co
     }
     // ---- edge table
     for (uint32_t seed = 0;; seed++) {
-        const uint32_t m1 = (0x9E3779B1u + seed * 0x7F4A7C15u * 2u) | 1u, m2 = (0x85EBCA77u + seed * 0x3C6EF372u) | 1u;
+        // odd multipliers, pre-shifted by 7: key * m carries the 25-bit bijection in bits 7..31
+        const uint32_t m1 = ((0x9E3779B1u + seed * 0x7F4A7C15u * 2u) | 1u) << 7, m2 = ((0x85EBCA77u + seed * 0x3C6EF372u) | 1u) << 7;
         eb.reset(m1, m2);
         if (eb.settle()) {
             ph.tables.mul_e1 = m1;
