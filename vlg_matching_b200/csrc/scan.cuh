@@ -108,6 +108,7 @@ struct ScanArgs {
     uint32_t s_act;          // patterns in this pass
     uint32_t s_stride;       // row stride of the count matrix (multiple of 32)
     uint32_t has_short;      // the pass holds 1- or 2-byte patterns
+    uint32_t has_long;       // the pass holds patterns of 8 bytes and more
     uint32_t align;          // bit j set = position j of a lane's eight is symbol-aligned (all ones for byte texts;
                              // W-byte symbols start at multiples of W)
     const ScanTables* tables;
@@ -194,12 +195,12 @@ __device__ __forceinline__ void scan_emit(const ScanArgs& a, uint32_t hits, uint
 //      the chain of patterns that share their 8 bytes: every member is verified against the text, one per emit round.
 //   B. one lookup per item: the child for the next text byte (node items with children), or the pseudo key of an
 //      ambiguous prefix / a short pattern.  Lanes that find a node append it to the queue as a new item.
-// `careful` (warp-uniform): the row ends within 8 bytes of the text's end, so occurrences are checked against it.
-// Returns the number of items appended.
+// `slow` (warp-uniform, fixed for the row): the row ends within 8 bytes of the text's end, so occurrences are checked
+// against it, or the pass holds patterns of 8 bytes and more (chains to verify).  Returns the number of items appended.
 template <int MODE, bool FULL>
 __device__ __forceinline__ uint32_t scan_drain_round(const ScanArgs& a, const ScanTables* T, uint32_t* q, uint32_t qhead, uint32_t n,
                                                      uint32_t qtail, uint32_t row_lo, uint32_t* mrow, uint32_t lane, uint32_t lt_mask,
-                                                     uint32_t* stream_row, uint32_t& nh, uint32_t m1, uint32_t m2, bool careful)
+                                                     uint32_t* stream_row, uint32_t& nh, uint32_t m1, uint32_t m2, bool slow)
 {
     const bool active = FULL || lane < n;
     const uint32_t e = active ? q[(qhead + lane) & (SCAN_QCAP - 1)] : ITEM_SPECIAL;
@@ -211,7 +212,7 @@ __device__ __forceinline__ uint32_t scan_drain_round(const ScanArgs& a, const Sc
     const bool term = (info & NODE_TERM) != 0u;
     const uint32_t terms = __ballot_sync(0xffffffffu, term);
     if (terms) {
-        if (!careful && !__any_sync(0xffffffffu, term && depth >= 8u)) {
+        if (!slow) {
             scan_emit<MODE>(a, terms, term ? (info & 0x7FFu) : NONE32, p, rel, mrow, lane, lt_mask, stream_row, nh);
         } else {
             uint32_t cand = term ? (info & 0x7FFu) : NONE32;
@@ -243,14 +244,13 @@ __device__ __forceinline__ uint32_t scan_drain_round(const ScanArgs& a, const Sc
             }
         }
     }
-    // ---- B. one lookup per item
+    // ---- B. one lookup per item: node items look for the child under the next text byte; the rare kinds (ambiguous
+    // prefix, short pattern) look their first bytes up under a pseudo key -- one code path, the key is selected
     uint32_t child = 0;
-    if (info & NODE_CHILD) {
-        const uint32_t key = ((e >> 11) & 0x1FFF00u) | __ldg(a.text + p + depth);
-        child = edge_lookup(T, key, m1, m2);
-    } else if (special && active) {  // rare kinds
-        const uint32_t w = text_u32(a.text, p);
-        const uint32_t key = (e & ROOT_AMB_BIT) ? (KEY_PREFIX3 | (w & 0xFFFFFFu)) : (e & ITEM_SHORT1) ? (KEY_SHORT1 | (w & 0xFFu)) : (KEY_SHORT2 | (w & 0xFFFFu));
+    if ((info & NODE_CHILD) || (special && active)) {
+        const uint32_t w = text_u32(a.text, p + depth);  // depth = 0 for the rare kinds
+        uint32_t key = ((e >> 11) & 0x1FFF00u) | (w & 0xFFu);
+        if (special) key = (e & ROOT_AMB_BIT) ? (KEY_PREFIX3 | (w & 0xFFFFFFu)) : (e & ITEM_SHORT1) ? (KEY_SHORT1 | (w & 0xFFu)) : (KEY_SHORT2 | (w & 0xFFFFu));
         child = edge_lookup(T, key, m1, m2);
     }
     const uint32_t found = __ballot_sync(0xffffffffu, child != 0u);
@@ -293,7 +293,9 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 
     const uint32_t lo = live ? row * a.chunk : 0u;
     const uint32_t hi = live ? (uint32_t)min((uint64_t)lo + a.chunk, (uint64_t)a.valid_len) : 0u;  // 64-bit: lo + chunk may pass 2^32 in the last row
-    const bool careful = (uint64_t)hi + 8u > a.valid_len;  // an occurrence that starts in this row can reach past the text
+    // occurrences need a second look when one that starts in this row can reach past the text, or when the pass holds
+    // patterns of 8 bytes and more (their chains are verified byte by byte)
+    const bool slow = (uint64_t)hi + 8u > a.valid_len || a.has_long != 0u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t mul_root = T->mul_root, m1 = T->mul_e1, m2 = T->mul_e2;
     uint32_t qhead = 0, qcount = 0;  // warp-uniform
@@ -302,7 +304,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 
     auto drain_full_rounds = [&]() {
         while (qcount >= 32) {
-            const uint32_t added = scan_drain_round<MODE, true>(a, T, q, qhead, 32u, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh, m1, m2, careful);
+            const uint32_t added = scan_drain_round<MODE, true>(a, T, q, qhead, 32u, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh, m1, m2, slow);
             qhead = (qhead + 32) & (SCAN_QCAP - 1);
             qcount += added - 32;
         }
@@ -412,7 +414,7 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
     // the tail: rounds until the queue runs dry (a round can append what it finds)
     while (qcount) {
         const uint32_t n = min(qcount, 32u);
-        const uint32_t added = scan_drain_round<MODE, false>(a, T, q, qhead, n, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh, m1, m2, careful);
+        const uint32_t added = scan_drain_round<MODE, false>(a, T, q, qhead, n, qhead + qcount, lo, mrow, lane, lt_mask, stream_row, nh, m1, m2, slow);
         qhead = (qhead + n) & (SCAN_QCAP - 1);
         qcount += added - n;
     }
@@ -539,6 +541,32 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
     }
 }
 
+// gm[g][pid] (occurrences of pid in row group g) -> exclusive prefix over the groups (in place) = the group's write
+// cursor inside list pid; total[pid] = list length.  32 consecutive patterns x 32 segments of groups per CTA: loads
+// are coalesced over the patterns, the segments are scanned in shared memory.
+__global__ void __launch_bounds__(1024) scan_groupbase_kernel(uint32_t* gm, uint32_t ngroups, uint32_t stride, uint32_t* total)
+{
+    __shared__ uint32_t seg_sum[32][33];
+    const uint32_t pid = blockIdx.x * 32 + threadIdx.x, seg = threadIdx.y;
+    const uint32_t per = (ngroups + 31) / 32;
+    const uint32_t g0 = min(ngroups, seg * per), g1 = min(ngroups, g0 + per);
+    uint32_t s = 0;
+    if (pid < stride)
+        for (uint32_t g = g0; g < g1; g++) s += gm[(size_t)g * stride + pid];
+    seg_sum[seg][threadIdx.x] = s;
+    __syncthreads();
+    uint32_t run = 0;
+    for (uint32_t k = 0; k < seg; k++) run += seg_sum[k][threadIdx.x];
+    if (pid < stride) {
+        for (uint32_t g = g0; g < g1; g++) {
+            const uint32_t v = gm[(size_t)g * stride + pid];
+            gm[(size_t)g * stride + pid] = run;
+            run += v;
+        }
+        if (seg == 31) total[pid] = run;
+    }
+}
+
 // ---- count-matrix column scans -----------------------------------------------------------------
 // part[rb][pid] = sum of matrix[r][pid] over the rows of row-block rb
 __global__ void scan_colsum_kernel(const uint32_t* matrix, uint32_t rows, uint32_t stride, uint32_t* part)
@@ -655,7 +683,7 @@ struct PassHost {
     std::vector<uint32_t> long_len, long_off, long_next;
     std::string long_blob;
     uint32_t first = 0, count = 0;  // patterns [first, first+count) of the dictionary
-    bool has_short = false;
+    bool has_short = false, has_long = false;
 };
 
 // two-choice placement of (key -> child) in the edge table, moving earlier entries to their other home when both
@@ -719,7 +747,7 @@ inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_co
     ph.long_off.clear();
     ph.long_next.clear();
     ph.long_blob.clear();
-    ph.has_short = false;
+    ph.has_short = ph.has_long = false;
     std::vector<uint32_t> info;  // per node
     info.reserve(SCAN_NODES);
     // (kind, parent / prefix, byte) -> node id: open addressing in a table that is reused from pass to pass
@@ -800,6 +828,7 @@ inline uint32_t build_pass(const PatternDict& d, uint32_t first, uint32_t max_co
         ph.long_off.push_back(0);
         ph.long_next.push_back(NONE32);
         if (len >= 8) {
+            ph.has_long = true;
             ph.long_len[count] = len;
             ph.long_off[count] = (uint32_t)ph.long_blob.size();
             ph.long_blob += s;

@@ -100,7 +100,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     }
 
     struct PassDev {
-        uint32_t first, s_act, stride, has_short;  // dictionary patterns [first, first + s_act)
+        uint32_t first, s_act, stride, has_short, has_long;  // dictionary patterns [first, first + s_act)
         size_t o_tables, o_len, o_off, o_next, o_blob, o_base;  // inside the control blob
         uint32_t *gmatrix, *total;                 // stream path: [groups][stride] counts -> group cursors
         uint32_t *matrix = nullptr, *part = nullptr;  // legacy path: [rows][stride] counts -> row cursors, row-block sums
@@ -118,6 +118,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         d.s_act = cnt;
         d.stride = (cnt + 31) & ~31u;
         d.has_short = ph->has_short;
+        d.has_long = ph->has_long;
         d.o_tables = ctl.put(&ph->tables, 1);
         d.o_len = ctl.put(ph->long_len);
         d.o_off = ctl.put(ph->long_off);
@@ -197,6 +198,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.s_act = pd[p].s_act;
         a.s_stride = pd[p].stride;
         a.has_short = pd[p].has_short;
+        a.has_long = pd[p].has_long;
         static const uint32_t al[4] = {0xFFu, 0x55u, 0x11u, 0x01u};
         a.align = al[sym_shift];
         a.tables = dev_at<const ScanTables>(d_ctl, pd[p].o_tables);
@@ -243,7 +245,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
             c.end(ST_SCAN_COUNT, 1, n);  // n read + 4 B per occurrence (added below once the counts are known)
             c.begin(ST_SCAN_OFFSETS);
             // group counts -> exclusive prefix over the groups (in place) = every group's cursor; totals = list lengths
-            scan_colbase_kernel<<<(pd[p].stride + 127) / 128, 128, 0, c.stream>>>(pd[p].gmatrix, ngroups, pd[p].stride, pd[p].total);
+            scan_groupbase_kernel<<<(pd[p].stride + 31) / 32, dim3(32, 32), 0, c.stream>>>(pd[p].gmatrix, ngroups, pd[p].stride, pd[p].total);
             c.end(ST_SCAN_OFFSETS, 1, (uint64_t)ngroups * pd[p].stride * 8);
         } else {
             legacy_count(p, pd[p].matrix, pd[p].part, pd[p].total);
