@@ -106,31 +106,55 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         uint32_t *matrix = nullptr, *part = nullptr;  // legacy path: [rows][stride] counts -> row cursors, row-block sums
         uint32_t *stream = nullptr, *row_hits = nullptr, *overflow = nullptr;  // hit stream (if the budget allows one)
     };
-    // passes: as many patterns each as fit the ids (SCAN_S) and the trie tables of one pass (build_pass decides)
+    // passes: as many patterns each as fit the ids (SCAN_S) and the trie tables of one pass (build_pass decides).
+    // The tables of the last dictionary are kept (per thread): a caller that searches the same pattern set again (the
+    // same batch on the next shard of a sharded search, a repeated query file) skips the host build; the comparison
+    // is on the pattern bytes themselves, not on a hash.
+    struct TableCache {
+        std::string key;  // lengths + bytes of every pattern of the dictionary it was built for
+        std::vector<PassDev> pd;
+        std::vector<uint8_t> ctl;
+    };
+    static thread_local TableCache cache;
+    std::string key;
+    key.reserve(P * 12);
+    for (uint32_t i = 0; i < P; i++) {
+        const uint32_t l = (uint32_t)dict.pats[i].size();
+        key.append(reinterpret_cast<const char*>(&l), 4);
+        key += dict.pats[i];
+    }
     std::vector<PassDev> pd;
     Packer ctl;
-    std::unique_ptr<PassHost> ph(new PassHost());
     size_t work_bytes = 0;
-    for (uint32_t first = 0; first < P;) {
-        const uint32_t cnt = build_pass(dict, first, P - first, *ph);
-        PassDev d;
-        d.first = first;
-        d.s_act = cnt;
-        d.stride = (cnt + 31) & ~31u;
-        d.has_short = ph->has_short;
-        d.has_long = ph->has_long;
-        d.o_tables = ctl.put(&ph->tables, 1);
-        d.o_len = ctl.put(ph->long_len);
-        d.o_off = ctl.put(ph->long_off);
-        d.o_next = ctl.put(ph->long_next);
-        ph->long_blob.append(16, '\0');
-        d.o_blob = ctl.put(ph->long_blob.data(), ph->long_blob.size());
-        std::vector<uint64_t> zero(cnt, 0);
-        d.o_base = ctl.put(zero);
-        work_bytes += Arena::padded((size_t)ngroups * d.stride, 4) + Arena::padded(d.stride, 4);
-        pd.push_back(d);
-        first += cnt;
+    if (key == cache.key && !cache.pd.empty()) {
+        pd = cache.pd;
+        ctl.host = cache.ctl;
+    } else {
+        std::unique_ptr<PassHost> ph(new PassHost());
+        for (uint32_t first = 0; first < P;) {
+            const uint32_t cnt = build_pass(dict, first, P - first, *ph);
+            PassDev d;
+            d.first = first;
+            d.s_act = cnt;
+            d.stride = (cnt + 31) & ~31u;
+            d.has_short = ph->has_short;
+            d.has_long = ph->has_long;
+            d.o_tables = ctl.put(&ph->tables, 1);
+            d.o_len = ctl.put(ph->long_len);
+            d.o_off = ctl.put(ph->long_off);
+            d.o_next = ctl.put(ph->long_next);
+            ph->long_blob.append(16, '\0');
+            d.o_blob = ctl.put(ph->long_blob.data(), ph->long_blob.size());
+            std::vector<uint64_t> zero(cnt, 0);
+            d.o_base = ctl.put(zero);
+            pd.push_back(d);
+            first += cnt;
+        }
+        cache.key = key;
+        cache.pd = pd;
+        cache.ctl = ctl.host;
     }
+    for (const PassDev& d : pd) work_bytes += Arena::padded((size_t)ngroups * d.stride, 4) + Arena::padded(d.stride, 4);
     const uint32_t npass = (uint32_t)pd.size();
     const size_t o_allbase = ctl.put(so.base);  // P+1 u64, filled later (owned kernel)
     work_bytes += 2 * Arena::padded(P, 4);      // owned[], totals[]
@@ -926,9 +950,8 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
         S.chunk_tile0 = dev_at<const uint32_t>(d_ctl2, o_chunk_tile0);
         S.q_chunk0 = dev_at<const uint32_t>(d_ctl2, o_q_chunk0);
         c.begin(ST_SELECT_TILE);
-        sel_succ_kernel<<<ntiles * (SEL_TILE / 256), 256, 0, c.stream>>>(S);
-        sel_tile_kernel<<<(ntiles + MARK_WARPS - 1) / MARK_WARPS, MARK_WARPS * 32, 0, c.stream>>>(S);
-        c.end(ST_SELECT_TILE, 2, (uint64_t)sel_total * 20);
+        sel_succtile_kernel<<<ntiles, SELT_THREADS, 0, c.stream>>>(S);
+        c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 16);  // V_0 + tuple ends read, succ + exit written
         c.begin(ST_SELECT_WALK);
         VLGB_CUDA(cudaMemsetAsync(d_entry, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
         VLGB_CUDA(cudaMemsetAsync(d_spec, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));

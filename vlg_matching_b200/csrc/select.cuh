@@ -179,6 +179,90 @@ __global__ void __launch_bounds__(MARK_WARPS * 32) sel_tile_kernel(SelDesc s)
         if (base + i < len) s.exitp[slot0 + i] = ptr[i];
 }
 
+// succ[] and exitp[] of one tile in ONE kernel (replaces sel_succ_kernel + sel_tile_kernel: every viable start was
+// galloped for in global memory by its own thread, L2 hit rate 13 %, and the tile's succ values were read back).
+// E(x) is monotone in x and a match spans a few hundred bytes, so the successors of a tile's 1024 starts lie in the
+// tile itself or just behind it: the CTA stages V_0[base, base + SELT_WIN) in shared memory with coalesced loads and
+// every thread searches its 4 consecutive starts there (gallop from the previous answer); only a successor beyond the
+// window is searched in global memory.  Then the exits: every warp resolves its block of 128 slots from the right
+// (shuffle pointer jumping inside a segment of 32, as before), and a second step follows the at most 7 block exits.
+constexpr int SELT_THREADS = 256;
+constexpr int SELT_ITEMS = SEL_TILE / SELT_THREADS;  // consecutive slots per thread
+constexpr int SELT_WIN = 3 * SEL_TILE;               // staged elements of V_0
+constexpr int SELT_BLOCK = SEL_TILE / (SELT_THREADS / 32);  // slots per warp in the exit step
+static_assert(SELT_BLOCK % 32 == 0, "a warp's block is whole segments");
+
+__global__ void __launch_bounds__(SELT_THREADS) sel_succtile_kernel(SelDesc s)
+{
+    __shared__ uint32_t s_v[SELT_WIN];
+    __shared__ uint32_t s_ptr[SEL_TILE];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    const uint32_t q = sel_query_of_tile(s, slot0);
+    const uint32_t base = slot0 - s.sel_off[q];  // V_0 index of the tile's first element
+    const uint32_t len = s.v0_len[q];
+    if (base >= len) return;  // CTA-uniform
+    const uint32_t* v = s.v0[q];
+    const uint32_t* vl = s.vlast[q];
+    const uint32_t ll = s.last_len[q];
+    const uint32_t wn = min((uint32_t)SELT_WIN, len - base);
+    for (uint32_t i = tid; i < wn; i += SELT_THREADS) s_v[i] = __ldg(v + base + i);
+    const uint32_t rel0 = tid * SELT_ITEMS;
+    uint32_t last[SELT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SELT_ITEMS; i++) last[i] = (vl && base + rel0 + i < len) ? __ldg(vl + base + rel0 + i) : 0u;
+    __syncthreads();
+    const bool quirk = !vl && ll == (1u << s.sym_shift);  // k = 1, one symbol: sibling skip after an even position
+    const bool window_is_all = base + wn == len;          // the window reaches the end of V_0
+    uint32_t from = rel0 + 1;
+#pragma unroll
+    for (int i = 0; i < SELT_ITEMS; i++) {
+        const uint32_t rel = rel0 + i;
+        uint32_t sc = 0xFFFFFFF0u;
+        if (base + rel < len) {
+            const uint32_t x = s_v[rel];
+            uint64_t e = (uint64_t)(vl ? last[i] : x) + ll;
+            if (quirk && ((((uint64_t)x + s.global_offset) >> s.sym_shift) & 1ull) == 0) e = (uint64_t)x + (2u << s.sym_shift);
+            const uint32_t need = e > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)e;
+            from = max(from, rel + 1);
+            const uint32_t at = smem_gallop(s_v, from, wn, need);  // in [from, wn]
+            from = at;
+            if (at < wn || window_is_all) sc = base + at;
+            else sc = gallop_lower_bound(v, base + wn, len, e);    // beyond the window (dense V_0, long matches)
+        }
+        s_ptr[rel] = sc;
+        if (base + rel < len) s.succ[slot0 + rel] = sc;
+    }
+    __syncthreads();
+    // ---- exits, step 1: inside the warp's block, segments of 32 from the right
+    const uint32_t brel = warp * SELT_BLOCK;
+    for (int seg = SELT_BLOCK / 32 - 1; seg >= 0; seg--) {
+        const uint32_t segrel = brel + seg * 32;
+        uint32_t p = s_ptr[segrel + lane];
+#pragma unroll
+        for (int r = 0; r < 5; r++) {
+            const uint32_t rr = p - (base + segrel);
+            const uint32_t o = __shfl_sync(0xffffffffu, p, rr & 31);
+            if (rr < 32u) p = o;
+        }
+        const uint32_t rb = p - (base + brel);
+        if (rb < (uint32_t)SELT_BLOCK) p = s_ptr[brel + rb];  // a later segment of the block: final already
+        __syncwarp();
+        s_ptr[segrel + lane] = p;
+        __syncwarp();
+    }
+    __syncthreads();
+    // ---- step 2: from block exit to block exit until the orbit leaves the tile (at most 7 hops)
+#pragma unroll
+    for (int i = 0; i < SELT_ITEMS; i++) {
+        const uint32_t rel = tid + i * SELT_THREADS;  // coalesced stores
+        if (base + rel >= len) continue;
+        uint32_t p = s_ptr[rel];
+        while (p - base < (uint32_t)SEL_TILE) p = s_ptr[p - base];
+        s.exitp[slot0 + rel] = p;
+    }
+}
+
 __global__ void sel_spec_kernel(SelDesc s)
 {
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
