@@ -1008,7 +1008,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             co.d_starts = d_starts;
             co.d_tuples = d_tuples;
             c.begin(ST_EMIT);
-            sel_emit_kernel<<<ntiles, SEL_TILE, 0, c.stream>>>(S);
+            sel_emit_kernel<<<(ntiles + EMIT_WARPS - 1) / EMIT_WARPS, EMIT_WARPS * 32, 0, c.stream>>>(S);
             c.end(ST_EMIT, 1, co.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? co.tuple_words * 12 : 0));
             d2h(c, co.exit_cursor.data(), S.exit_cursor, (size_t)nq * 8);
             d2h(c, co.first_start.data(), S.first_start, (size_t)nq * 8);
@@ -1137,7 +1137,7 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     ro.d_starts = d_starts;
     ro.d_tuples = d_tuples;
     c.begin(ST_EMIT);
-    sel_emit_kernel<<<T.ntiles, SEL_TILE, 0, c.stream>>>(S);
+    sel_emit_kernel<<<(T.ntiles + EMIT_WARPS - 1) / EMIT_WARPS, EMIT_WARPS * 32, 0, c.stream>>>(S);
     c.end(ST_EMIT, 1, ro.matches * (4 + (want_starts ? 8 : 0)) + (want_tuples ? ro.tuple_words * 12 : 0));
     std::vector<uint64_t> ex(nq), fs(nq);
     d2h(c, ex.data(), S.exit_cursor, (size_t)nq * 8);

@@ -312,13 +312,15 @@ __global__ void sel_entry_kernel(SelDesc s)
     if (from != NONE32 && tile >= from) s.entry[tile] = s.spec[tile];
 }
 
-// One warp per tile: the tile's succ[] values are staged in shared memory (coalesced), lane 0 follows the orbit
-// of entry[tile] through them (a few hundred dependent shared-memory loads) and sets one bit per visited slot.
-// (Marking by pointer doubling with the whole CTA cost 4x the instructions and 20 block barriers per tile.)
+// One warp per entered tile: the tile's succ[] values are staged in shared memory (coalesced) and the orbit of
+// entry[tile] is marked segment by segment (32 slots = one flag word).  Inside a segment the orbit is the set reachable
+// from its first element under j(i) = succ(i): five rounds of "add the image of the set under j, square j" with one
+// warp-wide OR-reduction and one shuffle each; the successor of the segment's last orbit element enters the next
+// segment.  (Lane 0 walking the orbit alone -- one dependent shared-memory load per selected element, 3 of 32 lanes
+// active -- cost 110 M warp instructions, profiles/r02p.)
 __global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
 {
     __shared__ uint32_t s_succ[MARK_WARPS][SEL_TILE];
-    __shared__ uint32_t s_bits[MARK_WARPS][32];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tile = blockIdx.x * MARK_WARPS + warp;
     if (tile >= s.total_slots / SEL_TILE) return;
@@ -335,27 +337,29 @@ __global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
     uint32_t* sc = s_succ[warp];
 #pragma unroll 8
     for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32) sc[i] = base + i < len ? s.succ[slot0 + i] : 0xFFFFFFF0u;
-    s_bits[warp][lane] = 0u;
     __syncwarp();
-    uint32_t cnt = 0;
-    if (lane == 0) {
-        const uint32_t end = min((uint32_t)SEL_TILE, len - base);  // succ = len ("no successor") may fall inside the tile
-        uint32_t rel = e - base, word = rel >> 5, bits = 0;
-        while (rel < end) {
-            if ((rel >> 5) != word) {
-                s_bits[warp][word] = bits;
-                word = rel >> 5;
-                bits = 0;
-            }
-            bits |= 1u << (rel & 31);
-            cnt++;
-            rel = sc[rel] - base;  // a successor beyond the tile (or the list) wraps to a huge value
+    const uint32_t end = min((uint32_t)SEL_TILE, len - base);  // succ = len ("no successor") may fall inside the tile
+    uint32_t cur = e - base;  // warp-uniform: the orbit element that enters the next segment
+    uint32_t cnt = 0, my_bits = 0;
+    while (cur < end) {
+        const uint32_t w = cur >> 5, segbase = w * 32;
+        uint32_t j = sc[segbase + lane] - base - segbase;  // >= 32: the successor lies outside the segment (wraps to huge)
+        uint32_t R = 1u << (cur & 31);
+#pragma unroll
+        for (int r = 0; r < 5; r++) {
+            const uint32_t img = __reduce_or_sync(0xffffffffu, (((R >> lane) & 1u) && j < 32u) ? (1u << j) : 0u);
+            R |= img;
+            const uint32_t j2 = __shfl_sync(0xffffffffu, j, j & 31);
+            if (j < 32u) j = j2;
         }
-        s_bits[warp][word] = bits;
-        s.tile_count[tile] = cnt;
+        // "no successor" is index len, which may fall inside the segment: not an element
+        if (end - segbase < 32u) R &= (1u << (end - segbase)) - 1u;
+        if (lane == w) my_bits = R;
+        cnt += __popc(R);
+        cur = sc[segbase + 31 - __clz(R)] - base;  // successor of the segment's last orbit element
     }
-    __syncwarp();
-    s.flagbits[tile * 32 + lane] = s_bits[warp][lane];
+    s.flagbits[tile * 32 + lane] = my_bits;
+    if (lane == 0) s.tile_count[tile] = cnt;
 }
 
 // counts[q] = selected elements in the query's tiles
@@ -365,55 +369,70 @@ __global__ void sel_counts_kernel(SelDesc s)
     if (q < s.nq) s.counts[q] = (uint64_t)(s.tile_prefix[s.sel_off[q + 1] / SEL_TILE] - s.tile_prefix[s.sel_off[q] / SEL_TILE]);
 }
 
-__global__ void __launch_bounds__(SEL_TILE) sel_emit_kernel(SelDesc s)
+// One WARP per entered tile, one LANE per flag word (32 slots): the lane's rank is the tile's prefix plus a warp scan
+// over the words' popcounts, then every lane walks the set bits of its word.  (One thread per slot -- 1024-thread
+// CTAs, every warp redoing the scan, 29 % of the lanes with anything to write -- cost 92 M warp instructions for 7 M
+// matches, profiles/r02p.)  The tile's V_0 values are staged in shared memory with coalesced loads.
+constexpr int EMIT_WARPS = 8;
+__global__ void __launch_bounds__(EMIT_WARPS * 32) sel_emit_kernel(SelDesc s)
 {
-    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    __shared__ uint32_t s_x[EMIT_WARPS][SEL_TILE];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    // independent loads first (every thread reads the same few words: one L1 line each), then what depends on q
-    const uint32_t entered = s.entry[blockIdx.x];
+    const uint32_t tile = blockIdx.x * EMIT_WARPS + warp;
+    if (tile >= s.total_slots / SEL_TILE) return;
+    // independent loads first, then what depends on q
+    const uint32_t entered = s.entry[tile];
+    const uint32_t slot0 = tile * SEL_TILE;
     const uint32_t q = sel_query_of_tile(s, slot0);
-    const uint32_t wbits = s.flagbits[blockIdx.x * 32 + lane];  // lane l holds warp l's bits
-    const uint32_t tile_base = s.tile_prefix[blockIdx.x];
-    if (entered == NONE32) return;
+    uint32_t bits = s.flagbits[tile * 32 + lane];
+    const uint32_t tile_base = s.tile_prefix[tile];
+    if (entered == NONE32) return;  // warp-uniform
     const uint32_t off = s.sel_off[q], off_end = s.sel_off[q + 1];
     const uint32_t* v0 = s.v0[q];
-    const uint32_t slot = slot0 + threadIdx.x;
-    const uint32_t t = slot - off;
-    // rank of the element = matches of earlier tiles + of earlier warps of this tile + of earlier lanes
-    uint32_t inc = __popc(wbits);
+    const uint32_t len = s.v0_len[q];
+    const uint32_t tbase = slot0 - off;  // V_0 index of the tile's first slot
+    uint32_t* sx = s_x[warp];
+#pragma unroll 8
+    for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32) sx[i] = tbase + i < len ? __ldg(v0 + tbase + i) : 0u;
+    uint32_t inc = __popc(bits);
+    const uint32_t mine = inc;
 #pragma unroll
     for (int dd = 1; dd < 32; dd <<= 1) {
         const uint32_t up = __shfl_up_sync(0xffffffffu, inc, dd);
         if (lane >= (uint32_t)dd) inc += up;
     }
-    const uint32_t before = __shfl_sync(0xffffffffu, inc - __popc(wbits), warp);
-    const uint32_t bits = __shfl_sync(0xffffffffu, wbits, warp);
-    if (!((bits >> lane) & 1u)) return;
-    const uint32_t o = tile_base + before + __popc(bits & ((1u << lane) - 1u));
-    const uint32_t x = __ldg(v0 + t);
+    uint32_t o = tile_base + inc - mine;  // rank of the lane's first selected element among the chunk's matches
     const uint32_t qfirst = s.tile_prefix[off / SEL_TILE];
     const uint32_t qend = s.tile_prefix[off_end / SEL_TILE];
     const uint32_t k = s.kq[q];
     const uint64_t g = s.global_offset;
     const uint32_t sh = s.sym_shift;
-    if (s.starts) s.starts[o] = (g + x) >> sh;
-    if (o == qfirst) s.first_start[q] = (g + x) >> sh;
     const uint32_t* vl = s.vlast[q];
-    if (o + 1 == qend) {  // last match of the query: the cursor it leaves behind
-        const uint32_t ll = s.last_len[q];
-        uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
-        if (!vl && ll == (1u << sh) && ((((uint64_t)x + g) >> sh) & 1ull) == 0) e = (uint64_t)x + (2u << sh);
-        s.exit_cursor[q] = (g + e) >> sh;
-    }
-    if (s.tuples) {
-        uint64_t* out = s.tuples + s.tuple_off[q] + (uint64_t)(o - qfirst) * k;
-        out[0] = (g + x) >> sh;
-        uint32_t idx = t;
-        for (uint32_t d = k - 1, i = 1; d >= 1; d--, i++) {
-            idx = __ldg(s.depth_vnxt[d] + s.depth_vseg[d][q] + idx);
-            uint32_t pos = d > 1 ? __ldg(s.depth_vpos[d - 1] + s.depth_vseg[d - 1][q] + idx) : __ldg(s.last_list[q] + idx);
-            out[i] = (g + pos) >> sh;
+    __syncwarp();
+    while (bits) {
+        const uint32_t b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const uint32_t rel = lane * 32 + b, t = tbase + rel;
+        const uint32_t x = sx[rel];
+        if (s.starts) s.starts[o] = (g + x) >> sh;
+        if (o == qfirst) s.first_start[q] = (g + x) >> sh;
+        if (o + 1 == qend) {  // last match of the query: the cursor it leaves behind
+            const uint32_t ll = s.last_len[q];
+            uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
+            if (!vl && ll == (1u << sh) && ((((uint64_t)x + g) >> sh) & 1ull) == 0) e = (uint64_t)x + (2u << sh);
+            s.exit_cursor[q] = (g + e) >> sh;
         }
+        if (s.tuples) {
+            uint64_t* out = s.tuples + s.tuple_off[q] + (uint64_t)(o - qfirst) * k;
+            out[0] = (g + x) >> sh;
+            uint32_t idx = t;
+            for (uint32_t d = k - 1, i = 1; d >= 1; d--, i++) {
+                idx = __ldg(s.depth_vnxt[d] + s.depth_vseg[d][q] + idx);
+                uint32_t pos = d > 1 ? __ldg(s.depth_vpos[d - 1] + s.depth_vseg[d - 1][q] + idx) : __ldg(s.last_list[q] + idx);
+                out[i] = (g + pos) >> sh;
+            }
+        }
+        o++;
     }
 }
 
