@@ -444,18 +444,17 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 //   1. histogram: every warp counts its slice per pattern in its PRIVATE 16-bit counters (shared-memory atomics
 //      without return value; measured ~1 cycle of the load/store pipe per warp instruction, tools/microbench),
 //   2. the counters become exclusive prefixes over the slices; base[pid] advances by the block total,
-//   3. scatter: rank among equal patterns = atomic fetch-add on the private counter.  The hardware serialises the
-//      lanes of one instruction that hit the same counter, but in an order the ISA does not define, and positions
-//      must land in lane (= text) order.  So after the fetch-add every lane re-reads its counter: a lane whose counter
-//      moved by more than its own increment shares the pattern with other lanes of the round.  Those lanes raise a
-//      marker bit in the counter (that also tells the one lane of the group that saw a difference of exactly 1),
-//      and only they run MATCH.ANY to rank themselves in lane order -- MATCH costs ~2 cycles per DISTINCT value among
-//      the participating lanes, so it is kept to the few repeated (frequent) patterns of a round.
+//   3. scatter: rank among equal patterns = the private counter read BEFORE the round's increments (all lanes read,
+//      then all lanes add 1 with an atomic without return value, then all lanes read again).  A counter that moved by
+//      more than 1 is shared by several lanes of the round; the order in which the hardware serialises them is not
+//      defined by the ISA and positions must land in lane (= text) order, so only those lanes run MATCH.ANY and add
+//      the number of earlier lanes with the same pattern -- MATCH costs ~2 cycles per DISTINCT value among the
+//      participating lanes (tools/microbench), so it is kept to the few repeated (frequent) patterns of a round.
 constexpr int SCAT_WARPS = 16;
 constexpr int SCAT_ROUNDS = 16;
 constexpr int SCAT_BLOCK = SCAT_WARPS * 32 * SCAT_ROUNDS;  // hits per block: every counter stays below 2^15 (marker bit)
 constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * SCAN_S * sizeof(uint16_t) + (size_t)SCAN_S * sizeof(uint64_t);
-static_assert(SCAT_BLOCK < (1 << 15), "counter halves carry a marker in bit 15");
+static_assert(SCAT_BLOCK < (1 << 16), "16-bit counter halves");
 
 __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
 {
@@ -488,8 +487,8 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
             // slices start from zero (one thread per counter word, the same thread for all slices)
             for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
                 const uint32_t t = cnt32[(SCAT_WARPS - 1) * (SCAN_S / 2) + i];
-                base[2 * i] += t & 0x7FFFu;
-                base[2 * i + 1] += (t >> 16) & 0x7FFFu;
+                base[2 * i] += t & 0xFFFFu;
+                base[2 * i + 1] += t >> 16;
 #pragma unroll
                 for (int w = 0; w < SCAT_WARPS; w++) cnt32[w * (SCAN_S / 2) + i] = 0u;
             }
@@ -510,31 +509,21 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
                 }
             }
             __syncthreads();
-            // ---- 3. scatter: rank = fetch-add on the slice's counter, put into lane order where lanes share a pattern
+            // ---- 3. scatter: rank = the slice's counter before the round (+ the lanes of the round that hold the same
+            // pattern and come earlier)
 #pragma unroll
             for (int r = 0; r < SCAT_ROUNDS; r++) {
                 if (i0 + r * 32 >= i1) break;  // uniform
                 const bool valid = e[r] != NONE32;
                 const uint32_t pid = e[r] >> 16, w = (e[r] >> 17) & (SCAN_S / 2 - 1), sh = (e[r] >> 12) & 16u;
-                uint32_t rk = 0, now = 0;
-                if (valid) rk = (atomicAdd(&cur[w], 1u << sh) >> sh) & 0x7FFFu;
+                uint32_t rk = valid ? (vcur[w] >> sh) & 0xFFFFu : 0u;  // every lane reads before any lane adds
                 __syncwarp();
-                if (valid) now = (vcur[w] >> sh) & 0x7FFFu;
-                bool dup = valid && now - rk > 1u;
-                if (__any_sync(0xffffffffu, dup)) {
-                    if (dup) atomicOr(&cur[w], 0x8000u << sh);
-                    __syncwarp();
-                    const bool last = valid && !dup && ((vcur[w] >> sh) & 0x8000u);
-                    __syncwarp();
-                    if (dup) atomicAnd(&cur[w], ~(0x8000u << sh));
-                    dup |= last;
-                    const uint32_t m = __ballot_sync(0xffffffffu, dup);
-                    if (dup) {
-                        const uint32_t g = __match_any_sync(m, pid);
-                        rk = now - __popc(g) + __popc(g & lt_mask);
-                    }
-                    __syncwarp();
-                }
+                if (valid) atomicAdd(&cur[w], 1u << sh);
+                __syncwarp();
+                // a counter that moved by more than 1: other lanes of the round hold the same pattern
+                const bool dup = valid && ((vcur[w] >> sh) & 0xFFFFu) - rk > 1u;
+                const uint32_t m = __ballot_sync(0xffffffffu, dup);
+                if (dup) rk += __popc(__match_any_sync(m, pid) & lt_mask);
                 if (valid) a.out[base[pid] + rk] = lo + (e[r] & 0xFFFFu);
             }
         }

@@ -654,7 +654,6 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     const uint32_t sel_total_ub = (uint32_t)sel_run;
     const uint32_t ntiles_ub = sel_total_ub / SEL_TILE;
     const uint32_t nchunks_ub = ntiles_ub / SEL_CHUNK_TILES + nq;
-    std::vector<uint32_t> chunk_q, chunk_tile0, q_chunk0(nq);
 
     // ---- control blob
     Packer ctl;
@@ -697,7 +696,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     need += 2 * Arena::padded(sel_total_ub, 4) + Arena::padded((size_t)ntiles_ub * 32, 4);  // succ, exitp, flag bits
     need += 4 * Arena::padded(ntiles_ub + 2, 4);                                       // entry, spec, tile count / prefix
     need += 2 * Arena::padded(nchunks_ub + 1, 4);                                      // spec_exit, coalesce
-    const size_t ctl2_bytes = Arena::padded(nq + 1, 4) + Arena::padded(nq, 4) + 2 * Arena::padded(nchunks_ub, 4) + Arena::padded(ntiles_ub + 1, 4);
+    const size_t ctl2_bytes = 256 + Arena::padded(nq + 1, 4) + Arena::padded(nq, 4) + 2 * Arena::padded(nchunks_ub, 4) + Arena::padded(ntiles_ub + 1, 4);
     need += ctl2_bytes + 1024;                                                         // selection layout (second blob)
     need += Arena::padded(nq, 8) + Arena::padded(kmax + 1, 4);                         // counts, viable totals
     const size_t scratch_words = pfx_scratch_words(std::max<uint64_t>(std::max<uint64_t>(max_slots, max_rslots), sel_total_ub));
@@ -857,7 +856,7 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     // ---- selection
     SelDesc S;
     S.nq = nq;
-    S.total_slots = 0;     // layout fields are set once the V_0 sizes are known (below)
+    S.lay = nullptr;       // the layout fields are set below (built on the device once the V_0 sizes exist)
     S.sel_off = nullptr;
     S.tile_q = nullptr;
     S.kq = dev_at<const uint32_t>(d_ctl, o_kq);
@@ -883,7 +882,6 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     S.tile_count = d_tile_count;
     S.tile_prefix = d_tile_prefix;
     S.entry = d_entry;
-    S.nchunks = 0;
     S.chunk_q = S.chunk_tile0 = S.q_chunk0 = nullptr;
     S.spec = d_spec;
     S.spec_exit = d_spec_exit;
@@ -903,76 +901,60 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
     co.h_starts = co.h_tuples = nullptr;
     std::vector<uint32_t> viable(kmax + 1, 0);
 
-    // ---- V_0 of every query (sizes travel to the host: selection tiles are laid out over the viable starts
-    // only -- on the configs of BASELINE.json fewer than a sixth of the occurrences of P_1 are viable)
-    std::vector<uint32_t> v0_len(nq, 0);
+    // ---- V_0 of every query, then the selection layout -- tiles over the VIABLE starts only (on the configs of
+    // BASELINE.json fewer than a sixth of the occurrences of P_1 are viable) -- built on the device: persistent
+    // kernels read the tile / chunk counts from there, no size travels to the host between join and selection
+    uint32_t lay[3] = {0, 0, 0};  // slots, tiles, chunks (read back with the match counts)
     if (sel_total_ub) {
+        uint32_t* d_lay = reinterpret_cast<uint32_t*>(d_ctl2);
+        size_t o2 = 256;
+        S.lay = d_lay;
+        S.sel_off = dev_at<uint32_t>(d_ctl2, o2);
+        o2 += Arena::padded(nq + 1, 4);
+        S.q_chunk0 = dev_at<uint32_t>(d_ctl2, o2);
+        o2 += Arena::padded(nq, 4);
+        S.chunk_q = dev_at<uint32_t>(d_ctl2, o2);
+        o2 += Arena::padded(nchunks_ub, 4);
+        S.chunk_tile0 = dev_at<uint32_t>(d_ctl2, o2);
+        o2 += Arena::padded(nchunks_ub, 4);
+        S.tile_q = dev_at<uint32_t>(d_ctl2, o2);
+        // persistent kernels: CTAs that take tiles in turn.  Four waves' worth: tiles differ in cost (a dense V_0 gallops
+        // beyond the staged window), finer turns balance better than exactly one resident wave (measured)
+        const uint32_t pgrid = (uint32_t)c.sm_count * 32u;
         c.begin(ST_SELECT_SUCC);
         sel_resolve_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
-        c.end(ST_SELECT_SUCC, 1, (uint64_t)nq * 32);
-        d2h(c, v0_len.data(), d_v0_len, (size_t)nq * 4);
-        VLGB_CUDA(cudaGetLastError());
-        trace().mark("chunk: join launched");
-        sync_stream(c);  // sync: viable-start counts
-        trace().mark("chunk: sync viable");
-        c.stats.d2h_bytes += (uint64_t)nq * 4;
-    }
-    sel_run = 0;
-    for (uint32_t s = 0; s < nq; s++) {
-        sel_off[s] = (uint32_t)sel_run;
-        sel_run += ((uint64_t)v0_len[s] + SEL_TILE - 1) / SEL_TILE * SEL_TILE;
-    }
-    sel_off[nq] = (uint32_t)sel_run;
-    const uint32_t sel_total = (uint32_t)sel_run;
-    const uint32_t ntiles = sel_total / SEL_TILE;
-    std::vector<uint32_t> tile_q(ntiles + 1, 0);
-    for (uint32_t s = 0; s < nq; s++) {
-        q_chunk0[s] = (uint32_t)chunk_q.size();
-        const uint32_t t0 = sel_off[s] / SEL_TILE, t1 = sel_off[s + 1] / SEL_TILE;
-        for (uint32_t t = t0; t < t1; t++) tile_q[t] = s;
-        for (uint32_t t = t0; t < t1; t += SEL_CHUNK_TILES) {
-            chunk_q.push_back(s);
-            chunk_tile0.push_back(t);
-        }
-    }
-    const uint32_t nchunks = (uint32_t)chunk_q.size();
-    if (sel_total) {
-        Packer ctl2;
-        const size_t o_sel_off = ctl2.put(sel_off), o_q_chunk0 = ctl2.put(q_chunk0), o_chunk_q = ctl2.put(chunk_q),
-                     o_chunk_tile0 = ctl2.put(chunk_tile0), o_tile_q = ctl2.put(tile_q);
-        h2d(c, d_ctl2, ctl2.host.data(), ctl2.host.size());
-        c.stats.h2d_bytes += ctl2.host.size();
-        S.total_slots = sel_total;
-        S.sel_off = dev_at<const uint32_t>(d_ctl2, o_sel_off);
-        S.tile_q = dev_at<const uint32_t>(d_ctl2, o_tile_q);
-        S.nchunks = nchunks;
-        S.chunk_q = dev_at<const uint32_t>(d_ctl2, o_chunk_q);
-        S.chunk_tile0 = dev_at<const uint32_t>(d_ctl2, o_chunk_tile0);
-        S.q_chunk0 = dev_at<const uint32_t>(d_ctl2, o_q_chunk0);
+        sel_layout_kernel<<<1, 1024, 0, c.stream>>>(S, d_lay);
+        sel_fill_kernel<<<std::min<uint32_t>((ntiles_ub + 255) / 256, pgrid), 256, 0, c.stream>>>(S);
+        c.end(ST_SELECT_SUCC, 3, (uint64_t)nq * 48);
         c.begin(ST_SELECT_TILE);
-        sel_succtile_kernel<<<ntiles, SELT_THREADS, 0, c.stream>>>(S);
-        c.end(ST_SELECT_TILE, 1, (uint64_t)sel_total * 16);  // V_0 + tuple ends read, succ + exit written
+        sel_succtile_kernel<<<std::min<uint32_t>(ntiles_ub, pgrid), SELT_THREADS, 0, c.stream>>>(S);
+        c.end(ST_SELECT_TILE, 1, 0);  // 16 B per slot (V_0 + tuple ends read, succ + exit written), added below
         c.begin(ST_SELECT_WALK);
-        VLGB_CUDA(cudaMemsetAsync(d_entry, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
-        VLGB_CUDA(cudaMemsetAsync(d_spec, 0xFF, (size_t)(ntiles + 1) * 4, c.stream));
-        VLGB_CUDA(cudaMemsetAsync(d_coalesce, 0xFF, (size_t)(nchunks + 1) * 4, c.stream));
-        sel_spec_kernel<<<(nchunks + 31) / 32, 32, 0, c.stream>>>(S);
+        VLGB_CUDA(cudaMemsetAsync(d_entry, 0xFF, (size_t)(ntiles_ub + 1) * 4, c.stream));
+        VLGB_CUDA(cudaMemsetAsync(d_spec, 0xFF, (size_t)(ntiles_ub + 1) * 4, c.stream));
+        VLGB_CUDA(cudaMemsetAsync(d_coalesce, 0xFF, (size_t)(nchunks_ub + 1) * 4, c.stream));
+        VLGB_CUDA(cudaMemsetAsync(d_tile_count, 0, (size_t)(ntiles_ub + 2) * 4, c.stream));  // tiles beyond the real count stay 0
+        sel_spec_kernel<<<std::min<uint32_t>((nchunks_ub + 31) / 32, pgrid), 32, 0, c.stream>>>(S);
         sel_walk_kernel<<<(nq + 31) / 32, 32, 0, c.stream>>>(S);
-        sel_entry_kernel<<<(ntiles + 255) / 256, 256, 0, c.stream>>>(S);
-        sel_mark_kernel<<<(ntiles + MARK_WARPS - 1) / MARK_WARPS, MARK_WARPS * 32, 0, c.stream>>>(S);
-        c.end(ST_SELECT_WALK, 4, (uint64_t)sel_total * 5);
+        sel_entry_kernel<<<std::min<uint32_t>((ntiles_ub + 255) / 256, pgrid), 256, 0, c.stream>>>(S);
+        sel_mark_kernel<<<std::min<uint32_t>((ntiles_ub + MARK_WARPS - 1) / MARK_WARPS, pgrid), MARK_WARPS * 32, 0, c.stream>>>(S);
+        c.end(ST_SELECT_WALK, 4, 0);  // 5 B per slot, added below
         c.begin(ST_EMIT);
-        uint32_t l = exclusive_scan(ValueU32{d_tile_count}, ntiles, d_tile_prefix, scratch, c.stream);
+        uint32_t l = exclusive_scan(ValueU32{d_tile_count}, ntiles_ub, d_tile_prefix, scratch, c.stream);
         sel_counts_kernel<<<(nq + 127) / 128, 128, 0, c.stream>>>(S);
-        c.end(ST_EMIT, l + 1, (uint64_t)ntiles * 12);
+        c.end(ST_EMIT, l + 1, (uint64_t)ntiles_ub * 12);
         d2h(c, co.counts.data(), d_counts, (size_t)nq * 8);
+        d2h(c, lay, d_lay, sizeof lay);
         if (kmax > 1)
             d2h(c, viable.data(), d_viable, (size_t)(kmax + 1) * 4);
         VLGB_CUDA(cudaGetLastError());
-        trace().mark("chunk: select launched");
+        trace().mark("chunk: join + select launched");
         sync_stream(c);  // sync: match counts
         trace().mark("chunk: sync counts");
-        c.stats.d2h_bytes += (uint64_t)nq * 8 + (kmax + 1) * 4;
+        c.stats.d2h_bytes += (uint64_t)nq * 8 + (kmax + 1) * 4 + sizeof lay;
+        const uint32_t sel_total = lay[0], ntiles = lay[1];
+        c.stats.bytes[ST_SELECT_TILE] += (uint64_t)sel_total * 16;
+        c.stats.bytes[ST_SELECT_WALK] += (uint64_t)sel_total * 5;
         for (uint32_t d = 1; d < kmax; d++)  // viable slots written; deeper levels read the previous viable list
         {
             c.stats.bytes[ST_JOIN_PROBE] += (uint64_t)viable[d] * 12;

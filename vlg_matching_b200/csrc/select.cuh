@@ -36,9 +36,11 @@ constexpr int MARK_WARPS = 8;        // tiles per CTA of the warp-per-tile kerne
 
 struct SelDesc {
     uint32_t nq;                 // queries of the chunk
-    uint32_t total_slots;        // sel_off[nq], multiple of SEL_TILE
-    const uint32_t* sel_off;     // [nq+1], TILE-aligned prefix of the V_0 sizes
-    const uint32_t* tile_q;      // [total_slots / SEL_TILE] query of every tile
+    // the selection layout is built ON THE DEVICE from the V_0 sizes the join left there (sel_layout_kernel,
+    // sel_fill_kernel): no size travels to the host between join and selection
+    const uint32_t* lay;         // [3]: slots (= sel_off[nq], multiple of SEL_TILE), tiles, speculative chunks
+    uint32_t* sel_off;           // [nq+1], TILE-aligned prefix of the V_0 sizes
+    uint32_t* tile_q;            // [tiles] query of every tile
     const uint32_t* kq;          // subpatterns of each query
     const uint32_t* last_len;    // |P_k|
     const uint64_t* entry_local; // entry cursor relative to the shard start (saturated at 0)
@@ -67,10 +69,9 @@ struct SelDesc {
     const uint32_t* tile_prefix; // [tiles + 1] exclusive scan of tile_count
     uint32_t* entry;             // [total_slots / SEL_TILE]
     // speculative chunks (SEL_CHUNK_TILES tiles of one query each)
-    uint32_t nchunks;
-    const uint32_t* chunk_q;     // [nchunks] query of the chunk
-    const uint32_t* chunk_tile0; // [nchunks] first tile (global tile index)
-    const uint32_t* q_chunk0;    // [nq] first chunk of the query
+    uint32_t* chunk_q;           // [chunks] query of the chunk
+    uint32_t* chunk_tile0;       // [chunks] first tile (global tile index)
+    uint32_t* q_chunk0;          // [nq] first chunk of the query
     uint32_t* spec;              // [tiles] element the speculative hop entered the tile with (NONE32: not visited)
     uint32_t* spec_exit;         // [nchunks] where the speculative hop left the chunk
     uint32_t* coalesce;          // [nchunks] first tile from which the speculative entries are the true ones
@@ -82,6 +83,79 @@ struct SelDesc {
     uint64_t* first_start;       // [nq] whole-text position of the first reported match, pre-set to ~0
     uint64_t* counts;            // [nq]
 };
+
+// ---- selection layout on the device ----------------------------------------------------------------------------
+// Every query owns a TILE-aligned range of slots for its V_0 (so a tile never straddles two queries), cut into
+// speculative chunks of SEL_CHUNK_TILES tiles.  One CTA: exclusive scans of tiles and chunks per query.
+__global__ void __launch_bounds__(1024) sel_layout_kernel(SelDesc s, uint32_t* lay)
+{
+    __shared__ uint64_t wsum[32];
+    __shared__ uint64_t carry_s;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (uint32_t q0 = 0; q0 < s.nq; q0 += 1024) {
+        const uint32_t q = q0 + tid;
+        const uint32_t tiles = q < s.nq ? (s.v0_len[q] + SEL_TILE - 1) / SEL_TILE : 0u;
+        const uint32_t chunks = (tiles + SEL_CHUNK_TILES - 1) / SEL_CHUNK_TILES;
+        const uint64_t mine = ((uint64_t)tiles << 32) | chunks;  // both sums stay below 2^32
+        uint64_t inc = mine;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint64_t o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= (uint32_t)d) inc += o;
+        }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const uint64_t w = wsum[lane];
+            uint64_t winc = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint64_t o = __shfl_up_sync(0xffffffffu, winc, d);
+                if (lane >= (uint32_t)d) winc += o;
+            }
+            wsum[lane] = winc - w;
+        }
+        __syncthreads();
+        const uint64_t excl = carry_s + wsum[warp] + inc - mine;
+        if (q < s.nq) {
+            s.sel_off[q] = (uint32_t)(excl >> 32) * SEL_TILE;
+            s.q_chunk0[q] = (uint32_t)excl;
+        }
+        __syncthreads();
+        if (tid == 1023) carry_s = excl + mine;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const uint64_t all = carry_s;
+        s.sel_off[s.nq] = (uint32_t)(all >> 32) * SEL_TILE;
+        lay[0] = (uint32_t)(all >> 32) * SEL_TILE;
+        lay[1] = (uint32_t)(all >> 32);
+        lay[2] = (uint32_t)all;
+    }
+}
+
+// tile -> query map and the chunk tables
+__global__ void sel_fill_kernel(SelDesc s)
+{
+    const uint32_t ntiles = s.lay[1];
+    for (uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x; tile < ntiles; tile += gridDim.x * blockDim.x) {
+        const uint32_t slot = tile * SEL_TILE;
+        uint32_t lo = 0, hi = s.nq;  // last q with sel_off[q] <= slot (empty queries share their offset with the next one)
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if (s.sel_off[mid] <= slot) lo = mid; else hi = mid - 1;
+        }
+        s.tile_q[tile] = lo;
+        const uint32_t rel = tile - s.sel_off[lo] / SEL_TILE;
+        if (rel % SEL_CHUNK_TILES == 0) {
+            const uint32_t c = s.q_chunk0[lo] + rel / SEL_CHUNK_TILES;
+            s.chunk_q[c] = lo;
+            s.chunk_tile0[c] = tile;
+        }
+    }
+}
 
 __global__ void sel_resolve_kernel(SelDesc s)
 {
@@ -120,67 +194,9 @@ __device__ __forceinline__ uint32_t sel_hop(const uint32_t* ptr, uint32_t p, uin
     return rel < (uint32_t)SEL_TILE ? ptr[rel] : p;
 }
 
-// succ[slot] for every viable start of every query: one thread per slot, gallop from t + 1.
-__global__ void __launch_bounds__(256) sel_succ_kernel(SelDesc s)
-{
-    const uint32_t tile = blockIdx.x / (SEL_TILE / 256);
-    const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);  // same word for the whole CTA: one L1 line
-    const uint32_t slot = blockIdx.x * 256 + threadIdx.x;
-    const uint32_t t = slot - s.sel_off[q];  // V_0 index
-    const uint32_t len = s.v0_len[q];
-    if (t >= len) return;
-    const uint32_t* v = s.v0[q];
-    const uint32_t* vl = s.vlast[q];
-    const uint32_t x = __ldg(v + t);
-    const uint32_t ll = s.last_len[q];
-    uint64_t e = (uint64_t)(vl ? __ldg(vl + t) : x) + ll;
-    if (!vl && ll == (1u << s.sym_shift) && ((((uint64_t)x + s.global_offset) >> s.sym_shift) & 1ull) == 0)
-        e = (uint64_t)x + (2u << s.sym_shift);  // k = 1 sibling skip
-    s.succ[slot] = gallop_lower_bound(v, t + 1, len, e);
-}
-
-// exitp[slot] = first element of slot's orbit that lies outside its tile.  One warp per tile: the tile's succ
-// values are staged in shared memory and resolved segment by segment (32 slots) from the right: inside a
-// segment by pointer jumping through shuffles (succ(t) > t, so 5 rounds settle 32 slots), then one look-up
-// into the already final part to the right.  (Pointer doubling over the whole tile by a 1024-thread CTA took
-// 20 block barriers and three times the instructions.)
-__global__ void __launch_bounds__(MARK_WARPS * 32) sel_tile_kernel(SelDesc s)
-{
-    __shared__ uint32_t s_ptr[MARK_WARPS][SEL_TILE];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tile = blockIdx.x * MARK_WARPS + warp;
-    if (tile >= s.total_slots / SEL_TILE) return;
-    const uint32_t slot0 = tile * SEL_TILE;
-    const uint32_t q = sel_query_of_tile(s, slot0);
-    const uint32_t base = slot0 - s.sel_off[q];  // V_0 index of the tile's first element
-    const uint32_t len = s.v0_len[q];
-    if (base >= len) return;
-    uint32_t* ptr = s_ptr[warp];
-#pragma unroll 8
-    for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32) ptr[i] = base + i < len ? s.succ[slot0 + i] : 0xFFFFFFF0u;
-    __syncwarp();
-    for (int seg = SEL_TILE / 32 - 1; seg >= 0; seg--) {
-        const uint32_t segbase = base + seg * 32;
-        uint32_t p = ptr[seg * 32 + lane];
-#pragma unroll
-        for (int r = 0; r < 5; r++) {
-            const uint32_t rel = p - segbase;
-            const uint32_t o = __shfl_sync(0xffffffffu, p, rel & 31);
-            if (rel < 32u) p = o;
-        }
-        const uint32_t relt = p - base;
-        if (relt < (uint32_t)SEL_TILE) p = ptr[relt];  // a later segment: final already
-        __syncwarp();
-        ptr[seg * 32 + lane] = p;
-        __syncwarp();
-    }
-#pragma unroll 8
-    for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32)
-        if (base + i < len) s.exitp[slot0 + i] = ptr[i];
-}
-
-// succ[] and exitp[] of one tile in ONE kernel (replaces sel_succ_kernel + sel_tile_kernel: every viable start was
-// galloped for in global memory by its own thread, L2 hit rate 13 %, and the tile's succ values were read back).
+// succ[] and exitp[] of one tile in ONE kernel (before: one thread per viable start galloping in global memory, L2
+// hit rate 13 %, then a second kernel that read the tile's succ values back).  Persistent CTAs take tiles in turn:
+// the number of tiles is known on the device only.
 // E(x) is monotone in x and a match spans a few hundred bytes, so the successors of a tile's 1024 starts lie in the
 // tile itself or just behind it: the CTA stages V_0[base, base + SELT_WIN) in shared memory with coalesced loads and
 // every thread searches its 4 consecutive starts there (gallop from the previous answer); only a successor beyond the
@@ -197,11 +213,14 @@ __global__ void __launch_bounds__(SELT_THREADS) sel_succtile_kernel(SelDesc s)
     __shared__ uint32_t s_v[SELT_WIN];
     __shared__ uint32_t s_ptr[SEL_TILE];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t slot0 = blockIdx.x * SEL_TILE;
+    const uint32_t ntiles = s.lay[1];
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    __syncthreads();  // the previous tile's shared arrays are no longer in use
+    const uint32_t slot0 = tile * SEL_TILE;
     const uint32_t q = sel_query_of_tile(s, slot0);
     const uint32_t base = slot0 - s.sel_off[q];  // V_0 index of the tile's first element
     const uint32_t len = s.v0_len[q];
-    if (base >= len) return;  // CTA-uniform
+    if (base >= len) continue;  // CTA-uniform
     const uint32_t* v = s.v0[q];
     const uint32_t* vl = s.vlast[q];
     const uint32_t ll = s.last_len[q];
@@ -261,12 +280,13 @@ __global__ void __launch_bounds__(SELT_THREADS) sel_succtile_kernel(SelDesc s)
         while (p - base < (uint32_t)SEL_TILE) p = s_ptr[p - base];
         s.exitp[slot0 + rel] = p;
     }
+    }
 }
 
 __global__ void sel_spec_kernel(SelDesc s)
 {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= s.nchunks) return;
+    const uint32_t nchunks = s.lay[2];
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < nchunks; c += gridDim.x * blockDim.x) {
     const uint32_t q = s.chunk_q[c];
     const uint32_t off = s.sel_off[q];
     const uint32_t len = s.v0_len[q];
@@ -278,6 +298,7 @@ __global__ void sel_spec_kernel(SelDesc s)
         cur = s.exitp[off + cur];
     }
     s.spec_exit[c] = cur;
+    }
 }
 
 __global__ void sel_walk_kernel(SelDesc s)
@@ -304,12 +325,13 @@ __global__ void sel_walk_kernel(SelDesc s)
 
 __global__ void sel_entry_kernel(SelDesc s)
 {
-    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tile >= s.total_slots / SEL_TILE) return;
-    const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);
-    const uint32_t c = s.q_chunk0[q] + (tile - s.sel_off[q] / SEL_TILE) / SEL_CHUNK_TILES;
-    const uint32_t from = s.coalesce[c];
-    if (from != NONE32 && tile >= from) s.entry[tile] = s.spec[tile];
+    const uint32_t ntiles = s.lay[1];
+    for (uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x; tile < ntiles; tile += gridDim.x * blockDim.x) {
+        const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);
+        const uint32_t c = s.q_chunk0[q] + (tile - s.sel_off[q] / SEL_TILE) / SEL_CHUNK_TILES;
+        const uint32_t from = s.coalesce[c];
+        if (from != NONE32 && tile >= from) s.entry[tile] = s.spec[tile];
+    }
 }
 
 // One warp per entered tile: the tile's succ[] values are staged in shared memory (coalesced) and the orbit of
@@ -322,13 +344,14 @@ __global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
 {
     __shared__ uint32_t s_succ[MARK_WARPS][SEL_TILE];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tile = blockIdx.x * MARK_WARPS + warp;
-    if (tile >= s.total_slots / SEL_TILE) return;
+    const uint32_t ntiles = s.lay[1];
+    for (uint32_t tile = blockIdx.x * MARK_WARPS + warp; tile < ntiles; tile += gridDim.x * MARK_WARPS) {
+    __syncwarp();
     const uint32_t e = s.entry[tile];
     if (e == NONE32) {  // tile not entered: no selected element (the flag words stay meaningful for re-entry)
         if (lane == 0) s.tile_count[tile] = 0;
         s.flagbits[tile * 32 + lane] = 0u;
-        return;
+        continue;
     }
     const uint32_t slot0 = tile * SEL_TILE;
     const uint32_t q = sel_query_of_tile(s, slot0);
@@ -360,6 +383,7 @@ __global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
     }
     s.flagbits[tile * 32 + lane] = my_bits;
     if (lane == 0) s.tile_count[tile] = cnt;
+    }
 }
 
 // counts[q] = selected elements in the query's tiles
@@ -379,7 +403,7 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) sel_emit_kernel(SelDesc s)
     __shared__ uint32_t s_x[EMIT_WARPS][SEL_TILE];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tile = blockIdx.x * EMIT_WARPS + warp;
-    if (tile >= s.total_slots / SEL_TILE) return;
+    if (tile >= s.lay[1]) return;
     // independent loads first, then what depends on q
     const uint32_t entered = s.entry[tile];
     const uint32_t slot0 = tile * SEL_TILE;
@@ -475,7 +499,7 @@ __global__ void sel_refix_kernel(SelDesc s, RefixDesc r)
 __global__ void sel_recount_kernel(SelDesc s, const uint32_t* redo_flag)
 {
     const uint32_t tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (tile >= s.total_slots / SEL_TILE) return;
+    if (tile >= s.lay[1]) return;
     const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);
     uint32_t c = 0;
     if (redo_flag[q]) c = __popc(s.flagbits[tile * 32 + lane]);
