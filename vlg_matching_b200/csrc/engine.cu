@@ -1,6 +1,7 @@
 // engine.cu — libvlgb200.so: the C ABI of include/vlgb200.h on top of the sm_100a kernels
 // (scan.cuh -> join.cuh -> select.cuh, prefix.cuh).  No CPU fallback: every compute entry point needs
 // a CUDA device and fails with VLGB_ERR_CUDA otherwise.
+#include <atomic>
 #include <algorithm>
 #include <cstdlib>
 #include <memory>
@@ -688,38 +689,74 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
         if (want_tuples && !keep_device) R.tuples[q] = EMPTY_LIST;
     }
 
-    // ---- classify queries, collect the distinct subpatterns
+    // ---- classify queries, collect the distinct subpatterns.  The outcome depends on the batch and on the shard's
+    // geometry only, so it is kept (per thread) and reused when the very same batch comes again -- the next shard of
+    // a sharded search, a repeated query file: the comparison is on the batch's bytes, not on a hash.
     const uint64_t halo = idx->n - idx->owned_len;
     const bool halo_truncated_by_shard = idx->global_offset + idx->n < idx->total_len;
-    PatternDict dict;
-    std::vector<uint32_t> sub_pid(ns, NONE32);
-    std::vector<PlanQuery> plan;
-    for (uint32_t q = 0; q < nq; q++) {
-        uint32_t s0 = batch->sub_off[q], s1 = batch->sub_off[q + 1], k = s1 - s0;
-        if (k == 0) { R.status[q] = VLGB_ERR_ARG; continue; }
-        if (k > (uint32_t)MAX_K) { R.status[q] = VLGB_ERR_TOO_LARGE; continue; }
-        bool empty_sub = false, bad_width = false;
-        uint64_t span = 0;
-        for (uint32_t s = s0; s < s1; s++) {
-            uint64_t len = batch->pat_off[s + 1] - batch->pat_off[s];
-            if (len == 0) empty_sub = true;
-            if (len & ((1u << idx->sym_shift) - 1u)) bad_width = true;
-            span = sat_add64(span, len);
-            if (s + 1 < s1) span = sat_add64(span, sat_shl64(batch->gap_max[s], idx->sym_shift));
+    struct PlanCache {
+        std::string key;
+        PatternDict dict;
+        std::vector<uint32_t> sub_pid;
+        std::vector<PlanQuery> plan;  // entry cursors are filled per call
+        std::vector<int32_t> status;
+    };
+    static thread_local PlanCache pc;
+    static std::atomic<uint64_t> next_stamp{1};
+    std::string key;
+    {
+        const uint64_t geo[6] = {nq, ns, idx->n, halo, (uint64_t)halo_truncated_by_shard, idx->sym_shift};
+        const uint64_t nbytes = ns ? batch->pat_off[ns] : 0;
+        key.reserve(sizeof geo + (nq + 1) * 4 + (ns + 1) * 8 + nbytes + (size_t)ns * 16);
+        key.append(reinterpret_cast<const char*>(geo), sizeof geo);
+        if (nq) {
+            key.append(reinterpret_cast<const char*>(batch->sub_off), (size_t)(nq + 1) * sizeof batch->sub_off[0]);
+            key.append(reinterpret_cast<const char*>(batch->pat_off), (size_t)(ns + 1) * sizeof batch->pat_off[0]);
+            key.append(reinterpret_cast<const char*>(batch->pat_bytes), (size_t)nbytes);
+            key.append(reinterpret_cast<const char*>(batch->gap_min), (size_t)ns * sizeof batch->gap_min[0]);
+            key.append(reinterpret_cast<const char*>(batch->gap_max), (size_t)ns * sizeof batch->gap_max[0]);
         }
-        if (empty_sub) { R.status[q] = VLGB_ERR_EMPTY_SUB; continue; }  // SURVEY A.4 fence
-        if (bad_width) { R.status[q] = VLGB_ERR_ARG; continue; }        // not a whole number of encoded symbols
-        // a match that starts in the owned part must end inside owned + halo
-        if (halo_truncated_by_shard && span > halo + 1) { R.status[q] = VLGB_ERR_TOO_LARGE; continue; }
-        bool impossible = false;
-        for (uint32_t s = s0; s < s1; s++) {
-            uint64_t len = batch->pat_off[s + 1] - batch->pat_off[s];
-            if (len > idx->n) { impossible = true; continue; }  // longer than the shard: cannot occur
-            sub_pid[s] = dict.add(batch->pat_bytes + batch->pat_off[s], len);
-        }
-        if (impossible) continue;
-        plan.push_back({q, k, s0, R.ext.entry[q]});
     }
+    if (key != pc.key || !pc.dict.stamp) {
+        pc.key.clear();
+        pc.dict = PatternDict();
+        pc.sub_pid.assign(ns, NONE32);
+        pc.plan.clear();
+        pc.status.assign(nq, VLGB_OK);
+        for (uint32_t q = 0; q < nq; q++) {
+            uint32_t s0 = batch->sub_off[q], s1 = batch->sub_off[q + 1], k = s1 - s0;
+            if (k == 0) { pc.status[q] = VLGB_ERR_ARG; continue; }
+            if (k > (uint32_t)MAX_K) { pc.status[q] = VLGB_ERR_TOO_LARGE; continue; }
+            bool empty_sub = false, bad_width = false;
+            uint64_t span = 0;
+            for (uint32_t s = s0; s < s1; s++) {
+                uint64_t len = batch->pat_off[s + 1] - batch->pat_off[s];
+                if (len == 0) empty_sub = true;
+                if (len & ((1u << idx->sym_shift) - 1u)) bad_width = true;
+                span = sat_add64(span, len);
+                if (s + 1 < s1) span = sat_add64(span, sat_shl64(batch->gap_max[s], idx->sym_shift));
+            }
+            if (empty_sub) { pc.status[q] = VLGB_ERR_EMPTY_SUB; continue; }  // SURVEY A.4 fence
+            if (bad_width) { pc.status[q] = VLGB_ERR_ARG; continue; }        // not a whole number of encoded symbols
+            // a match that starts in the owned part must end inside owned + halo
+            if (halo_truncated_by_shard && span > halo + 1) { pc.status[q] = VLGB_ERR_TOO_LARGE; continue; }
+            bool impossible = false;
+            for (uint32_t s = s0; s < s1; s++) {
+                uint64_t len = batch->pat_off[s + 1] - batch->pat_off[s];
+                if (len > idx->n) { impossible = true; continue; }  // longer than the shard: cannot occur
+                pc.sub_pid[s] = pc.dict.add(batch->pat_bytes + batch->pat_off[s], len);
+            }
+            if (impossible) continue;
+            pc.plan.push_back({q, k, s0, 0});
+        }
+        pc.dict.stamp = next_stamp.fetch_add(1);
+        pc.key = key;
+    }
+    R.status = pc.status;
+    const PatternDict& dict = pc.dict;
+    const std::vector<uint32_t>& sub_pid = pc.sub_pid;
+    std::vector<PlanQuery> plan = pc.plan;
+    for (PlanQuery& pq : plan) pq.entry = R.ext.entry[pq.q];
 
     // ---- scan: one sorted occurrence list per distinct subpattern
     ScanOut so;

@@ -620,6 +620,7 @@ __global__ void scan_owned_kernel(const uint32_t* pos, const uint64_t* base, con
 
 // ---- host side: pattern dictionary and pass tables ----------------------------------------------
 struct PatternDict {
+    uint64_t stamp = 0;                          // identity of a finished dictionary (0 = none): same stamp, same patterns
     std::vector<std::string> pats;               // distinct subpatterns of the batch
     // open addressing over (hash of the bytes) -> index in pats; no allocation per lookup
     std::vector<uint32_t> table;

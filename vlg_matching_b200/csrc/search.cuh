@@ -111,24 +111,33 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     // same batch on the next shard of a sharded search, a repeated query file) skips the host build; the comparison
     // is on the pattern bytes themselves, not on a hash.
     struct TableCache {
-        std::string key;  // lengths + bytes of every pattern of the dictionary it was built for
+        uint64_t stamp = 0;  // PatternDict::stamp it was built for (0 = none)
+        std::string key;     // lengths + bytes of every pattern of that dictionary
         std::vector<PassDev> pd;
         std::vector<uint8_t> ctl;
+        size_t o_allbase = 0;
+        DeviceBuffer dev;    // the control blob on the device (tables, long-pattern arrays, list bases)
+        int device = -1;
     };
     static thread_local TableCache cache;
+    bool hit = dict.stamp && dict.stamp == cache.stamp && cache.device == c.device;
     std::string key;
-    key.reserve(P * 12);
-    for (uint32_t i = 0; i < P; i++) {
-        const uint32_t l = (uint32_t)dict.pats[i].size();
-        key.append(reinterpret_cast<const char*>(&l), 4);
-        key += dict.pats[i];
+    if (!hit) {
+        key.reserve(P * 12);
+        for (uint32_t i = 0; i < P; i++) {
+            const uint32_t l = (uint32_t)dict.pats[i].size();
+            key.append(reinterpret_cast<const char*>(&l), 4);
+            key += dict.pats[i];
+        }
+        hit = key == cache.key && !cache.pd.empty() && cache.device == c.device;
     }
     std::vector<PassDev> pd;
     Packer ctl;
-    size_t work_bytes = 0;
-    if (key == cache.key && !cache.pd.empty()) {
+    size_t work_bytes = 0, o_allbase = 0;
+    if (hit) {
         pd = cache.pd;
-        ctl.host = cache.ctl;
+        o_allbase = cache.o_allbase;
+        cache.stamp = dict.stamp;
     } else {
         std::unique_ptr<PassHost> ph(new PassHost());
         for (uint32_t first = 0; first < P;) {
@@ -150,13 +159,16 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
             pd.push_back(d);
             first += cnt;
         }
+        o_allbase = ctl.put(so.base);  // P+1 u64, filled later (owned kernel)
+        cache.stamp = dict.stamp;
         cache.key = key;
         cache.pd = pd;
         cache.ctl = ctl.host;
+        cache.o_allbase = o_allbase;
+        cache.device = -1;  // the device copy follows below
     }
     for (const PassDev& d : pd) work_bytes += Arena::padded((size_t)ngroups * d.stride, 4) + Arena::padded(d.stride, 4);
     const uint32_t npass = (uint32_t)pd.size();
-    const size_t o_allbase = ctl.put(so.base);  // P+1 u64, filled later (owned kernel)
     work_bytes += 2 * Arena::padded(P, 4);      // owned[], totals[]
     // hit streams: stream_cap entries per row (2 per text position, else 1), for as many passes as the budget
     // (a third of the free device memory, at most 24 GiB) allows; the other passes take the legacy two-scan path
@@ -189,10 +201,15 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     const size_t legacy_bytes = Arena::padded((size_t)rows * SCAN_S, 4) + Arena::padded((size_t)nrb * SCAN_S, 4);
     work_bytes += (size_t)(npass - stream_passes + 1) * legacy_bytes;
     trace().mark("scan: tables built");
-    c.scan_arena.reserve(ctl.size() + work_bytes + 4096);
-    uint8_t* d_ctl = c.scan_arena.take<uint8_t>(ctl.size());
-    h2d(c, d_ctl, ctl.host.data(), ctl.host.size());
-    c.stats.h2d_bytes += ctl.host.size();
+    c.scan_arena.reserve(work_bytes + 4096);
+    // the control blob lives in the cache's own device buffer: a repeated dictionary is not uploaded again
+    if (!hit) {
+        uint8_t* d = (uint8_t*)cache.dev.get(ctl.size());
+        h2d(c, d, ctl.host.data(), ctl.host.size());
+        c.stats.h2d_bytes += ctl.host.size();
+        cache.device = c.device;
+    }
+    uint8_t* d_ctl = (uint8_t*)cache.dev.p;
     for (uint32_t p = 0; p < npass; p++) {
         pd[p].gmatrix = c.scan_arena.take<uint32_t>((size_t)ngroups * pd[p].stride);
         pd[p].total = c.scan_arena.take<uint32_t>(pd[p].stride);
