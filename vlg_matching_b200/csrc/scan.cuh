@@ -453,23 +453,29 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 constexpr int SCAT_WARPS = 16;
 constexpr int SCAT_ROUNDS = 16;
 constexpr int SCAT_BLOCK = SCAT_WARPS * 32 * SCAT_ROUNDS;  // hits per block: every counter stays below 2^15 (marker bit)
-constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * SCAN_S * sizeof(uint16_t) + (size_t)SCAN_S * sizeof(uint64_t);
+inline size_t scat_smem_bytes(uint32_t s_act)
+{
+    const size_t words = (s_act + 1) >> 1;
+    return 2 * words * sizeof(uint64_t) + (size_t)SCAT_WARPS * words * sizeof(uint32_t);
+}
+constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * SCAN_S * sizeof(uint16_t) + (size_t)SCAN_S * sizeof(uint64_t);  // the largest pass
 static_assert(SCAT_BLOCK < (1 << 16), "16-bit counter halves");
 
 __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    uint64_t* base = reinterpret_cast<uint64_t*>(smem_raw);  // [SCAN_S] next free word of pid's list for this group
-    uint32_t* cnt32 = reinterpret_cast<uint32_t*>(smem_raw + (size_t)SCAN_S * sizeof(uint64_t));  // [SCAT_WARPS][SCAN_S / 2], two patterns per word
+    // shared memory is sized by the patterns of the pass (scat_smem_bytes): 2 * words cursors, SCAT_WARPS * words counters
+    const uint32_t words = (a.s_act + 1) >> 1;  // counter words: two patterns each
+    uint64_t* base = reinterpret_cast<uint64_t*>(smem_raw);  // [2 * words] next free word of pid's list for this group
+    uint32_t* cnt32 = reinterpret_cast<uint32_t*>(smem_raw + (size_t)2 * words * sizeof(uint64_t));  // [SCAT_WARPS][words]
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* cur = cnt32 + warp * (SCAN_S / 2);
+    uint32_t* cur = cnt32 + warp * words;
     const volatile uint32_t* vcur = cur;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t words = (a.s_act + 1) >> 1;  // counter words in use
     const uint32_t grp = blockIdx.x;
     const uint32_t* gm = a.gmatrix + (size_t)grp * a.s_stride;
     for (uint32_t i = threadIdx.x; i < a.s_act; i += SCAT_WARPS * 32) base[i] = __ldg(a.list_base + i) + __ldg(gm + i);
-    for (uint32_t i = threadIdx.x; i < (uint32_t)SCAT_WARPS * (SCAN_S / 2); i += SCAT_WARPS * 32) cnt32[i] = 0u;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)SCAT_WARPS * words; i += SCAT_WARPS * 32) cnt32[i] = 0u;
     const uint32_t row_end = min(a.rows, (grp + 1) * (uint32_t)SCAN_GROUP_ROWS);
     for (uint32_t row = grp * SCAN_GROUP_ROWS; row < row_end; row++) {
         const uint32_t nh = a.row_hits[row];
@@ -486,11 +492,11 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
             // the last slice's counters now hold the previous block's totals: the group cursors advance; then all
             // slices start from zero (one thread per counter word, the same thread for all slices)
             for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
-                const uint32_t t = cnt32[(SCAT_WARPS - 1) * (SCAN_S / 2) + i];
+                const uint32_t t = cnt32[(SCAT_WARPS - 1) * words + i];
                 base[2 * i] += t & 0xFFFFu;
                 base[2 * i + 1] += t >> 16;
 #pragma unroll
-                for (int w = 0; w < SCAT_WARPS; w++) cnt32[w * (SCAN_S / 2) + i] = 0u;
+                for (int w = 0; w < SCAT_WARPS; w++) cnt32[w * words + i] = 0u;
             }
             __syncthreads();
             // ---- 1. histogram of the slice
@@ -503,8 +509,8 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
                 uint32_t run = 0;
 #pragma unroll
                 for (int w = 0; w < SCAT_WARPS; w++) {
-                    const uint32_t v = cnt32[w * (SCAN_S / 2) + i];
-                    cnt32[w * (SCAN_S / 2) + i] = run;
+                    const uint32_t v = cnt32[w * words + i];
+                    cnt32[w * words + i] = run;
                     run += v;
                 }
             }
@@ -515,7 +521,7 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
             for (int r = 0; r < SCAT_ROUNDS; r++) {
                 if (i0 + r * 32 >= i1) break;  // uniform
                 const bool valid = e[r] != NONE32;
-                const uint32_t pid = e[r] >> 16, w = (e[r] >> 17) & (SCAN_S / 2 - 1), sh = (e[r] >> 12) & 16u;
+                const uint32_t pid = e[r] >> 16, w = valid ? e[r] >> 17 : 0u, sh = (e[r] >> 12) & 16u;
                 uint32_t rk = valid ? (vcur[w] >> sh) & 0xFFFFu : 0u;  // every lane reads before any lane adds
                 __syncwarp();
                 if (valid) atomicAdd(&cur[w], 1u << sh);

@@ -326,7 +326,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         a.out = so.d_lists;
         if (pd[p].stream && !overflow[p]) {  // scatter the recorded occurrences
             c.begin(ST_SCAN_FILL);
-            scan_scatter_kernel<<<ngroups, SCAT_WARPS * 32, SCAT_SMEM, c.stream>>>(a);
+            scan_scatter_kernel<<<ngroups, SCAT_WARPS * 32, scat_smem_bytes(a.s_act), c.stream>>>(a);
             c.end(ST_SCAN_FILL, 1, pocc * 8);  // 4 B per occurrence read from the stream + 4 B written to its list
             c.stats.bytes[ST_SCAN_COUNT] += pocc * 4;
             continue;
