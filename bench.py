@@ -151,6 +151,18 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": self.n, "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
+def kernel_source_hash() -> str:
+    """sha256 over the CUDA sources: profiles/traffic.json records it, so that DRAM traffic captured for other kernels is
+    not reported beside this run's times (tools/make_profiles.py writes the same hash)."""
+    d = os.path.join(ROOT, "vlg_matching_b200", "csrc")
+    h = hashlib.sha256()
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".hpp")):
+            h.update(f.encode())
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -487,7 +499,7 @@ def main():
         if os.path.exists(tp):
             try:
                 tj = json.load(open(tp))
-                traffic = tj.get(name)
+                traffic = tj.get(name) if tj.get("source_hash") == kernel_source_hash() else None  # stale capture: say nothing
             except Exception:
                 traffic = None
         stages = {k: {"ms_per_step": v["ms"] / steps, "launches_per_step": v["launches"] / steps,

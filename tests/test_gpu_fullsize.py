@@ -192,3 +192,40 @@ def test_shard_near_4gib_limit(V):
     idx.free()
     del buf
     torch.cuda.empty_cache()
+
+
+def test_shard_at_the_size_limit(V):
+    """A shard of the largest size the library takes (2^32 - 4096 bytes: positions are shard-local u32): occurrences in
+    the first bytes, across row boundaries and in the very last bytes are found, nothing wraps in 32-bit arithmetic.
+    The text lives on the device only (vlgb_index_build_device); it is one filler byte with planted words, so the
+    expected lists are the planted positions."""
+    import torch
+    from vlg_matching_b200 import capi
+    n = 0xFFFFF000
+    free, _ = torch.cuda.mem_get_info()
+    if free < 60 << 30:
+        pytest.skip("needs ~60 GB of free device memory")
+    text = torch.full((n + 4096,), ord("x"), dtype=torch.uint8, device="cuda")
+    needle, hay = b"needle", b"hay"
+    plants = [0, 40, 65279, 65280 * 3 - 3, (1 << 31) - 2, (1 << 32) - 70000, n - 65280 - 3, n - 1030, n - 200, n - 9]
+    hays = [p + 6 + 20 for p in plants[:-1]] + [n - 3]  # the last hay ends exactly at the end of the shard
+    for p in plants:
+        text[p:p + 6] = torch.tensor(list(needle), dtype=torch.uint8, device="cuda")
+    for p in hays:
+        text[p:p + 3] = torch.tensor(list(hay), dtype=torch.uint8, device="cuda")
+    text[n:] = 0  # pad bytes after the shard
+    torch.cuda.synchronize()
+    idx = capi.Index.build_device(text.data_ptr(), n)
+    queries = [([needle], []), ([hay], []), ([needle, hay], [(0, 100)]), ([b"le", b"ha"], [(10, 30)]), ([b"needlex"], [])]
+    r = idx.search(V.PackedBatch(queries), capi.WANT_TUPLES)
+    assert r.tuples(0)[:, 0].tolist() == plants
+    assert r.tuples(1)[:, 0].tolist() == hays
+    # every needle but the last has its hay 26 bytes on (gap 20); the last needle (n - 9) is followed by the hay at n - 3: gap 0
+    assert r.tuples(2).tolist() == [[p, h] for p, h in zip(plants, hays)]
+    assert r.tuples(3).tolist() == [[p + 4, p + 26] for p in plants[:-1]]  # "le" .. "ha": gap 20 inside [10,30]; the last pair has gap 0
+    assert r.tuples(4)[:, 0].tolist() == plants[:-1]  # the last needle is followed by the hay, not by the filler
+    rc = idx.search(V.PackedBatch(queries), capi.WANT_COUNT)
+    assert np.array_equal(rc.counts(), r.counts())
+    idx.free()
+    del text
+    torch.cuda.empty_cache()

@@ -27,7 +27,10 @@ def g(name):
 stage = {"scan_count": g("scan_kernel"), "scan_fill": g("scan_scatter"), "join_probe": (g("join_probe") or 0) + (g("join_rev_count") or 0),
          "join_compact": (g("join_compact") or 0) + (g("join_rev_expand") or 0), "select_tile": (g("sel_succ") or 0) + (g("sel_tile") or 0),
          "select_walk": g("sel_mark"), "emit": g("sel_emit")}
-json.dump({"source": f"profiles/{tag}_full_summary.txt (dram__bytes_read.sum + dram__bytes_write.sum per launch)", **stage},
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+json.dump({"source": f"profiles/{tag}_full_summary.txt (dram__bytes_read.sum + dram__bytes_write.sum per launch)",
+           "source_hash": bench.kernel_source_hash(), **stage},
           open(os.path.join(pr, "traffic.json"), "w"), indent=1)
 os.remove(tj)
 print(open(out).read()[:3000])

@@ -194,14 +194,26 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
                 stream_passes = (uint32_t)std::min<uint64_t>(npass, budget / per_pass);
             }
         }
-        work_bytes += stream_passes * (Arena::padded((size_t)rows * stream_cap, 4) + Arena::padded(rows, 4)) + Arena::padded(npass, 4);
+        work_bytes += Arena::padded(npass, 4);
     }
     // legacy state: one per pass without a stream, plus ONE spare shared by the passes whose stream overflows
     // (they are redone one after the other)
     const size_t legacy_bytes = Arena::padded((size_t)rows * SCAN_S, 4) + Arena::padded((size_t)nrb * SCAN_S, 4);
-    work_bytes += (size_t)(npass - stream_passes + 1) * legacy_bytes;
+    auto total_bytes = [&](uint32_t sp) {
+        return work_bytes + sp * (Arena::padded((size_t)rows * stream_cap, 4) + Arena::padded(rows, 4)) +
+               (size_t)(npass - sp + 1) * legacy_bytes + 4096;
+    };
     trace().mark("scan: tables built");
-    c.scan_arena.reserve(work_bytes + 4096);
+    try {
+        c.scan_arena.reserve(total_bytes(stream_passes));
+    } catch (const CudaError& e) {
+        // the free-memory figure above is cached and does not see what other threads / libraries took since: without
+        // the streams the pass still runs (legacy two-scan path)
+        if (e.e != cudaErrorMemoryAllocation || !stream_passes) throw;
+        cudaGetLastError();
+        stream_passes = 0;
+        c.scan_arena.reserve(total_bytes(0));
+    }
     // the control blob lives in the cache's own device buffer: a repeated dictionary is not uploaded again
     if (!hit) {
         uint8_t* d = (uint8_t*)cache.dev.get(ctl.size());
