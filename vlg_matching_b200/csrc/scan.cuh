@@ -441,33 +441,35 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32, 1) scan_kernel(ScanArgs a)
 // 4736 rows in flight left every sector partially written for ~1 ms: 4x the algorithmic DRAM traffic, profiles/r01b.)
 //
 // A row's stream is taken in blocks of SCAT_WARPS x 32 x SCAT_ROUNDS hits, one slice of whole rounds per warp:
-//   1. histogram: every warp counts its slice per pattern in its PRIVATE 16-bit counters (shared-memory atomics
-//      without return value; measured ~1 cycle of the load/store pipe per warp instruction, tools/microbench),
-//   2. the counters become exclusive prefixes over the slices; base[pid] advances by the block total,
-//   3. scatter: rank among equal patterns = the private counter read BEFORE the round's increments (all lanes read,
-//      then all lanes add 1 with an atomic without return value, then all lanes read again).  A counter that moved by
-//      more than 1 is shared by several lanes of the round; the order in which the hardware serialises them is not
-//      defined by the ISA and positions must land in lane (= text) order, so only those lanes run MATCH.ANY and add
-//      the number of earlier lanes with the same pattern -- MATCH costs ~2 cycles per DISTINCT value among the
-//      participating lanes (tools/microbench), so it is kept to the few repeated (frequent) patterns of a round.
+//   1. rank + count: round by round every warp ranks the hits of its slice among equal patterns and counts them in
+//      its PRIVATE 16-bit counters: all lanes read their counter, then all lanes add 1 (shared-memory atomic without
+//      return value, ~1 cycle of the load/store pipe per warp instruction, tools/microbench), then all lanes read again.
+//      rank = the value read first; a counter that moved by more than 1 is shared by several lanes of the round -- the
+//      order in which the hardware serialises them is not defined by the ISA and positions must land in lane (= text)
+//      order, so only those lanes run MATCH.ANY and add the number of earlier lanes with the same pattern (MATCH costs
+//      ~2 cycles per DISTINCT value among the participating lanes, so it is kept to the few repeated patterns of a round).
+//   2. the counters become exclusive prefixes over the slices; the block totals advance base[pid] at the next block.
+//   3. scatter: out[base[pid] + prefix[slice][pid] + rank] = position -- independent gathers and stores.
 constexpr int SCAT_WARPS = 16;
 constexpr int SCAT_ROUNDS = 16;
 constexpr int SCAT_BLOCK = SCAT_WARPS * 32 * SCAT_ROUNDS;  // hits per block: every counter stays below 2^15 (marker bit)
 inline size_t scat_smem_bytes(uint32_t s_act)
 {
     const size_t words = (s_act + 1) >> 1;
-    return 2 * words * sizeof(uint64_t) + (size_t)SCAT_WARPS * words * sizeof(uint32_t);
+    return 2 * words * sizeof(uint64_t) + (size_t)(SCAT_WARPS + 1) * words * sizeof(uint32_t);
 }
-constexpr size_t SCAT_SMEM = (size_t)SCAT_WARPS * SCAN_S * sizeof(uint16_t) + (size_t)SCAN_S * sizeof(uint64_t);  // the largest pass
+constexpr size_t SCAT_SMEM = (size_t)(SCAT_WARPS + 1) * SCAN_S * sizeof(uint16_t) + (size_t)SCAN_S * sizeof(uint64_t);  // the largest pass
 static_assert(SCAT_BLOCK < (1 << 16), "16-bit counter halves");
 
 __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    // shared memory is sized by the patterns of the pass (scat_smem_bytes): 2 * words cursors, SCAT_WARPS * words counters
-    const uint32_t words = (a.s_act + 1) >> 1;  // counter words: two patterns each
+    // shared memory is sized by the patterns of the pass (scat_smem_bytes): 2 * words cursors, (SCAT_WARPS + 1) * words
+    // counter words (two patterns each): one line per slice and one for the block totals
+    const uint32_t words = (a.s_act + 1) >> 1;
     uint64_t* base = reinterpret_cast<uint64_t*>(smem_raw);  // [2 * words] next free word of pid's list for this group
     uint32_t* cnt32 = reinterpret_cast<uint32_t*>(smem_raw + (size_t)2 * words * sizeof(uint64_t));  // [SCAT_WARPS][words]
+    uint32_t* tot32 = cnt32 + SCAT_WARPS * words;  // [words] hits of the block per pattern
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* cur = cnt32 + warp * words;
     const volatile uint32_t* vcur = cur;
@@ -475,7 +477,7 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
     const uint32_t grp = blockIdx.x;
     const uint32_t* gm = a.gmatrix + (size_t)grp * a.s_stride;
     for (uint32_t i = threadIdx.x; i < a.s_act; i += SCAT_WARPS * 32) base[i] = __ldg(a.list_base + i) + __ldg(gm + i);
-    for (uint32_t i = threadIdx.x; i < (uint32_t)SCAT_WARPS * words; i += SCAT_WARPS * 32) cnt32[i] = 0u;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)(SCAT_WARPS + 1) * words; i += SCAT_WARPS * 32) cnt32[i] = 0u;
     const uint32_t row_end = min(a.rows, (grp + 1) * (uint32_t)SCAN_GROUP_ROWS);
     for (uint32_t row = grp * SCAN_GROUP_ROWS; row < row_end; row++) {
         const uint32_t nh = a.row_hits[row];
@@ -485,26 +487,40 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
             const uint32_t nb = min((uint32_t)SCAT_BLOCK, nh - b0);
             const uint32_t per = ((nb + SCAT_WARPS - 1) / SCAT_WARPS + 31) & ~31u;  // hits per slice, whole rounds
             const uint32_t i0 = b0 + min(nb, warp * per), i1 = b0 + min(nb, (warp + 1) * per);
-            uint32_t e[SCAT_ROUNDS];
+            uint32_t e[SCAT_ROUNDS], rk[SCAT_ROUNDS];
 #pragma unroll
             for (int r = 0; r < SCAT_ROUNDS; r++) e[r] = i0 + r * 32 + lane < i1 ? __ldg(st + i0 + r * 32 + lane) : NONE32;
             __syncthreads();  // the previous block is scattered (first block: base[] and the counters are set up)
-            // the last slice's counters now hold the previous block's totals: the group cursors advance; then all
-            // slices start from zero (one thread per counter word, the same thread for all slices)
+            // the group cursors advance by the previous block's totals; then all slices start from zero (one thread per
+            // counter word, the same thread for all slices)
             for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
-                const uint32_t t = cnt32[(SCAT_WARPS - 1) * words + i];
+                const uint32_t t = tot32[i];
                 base[2 * i] += t & 0xFFFFu;
                 base[2 * i + 1] += t >> 16;
 #pragma unroll
                 for (int w = 0; w < SCAT_WARPS; w++) cnt32[w * words + i] = 0u;
             }
             __syncthreads();
-            // ---- 1. histogram of the slice
+            // ---- 1. rank of every hit inside its slice, counting as it goes: the slice's counter read BEFORE the round's
+            // increments + the lanes of the round that hold the same pattern and come earlier
 #pragma unroll
-            for (int r = 0; r < SCAT_ROUNDS; r++)
-                if (e[r] != NONE32) atomicAdd(&cur[e[r] >> 17], 1u << ((e[r] >> 12) & 16u));
+            for (int r = 0; r < SCAT_ROUNDS; r++) {
+                rk[r] = 0;
+                if (i0 + r * 32 >= i1) continue;  // uniform
+                const bool valid = e[r] != NONE32;
+                const uint32_t pid = e[r] >> 16, w = valid ? e[r] >> 17 : 0u, sh = (e[r] >> 12) & 16u;
+                uint32_t before = valid ? (vcur[w] >> sh) & 0xFFFFu : 0u;  // every lane reads before any lane adds
+                __syncwarp();
+                if (valid) atomicAdd(&cur[w], 1u << sh);
+                __syncwarp();
+                // a counter that moved by more than 1: other lanes of the round hold the same pattern
+                const bool dup = valid && ((vcur[w] >> sh) & 0xFFFFu) - before > 1u;
+                const uint32_t m = __ballot_sync(0xffffffffu, dup);
+                if (dup) before += __popc(__match_any_sync(m, pid) & lt_mask);
+                rk[r] = before;
+            }
             __syncthreads();
-            // ---- 2. exclusive prefix over the slices
+            // ---- 2. exclusive prefix over the slices; the block totals wait for the next block's cursor advance
             for (uint32_t i = threadIdx.x; i < words; i += SCAT_WARPS * 32) {
                 uint32_t run = 0;
 #pragma unroll
@@ -513,24 +529,17 @@ __global__ void __launch_bounds__(SCAT_WARPS * 32) scan_scatter_kernel(ScanArgs 
                     cnt32[w * words + i] = run;
                     run += v;
                 }
+                tot32[i] = run;
             }
             __syncthreads();
-            // ---- 3. scatter: rank = the slice's counter before the round (+ the lanes of the round that hold the same
-            // pattern and come earlier)
+            // ---- 3. scatter: independent gathers and stores, nothing serialises the rounds any more
 #pragma unroll
             for (int r = 0; r < SCAT_ROUNDS; r++) {
-                if (i0 + r * 32 >= i1) break;  // uniform
-                const bool valid = e[r] != NONE32;
-                const uint32_t pid = e[r] >> 16, w = valid ? e[r] >> 17 : 0u, sh = (e[r] >> 12) & 16u;
-                uint32_t rk = valid ? (vcur[w] >> sh) & 0xFFFFu : 0u;  // every lane reads before any lane adds
-                __syncwarp();
-                if (valid) atomicAdd(&cur[w], 1u << sh);
-                __syncwarp();
-                // a counter that moved by more than 1: other lanes of the round hold the same pattern
-                const bool dup = valid && ((vcur[w] >> sh) & 0xFFFFu) - rk > 1u;
-                const uint32_t m = __ballot_sync(0xffffffffu, dup);
-                if (dup) rk += __popc(__match_any_sync(m, pid) & lt_mask);
-                if (valid) a.out[base[pid] + rk] = lo + (e[r] & 0xFFFFu);
+                if (e[r] != NONE32) {
+                    const uint32_t pid = e[r] >> 16;
+                    const uint32_t at = ((cur[pid >> 1] >> ((pid & 1u) * 16u)) & 0xFFFFu) + rk[r];
+                    a.out[base[pid] + at] = lo + (e[r] & 0xFFFFu);
+                }
             }
         }
     }
