@@ -163,6 +163,20 @@ def kernel_source_hash() -> str:
     return h.hexdigest()[:16]
 
 
+def bind_to_gpu_numa_node(device: int):
+    """Pin this process to the CPUs next to its GPU (NVML's ideal affinity).  With one process per GPU and eight GPUs on
+    two sockets, pinned result buffers otherwise land on whatever node the process started on and every device-to-host
+    copy crosses the socket link (measured: 58 MB took 4 ms with 8 ranks copying at once, 1 ms alone)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        phys = int(vis.split(",")[device]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else device
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(phys))
+    except Exception:
+        pass
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -292,6 +306,7 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
     if capi.device_count() < 1:
         raise SystemExit("no CUDA device: this benchmark has no CPU path")
+    bind_to_gpu_numa_node(local)  # before the CUDA context and any pinned allocation exist
     torch.cuda.set_device(local)
     capi.init(local)
     dev = torch.device("cuda", local)

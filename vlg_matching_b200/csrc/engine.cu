@@ -1202,6 +1202,7 @@ extern "C" int vlgb_search_sharded(const vlgb_index* const* shards, uint32_t n_l
                 if (nrc != ncclSuccess) return cleanup(fail(VLGB_ERR_CUDA, "ncclAllGather: %s", api.GetErrorString(nrc)));
                 VLGB_CUDA(cudaMemcpyAsync(h_buf + row_words, d_buf + row_words, G * row_words * 8, cudaMemcpyDeviceToHost, c.stream));
                 VLGB_CUDA(cudaStreamSynchronize(c.stream));
+                trace().mark("exchange: all-gather done (includes the wait for the slowest rank)");
                 memcpy(table.data(), h_buf + row_words, G * row_words * 8);
                 S.rounds++;
                 const uint32_t n_redo = chain_plan(table.data(), used.data(), G, nq, entries.data(), redo.data());
@@ -1221,6 +1222,7 @@ extern "C" int vlgb_search_sharded(const vlgb_index* const* shards, uint32_t n_l
                     }
                 }
                 used = entries;
+                trace().mark("exchange: cursors chained, re-entry done");
                 if (!n_redo) break;
                 S.reentered_shards += n_redo;
             }

@@ -103,6 +103,7 @@ __host__ __device__ inline uint32_t scan_h2(uint32_t w) { return ((w & 0xFFFFu) 
 struct ScanArgs {
     const uint8_t* text;     // shard start (device, 16-byte aligned), >= 16 readable bytes after valid_len
     uint32_t valid_len;      // bytes of the shard that may be matched (owned + halo)
+    uint32_t owned_len;      // occurrences at positions >= owned_len lie in the halo: counted per pattern in `halo`
     uint32_t chunk;          // positions per row (multiple of SCAN_STEP, <= SCAN_MAX_CHUNK)
     uint32_t rows;
     uint32_t s_act;          // patterns in this pass
@@ -128,6 +129,9 @@ struct ScanArgs {
     uint32_t stream_cap;
     uint32_t* row_hits;      // [rows] occurrences found in the row (stream pass out)
     uint32_t* overflow;      // number of rows with row_hits > stream_cap (stream pass out)
+    uint32_t* halo;          // [s_stride] occurrences per pattern in the halo (counting passes out; zeroed by the host).
+                             // The halo is the last ~1 KB of a shard: list length - halo count = the OWNED prefix of the
+                             // list, known with the list sizes, no second look at the lists
     uint32_t only_overflow;  // unused (kept for the ABI of the args block)
 };
 
@@ -173,10 +177,14 @@ __device__ __forceinline__ void scan_emit(const ScanArgs& a, uint32_t hits, uint
         if (pid != NONE32) {
             atomicAdd(mrow + pid, 1u);
             if (at < a.stream_cap) stream_row[at] = rel | (pid << 16);
+            if (p >= a.owned_len) atomicAdd(a.halo + pid, 1u);  // a handful per shard
         }
         nh += __popc(hits);
     } else if (MODE == SCAN_COUNT) {
-        if (pid != NONE32) atomicAdd(mrow + pid, 1u);  // fire-and-forget L2 reduction
+        if (pid != NONE32) {
+            atomicAdd(mrow + pid, 1u);  // fire-and-forget L2 reduction
+            if (p >= a.owned_len) atomicAdd(a.halo + pid, 1u);
+        }
     } else {
         // legacy pass 2: the matrix entry is the row's write cursor inside the list; rank among equal patterns of
         // the round = lane order = position order

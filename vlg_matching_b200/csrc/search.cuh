@@ -102,7 +102,7 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     struct PassDev {
         uint32_t first, s_act, stride, has_short, has_long;  // dictionary patterns [first, first + s_act)
         size_t o_tables, o_len, o_off, o_next, o_blob, o_base;  // inside the control blob
-        uint32_t *gmatrix, *total;                 // stream path: [groups][stride] counts -> group cursors
+        uint32_t *gmatrix, *total, *halo;          // stream path: [groups][stride] counts -> group cursors; occurrences in the halo
         uint32_t *matrix = nullptr, *part = nullptr;  // legacy path: [rows][stride] counts -> row cursors, row-block sums
         uint32_t *stream = nullptr, *row_hits = nullptr, *overflow = nullptr;  // hit stream (if the budget allows one)
     };
@@ -167,9 +167,8 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         cache.o_allbase = o_allbase;
         cache.device = -1;  // the device copy follows below
     }
-    for (const PassDev& d : pd) work_bytes += Arena::padded((size_t)ngroups * d.stride, 4) + Arena::padded(d.stride, 4);
+    for (const PassDev& d : pd) work_bytes += Arena::padded((size_t)ngroups * d.stride, 4) + 2 * Arena::padded(d.stride, 4);
     const uint32_t npass = (uint32_t)pd.size();
-    work_bytes += 2 * Arena::padded(P, 4);      // owned[], totals[]
     // hit streams: stream_cap entries per row (2 per text position, else 1), for as many passes as the budget
     // (a third of the free device memory, at most 24 GiB) allows; the other passes take the legacy two-scan path
     uint32_t stream_cap = 0, stream_passes = 0;
@@ -225,8 +224,9 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     for (uint32_t p = 0; p < npass; p++) {
         pd[p].gmatrix = c.scan_arena.take<uint32_t>((size_t)ngroups * pd[p].stride);
         pd[p].total = c.scan_arena.take<uint32_t>(pd[p].stride);
+        pd[p].halo = c.scan_arena.take<uint32_t>(pd[p].stride);
+        if (owned_len < n) VLGB_CUDA(cudaMemsetAsync(pd[p].halo, 0, (size_t)pd[p].stride * 4, c.stream));
     }
-    uint32_t* d_owned = c.scan_arena.take<uint32_t>(P);
     uint32_t* d_overflow = c.scan_arena.take<uint32_t>(npass);
     VLGB_CUDA(cudaMemsetAsync(d_overflow, 0, (size_t)npass * 4, c.stream));
     for (uint32_t p = 0; p < stream_passes; p++) {
@@ -246,6 +246,8 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         ScanArgs a;
         a.text = d_text;
         a.valid_len = (uint32_t)n;
+        a.owned_len = (uint32_t)std::min<uint64_t>(owned_len, n);
+        a.halo = pd[p].halo;
         a.chunk = chunk;
         a.rows = rows;
         a.s_act = pd[p].s_act;
@@ -305,6 +307,10 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
         }
         d2h(c, so.tot.data() + pd[p].first, pd[p].total, pd[p].s_act * 4);
         c.stats.d2h_bytes += pd[p].s_act * 4;
+        if (owned_len < n) {  // sharded text: the halo counts come down with the list sizes
+            d2h(c, so.own.data() + pd[p].first, pd[p].halo, pd[p].s_act * 4);
+            c.stats.d2h_bytes += pd[p].s_act * 4;
+        }
     }
     d2h(c, overflow.data(), d_overflow, (size_t)npass * 4);
     VLGB_CUDA(cudaGetLastError());
@@ -312,6 +318,12 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     sync_stream(c);  // sync 1: list sizes
     trace().mark("scan: sync 1");
 
+    // owned prefix of every list = its length minus the occurrences in the halo (lists are ascending)
+    if (owned_len < n) {
+        for (uint32_t i = 0; i < P; i++) so.own[i] = so.tot[i] - so.own[i];
+    } else {
+        so.own = so.tot;
+    }
     uint64_t words = 0;
     for (uint32_t i = 0; i < P; i++) {
         so.base[i] = words;
@@ -358,20 +370,6 @@ inline void run_scan(Context& c, const uint8_t* d_text, uint64_t n, uint64_t own
     c.stats.scan_passes += npass;
     c.stats.distinct_patterns += P;
 
-    if (owned_len >= n) {
-        so.own = so.tot;
-    } else {
-        // totals of all patterns, contiguous on the device for the owned-prefix search
-        uint32_t* d_tot = c.scan_arena.take<uint32_t>(P);
-        h2d(c, d_tot, so.tot.data(), (size_t)P * 4);
-        scan_owned_kernel<<<(P + 127) / 128, 128, 0, c.stream>>>(so.d_lists, dev_at<const uint64_t>(d_ctl, o_allbase), d_tot,
-                                                                 P, (uint32_t)owned_len, d_owned);
-        d2h(c, so.own.data(), d_owned, (size_t)P * 4);
-        VLGB_CUDA(cudaGetLastError());
-        sync_stream(c);  // sync 2 (sharded texts only)
-        c.stats.h2d_bytes += (uint64_t)P * 4;
-        c.stats.d2h_bytes += (uint64_t)P * 4;
-    }
 }
 
 // ---------------------------------------------------------------------------------------------
