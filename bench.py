@@ -429,6 +429,7 @@ def main():
 
     # ---- rank path: single rare-subpattern queries, scan vs suffix-array wavelet tree (N = 1 only)
     rank_block = None
+    rare = []
     if world == 1 and not args.no_rank_path:
         info = index.attach_rank()
         rare = S.sample_queries(own[:QUERY_SOURCE_BYTES], 32, 2, (9, 12), [(100, 1000)], 21, word_aligned=True)
@@ -555,6 +556,12 @@ def main():
             what = "the whole 200 MiB text" if r["n"] == SHARD_BYTES else f"first {r['n'] >> 20} MiB of the text"
             line["cpu_baseline"] = {"value": r["gbps"], "unit": "GB/s", "cores": threads, "kind": r["kind"],
                                     "sample": f"{what}, all {NQ} queries, {threads} threads, 1 pass", **r["info"]}
+            if r["n"] == SHARD_BYTES and r["kind"] == "reference" and rank_block is not None:
+                # the rare single queries of the rank_path block through the reference, one thread, same 200 MiB index
+                rr = cpu_reference_run(rare, 3, 1, 1, SHARD_BYTES, build_if_missing=False)
+                if rr is not None:
+                    line["cpu_baseline"]["rare_single_query_us"] = rr["seconds_per_step"] / len(rare) * 1e6
+                    line["cpu_baseline"]["rare_matches"] = rr["info"].get("num_results")
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     capi.comm_destroy()
