@@ -145,6 +145,21 @@ int vlgb_index_rank_info(const vlgb_index* idx, vlgb_rank_info* out);
 /* Copy SA[first .. first+count) to the host, read THROUGH the wavelet tree on the device (wt_int::operator[],
  * wt_int.hpp:339-361) -- what a caller of vlg_index::wt[i] gets.  Needs vlgb_index_attach_rank. */
 int vlgb_index_sa_extract(const vlgb_index* idx, uint64_t first, uint64_t count, uint64_t* out);
+/* The same read WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  vlgb_index_sa_extract stages the values in a device buffer it allocates; this variant stages
+ * them in a file-scope device array of VLGB_SA_EXTRACT_STATIC_MAX u64 entries (1 MiB; every GPU that loads the
+ * library holds it until the process exits) and calls no cudaMalloc / cudaFree / allocating library routine.
+ *   - count > VLGB_SA_EXTRACT_STATIC_MAX is rejected with VLGB_ERR_ARG (split the range, or use the call above);
+ *   - vlgb_init must have run on the calling thread (it creates the stream; that call allocates, this one does not);
+ *     the first call on a device looks the array's device address up (cudaGetSymbolAddress, once per device);
+ *   - `out` (count entries) may be host or device memory; the call returns after the copy has completed;
+ *   - every call on a GPU shares the ONE array, which keeps the last call's contents: entries [0, count) are written
+ *     before they are read, so nothing needs clearing, but calls that overlap on the same GPU (two host threads, each
+ *     on its own stream) race on it -- serialise them.
+ * Needs vlgb_index_attach_rank. */
+#define VLGB_SA_EXTRACT_STATIC_MAX (1ull << 17)
+int vlgb_index_sa_extract_static(const vlgb_index* idx, uint64_t first, uint64_t count, uint64_t* out);
 /* Pattern generation for the reference's experiment grid (examples/generate-pattern.cpp:1-120, driven by
  * benchmark/gapped-matching/Makefile:90-106): the `count` most frequent substrings of `length` symbols whose symbols
  * all belong to `charset` (0 = alpha-numerical + '_', 1 = 0 plus ' ', 2 = any: the tool's human_readable = 0), in the

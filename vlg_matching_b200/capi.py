@@ -32,7 +32,7 @@ SYMBOLS = [
     "vlgb_result_tuples", "vlgb_result_exit_cursors", "vlgb_result_first_starts", "vlgb_result_occurrences",
     "vlgb_result_fixup", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
     "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
-    "vlgb_parse_batch", "vlgb_parse_lines", "vlgb_index_attach_rank", "vlgb_index_rank_info", "vlgb_index_sa_extract",
+    "vlgb_parse_batch", "vlgb_parse_lines", "vlgb_index_attach_rank", "vlgb_index_rank_info", "vlgb_index_sa_extract", "vlgb_index_sa_extract_static",
     "vlgb_set_path", "vlgb_result_device_starts", "vlgb_result_device_tuples", "vlgb_comm_unique_id", "vlgb_comm_init",
     "vlgb_comm_destroy", "vlgb_search_sharded", "vlgb_chain_plan", "vlgb_index_frequent_phrases",
 ]
@@ -117,6 +117,8 @@ lib.vlgb_encode_symbols.argtypes = [C.c_uint32, _P, C.c_uint64, _P]
 lib.vlgb_index_attach_rank.argtypes = [_P, C.c_uint32]
 lib.vlgb_index_rank_info.argtypes = [_P, C.POINTER(RankInfo)]
 lib.vlgb_index_sa_extract.argtypes = [_P, C.c_uint64, C.c_uint64, _P]
+lib.vlgb_index_sa_extract_static.argtypes = [_P, C.c_uint64, C.c_uint64, _P]
+SA_EXTRACT_STATIC_MAX = 1 << 17
 lib.vlgb_set_path.argtypes = [C.c_int]
 lib.vlgb_index_frequent_phrases.argtypes = [_P, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, C.POINTER(C.c_uint32)]
 for _f in ("vlgb_result_device_starts", "vlgb_result_device_tuples"):

@@ -9,6 +9,7 @@
 
 #include "common.cuh"
 #include "parse.hpp"
+#include <mutex>
 #include "search.cuh"
 #include "phrases.cuh"
 #include <queue>
@@ -546,6 +547,69 @@ extern "C" int vlgb_index_sa_extract(const vlgb_index* idx, uint64_t first, uint
         if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
         buf.release();
         if (e != cudaSuccess) throw CudaError{e, __FILE__, __LINE__};
+        return VLGB_OK;
+    } catch (const CudaError& e) {
+        return cuda_fail(e);
+    }
+}
+
+// ---- vlgb_index_sa_extract_static: the same read, allocating nothing -----------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  vlgb_index_sa_extract
+// stages the values in a device buffer it allocates; this variant stages them in a file-scope device array of
+// VLGB_SA_EXTRACT_STATIC_MAX entries (1 MiB, held by every GPU that loads the library until the process exits).
+namespace {
+static __device__ __align__(256) uint64_t g_sa_static_scratch[VLGB_SA_EXTRACT_STATIC_MAX];
+constexpr int SA_STATIC_MAX_DEVICES = 64;
+uint64_t* g_sa_static_ptr[SA_STATIC_MAX_DEVICES] = {};  // device address of the array, per device (set-up, once)
+std::mutex g_sa_static_mutex;
+
+// In host code `g_sa_static_scratch` is a host-side stand-in, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, asked once per device with THAT device current.  No allocation.
+cudaError_t sa_static_setup(int device, uint64_t** out)
+{
+    std::lock_guard<std::mutex> lock(g_sa_static_mutex);
+    if (!g_sa_static_ptr[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_sa_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_sa_static_ptr[device] = static_cast<uint64_t*>(p);
+    }
+    *out = g_sa_static_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int vlgb_index_sa_extract_static(const vlgb_index* idx, uint64_t first, uint64_t count, uint64_t* out)
+{
+    if (!idx || (!out && count)) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract_static: null argument");
+    if (!idx->rank) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract_static: the index has no rank structures (vlgb_index_attach_rank)");
+    if (count > (uint64_t)VLGB_SA_EXTRACT_STATIC_MAX)
+        return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract_static: count %llu exceeds the static scratch (VLGB_SA_EXTRACT_STATIC_MAX = %llu entries); "
+                                  "split the range or use vlgb_index_sa_extract", (unsigned long long)count, (unsigned long long)VLGB_SA_EXTRACT_STATIC_MAX);
+    if (first > idx->n || count > idx->n - first) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract_static: range outside the suffix array");
+    Context& c = ctx();
+    // the stream is created by vlgb_init (that call allocates); this one must not
+    if (!c.ready) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract_static: call vlgb_init on this thread first");
+    if (c.device < 0 || c.device >= SA_STATIC_MAX_DEVICES) return fail(VLGB_ERR_ARG, "vlgb_index_sa_extract_static: device %d not supported", c.device);
+    if (!count) return VLGB_OK;
+    try {
+        int cur = -1;
+        VLGB_CUDA(cudaGetDevice(&cur));
+        if (cur != c.device) VLGB_CUDA(cudaSetDevice(c.device));
+        uint64_t* scratch = nullptr;
+        cudaError_t e = sa_static_setup(c.device, &scratch);
+        if (e != cudaSuccess) throw CudaError{e, __FILE__, __LINE__};
+        // every entry [0, count) of the scratch is written before it is read: nothing has to start at zero, and what the
+        // previous call left behind beyond `count` is never looked at
+        sa_extract_kernel<<<(unsigned)((count + 255) / 256), 256, 0, c.stream>>>(idx->rank->view, (uint32_t)first, (uint32_t)count, scratch);
+        VLGB_CUDA(cudaGetLastError());
+        VLGB_CUDA(cudaMemcpyAsync(out, scratch, count * 8, cudaMemcpyDefault, c.stream));  // out: host or device memory
+        VLGB_CUDA(cudaStreamSynchronize(c.stream));
         return VLGB_OK;
     } catch (const CudaError& e) {
         return cuda_fail(e);
