@@ -130,3 +130,47 @@ def test_generate_pattern_and_grid_pipeline(tmp_path):
     ref = O.search(text, queries, want_tuples=False, threads=8)
     assert int(keys["num_results"]) == sum(len(s) for _, s, _ in ref)
     assert int(keys["checksum"]) == sum(int(s.sum()) for _, s, _ in ref)
+
+
+@pytest.mark.gpu
+def test_gm_search_wcsearch3_gap_rule(tmp_path):
+    """gm_search --wcsearch3-gaps = the reference's index_wcsearch3 rule (ONE bound |P_1| + gaps[0] for every level,
+    index_wcsearch3.hpp:412-413) against tests/golden/wcsearch3_ref.json, generated from the reference's own
+    index_wcsearch3: num_results / checksum over all expressible golden patterns, per text; without the flag the
+    library's per-gap rule answers (a different checksum); the Python surface returns the same starts query by query;
+    a pattern the rule cannot express in per-gap form is an error, not a silent empty result."""
+    import numpy as np
+    import vlg_matching_b200 as V
+    from vlg_matching_b200 import capi, synth
+    from test_oracle_golden import wcsearch3_cases
+    from oracle import pyoracle as O
+    capi.init(0)
+    g, cases = wcsearch3_cases()
+    for ci, (text, raw, rewritten, want) in enumerate(cases):
+        idx = V.Index.build(text)
+        r = idx.search(V.PackedBatch(rewritten), capi.WANT_STARTS)
+        for q, w in enumerate(want):
+            assert r.status(q) == 0 and r.starts(q).tolist() == w, (ci, q, raw[q])
+        idx.free()
+        rawf = tmp_path / f"raw{ci}.txt"
+        text.tofile(rawf)
+        col = tmp_path / f"col{ci}"
+        assert run([os.path.join(BIN, "create_collection.x"), "-i", str(rawf), "-c", str(col)]).returncode == 0
+        assert run([os.path.join(BIN, "gm_index-VLGB200.x"), "-c", str(col)]).returncode == 0
+        pat = col / "patterns" / "w.txt"
+        pat.write_bytes(b"\n".join(synth.to_benchmark_syntax(q) for q in raw) + b"\n")
+        sums = {}
+        for flag in ([], ["--wcsearch3-gaps"]):
+            r = run([os.path.join(BIN, "gm_search-VLGB200.x"), "-c", str(col), "-p", str(pat), "-b", "1"] + flag)
+            assert r.returncode == 0, r.stderr
+            keys = dict(line[2:].split(" = ") for line in r.stdout.splitlines() if line.startswith("# ") and " = " in line)
+            sums[bool(flag)] = (int(keys["num_results"]), int(keys["checksum"]))
+        assert sums[True] == (sum(len(w) for w in want), sum(sum(w) for w in want))
+        lib = O.search(text, raw, want_tuples=False, threads=8)
+        assert sums[False] == (sum(len(s) for _, s, _ in lib), sum(int(s.sum()) for _, s, _ in lib))
+        assert sums[False] != sums[True]
+        if ci == 0:   # |P_2| = 6 > |P_1| + a_1 = 2: overlapping occurrences, not expressible
+            pat2 = col / "patterns" / "bad.txt"
+            pat2.write_bytes(b"th.{0,5}abcdef.{0,5}e\n")
+            r = run([os.path.join(BIN, "gm_search-VLGB200.x"), "-c", str(col), "-p", str(pat2), "-b", "1", "--wcsearch3-gaps"])
+            assert r.returncode != 0 and "wcsearch3 gap semantics" in r.stderr

@@ -116,3 +116,49 @@ def test_reference_experiment_grid():
             n += 1
             deep += c["count"] > 0 and tup.shape[1] >= 16
     assert n >= 600 and deep >= 30
+
+
+def wcsearch3_cases():
+    """tests/golden/wcsearch3_ref.json (from the reference's index_wcsearch3, make_golden_wcsearch3.py) ->
+    [(text, [(subs, gaps as the golden's pattern has them)], [(subs, per-gap form of the wcsearch3 rule)], starts)]
+    for the queries the per-gap form can express."""
+    import re
+    from vlg_matching_b200 import synth
+    g = json.load(open(os.path.join(HERE, "golden", "wcsearch3_ref.json")))
+    out = []
+    for c in g["cases"]:
+        gen = synth.english_text if "english" in c["text"]["generator"] else synth.dna_text
+        text = gen(c["text"]["n"], c["text"]["seed"])
+        assert synth.sha256(text) == c["sha256"]
+        raw, rewritten, want = [], [], []
+        for q in c["queries"]:
+            parts = re.split(r"\.\{(\d+),(\d+)\}", q["pattern"])
+            subs = [parts[0].encode("latin-1")] + [parts[i + 2].encode("latin-1") for i in range(1, len(parts), 3)]
+            gaps = [(int(parts[i]), int(parts[i + 1])) for i in range(1, len(parts), 3)]
+            lo, hi = len(subs[0]) + gaps[0][0], len(subs[0]) + gaps[0][1]     # index_wcsearch3.hpp:412-413
+            assert q["representable"] == all(len(s) <= lo for s in subs[:-1])
+            if not q["representable"]:
+                continue
+            raw.append((subs, gaps))
+            rewritten.append((subs, [(lo - len(s), hi - len(s)) for s in subs[:-1]]))
+            want.append(q["starts"])
+        out.append((text, raw, rewritten, want))
+    return g, out
+
+
+def test_wcsearch3_gap_rule_vs_reference_golden():
+    """The benchmark matcher index_wcsearch3 gives every level ONE start-to-start bound, |P_1| + gaps[0]
+    (index_wcsearch3.hpp:412-413).  Said in the library's per-gap form (a_i' = |P_1| + a_1 - |P_i|) and run through the
+    oracle it reproduces the reference's own index_wcsearch3 on every golden query -- and the goldens DO differ from
+    the library matcher's answers for a good part of them, so the rule is measured, not assumed."""
+    g, cases = wcsearch3_cases()
+    assert g["differs_from_library"] >= 20 and g["queries_total"] >= 200
+    n = differ = 0
+    for text, raw, rewritten, want in cases:
+        res = O.search(text, rewritten, want_tuples=False, threads=4)
+        lib = O.search(text, raw, want_tuples=False, threads=4)
+        for (st, starts, _), (_, lstarts, _), w in zip(res, lib, want):
+            assert st == 0 and starts.tolist() == w
+            differ += lstarts.tolist() != w
+            n += 1
+    assert n >= 190 and differ >= 20

@@ -8,6 +8,8 @@
 //   * index_b200::search applies every gap's own {a,b} with the lengths of its own subpattern (the library
 //     semantics of vlg_index.hpp:95).  index_wcsearch3 applies gaps[0] + |P_1| to every gap
 //     (index_wcsearch3.hpp:412-413); both agree for 2 subpatterns and for uniform gaps + lengths.
+//     set_gap_semantics(GAPS_WCSEARCH3) (gm_search --wcsearch3-gaps) reproduces index_wcsearch3's rule instead:
+//     pinned by tests/golden/wcsearch3_ref.json, generated from the reference's own index_wcsearch3.
 //   * a subpattern that does not occur gives an empty result (index_wcsearch3 has undefined behaviour there).
 //   * search_batch() answers a whole pattern file in one device pass; search() is the one-pattern call.
 #pragma once
@@ -96,6 +98,35 @@ struct collection {  // collection.hpp:17-44
         file_map["TEXT"] = text;
     }
 };
+
+// ---- which start-to-start bounds a pattern's levels get ----------------------------------------------------------
+// GAPS_PER_GAP (default): level i uses its own gap and its own length, lo_i = a_i + |P_i| (vlg_index.hpp:95).
+// GAPS_WCSEARCH3: every level uses ONE bound, [|P_1| + a_1, |P_1| + b_1] (index_wcsearch3.hpp:412-413 hands
+// wild_card_match_iterator3 a single (min_gap, max_gap); relax() applies it to every pair of neighbours, :217-236).
+// Expressed through the library's per-gap form: a_i' = |P_1| + a_1 - |P_i|, b_i' = |P_1| + b_1 - |P_i|.  A level
+// whose subpattern is longer than |P_1| + a_1 would need a negative gap (the reference then lets the occurrences
+// overlap): not representable, reported as an error for that pattern.
+enum gap_semantics_t { GAPS_PER_GAP = 0, GAPS_WCSEARCH3 = 1 };
+inline gap_semantics_t& gap_semantics_ref()
+{
+    static gap_semantics_t g = GAPS_PER_GAP;
+    return g;
+}
+inline void set_gap_semantics(gap_semantics_t g) { gap_semantics_ref() = g; }
+inline std::vector<std::pair<uint64_t, uint64_t>> effective_gaps(const gapped_pattern& p)
+{
+    if (gap_semantics_ref() == GAPS_PER_GAP || p.gaps.empty()) return p.gaps;
+    std::vector<std::pair<uint64_t, uint64_t>> g(p.gaps.size());
+    const uint64_t lo = p.subpatterns[0].size() + p.gaps[0].first, hi = p.subpatterns[0].size() + p.gaps[0].second;
+    for (size_t i = 0; i < g.size(); i++) {
+        const uint64_t len = p.subpatterns[i].size();
+        if (len > lo)
+            throw std::runtime_error("wcsearch3 gap semantics: subpattern " + std::to_string(i + 1) + " of '" + p.raw_regexp +
+                                     "' is longer than |P_1| + min gap (overlapping occurrences are not representable)");
+        g[i] = std::make_pair(lo - len, hi - len);
+    }
+    return g;
+}
 
 class index_b200 {
 public:
@@ -228,7 +259,7 @@ private:
                 }
                 subs.push_back(std::move(e));
             }
-            if (possible[i]) pb.add(subs, p.gaps);
+            if (possible[i]) pb.add(subs, effective_gaps(p));
         }
     }
     std::shared_ptr<vlg_b200::detail::index_handle> m_h;
@@ -259,6 +290,7 @@ inline multi_gpu_run search_batch_multi_gpu(const std::vector<uint8_t>& text, co
     for (size_t i = 0; i < pats.size(); i++) {
         std::vector<std::string> subs;
         uint64_t sp = 0;
+        const std::vector<std::pair<uint64_t, uint64_t>> gaps = effective_gaps(pats[i]);
         for (size_t j = 0; j < pats[i].subpatterns.size(); j++) {
             const string_type& s = pats[i].subpatterns[j];
             std::string e(s.size(), '\0');
@@ -266,11 +298,11 @@ inline multi_gpu_run search_batch_multi_gpu(const std::vector<uint8_t>& text, co
                 if (s[c] == 0 || s[c] > 255) possible[i] = 0;
                 e[c] = (char)s[c];
             }
-            sp += s.size() + (j < pats[i].gaps.size() ? pats[i].gaps[j].second : 0);
+            sp += s.size() + (j < gaps.size() ? gaps[j].second : 0);
             subs.push_back(std::move(e));
         }
         if (possible[i]) {
-            pb.add(subs, pats[i].gaps);
+            pb.add(subs, gaps);
             span = std::max(span, sp);
         }
     }

@@ -34,7 +34,7 @@ int main(int argc, char* const argv[])
     std::string dir, pattern_file;
     bool string_patterns = true, batch = false;
     int op, gpus = 1;
-    static const option long_opts[] = {{"gpus", required_argument, nullptr, 'g'}, {nullptr, 0, nullptr, 0}};
+    static const option long_opts[] = {{"gpus", required_argument, nullptr, 'g'}, {"wcsearch3-gaps", no_argument, nullptr, 'w'}, {nullptr, 0, nullptr, 0}};
     while ((op = getopt_long(argc, argv, "c:p:t:b:g:", long_opts, nullptr)) != -1) {
         switch (op) {
             case 'c': dir = optarg; break;
@@ -42,10 +42,11 @@ int main(int argc, char* const argv[])
             case 't': string_patterns = std::string(optarg) == "1"; break;
             case 'b': batch = std::string(optarg) == "1"; break;
             case 'g': gpus = atoi(optarg); break;
+            case 'w': gm_b200::set_gap_semantics(gm_b200::GAPS_WCSEARCH3); break;  // index_wcsearch3.hpp:412-413: gaps[0] + |P_1| for every level
         }
     }
     if (dir.empty() || pattern_file.empty()) {
-        fprintf(stdout, "%s -c <collection dir> -p <pattern file> [-t <string patterns>] [-b <one batch>]\n", argv[0]);
+        fprintf(stdout, "%s -c <collection dir> -p <pattern file> [-t <string patterns>] [-b <one batch>] [--gpus <n>] [--wcsearch3-gaps]\n", argv[0]);
         return EXIT_FAILURE;
     }
     try {
