@@ -369,18 +369,42 @@ def main():
         state["dev_ptr"] = rs[0].device_starts(0)
         rs[0].free()
 
-    def step_e2e():
+    def e2e_search(flags):
         b = capi.ParsedBatch(pattern_file, capi.SYNTAX_BENCHMARK)  # pattern-file image in host memory -> CSR batch, one ABI call
-        rs, gcounts, _ = capi.search_sharded([index], b, capi.WANT_STARTS)
+        rs, gcounts, _ = capi.search_sharded([index], b, capi.WANT_STARTS | flags)
         st = capi.last_stats()
         state["e2e_h2d"], state["e2e_d2h"] = st["h2d_bytes"], st["d2h_bytes"]
-        r = rs[0]
-        csum = 0
-        for q in (0, len(b) - 1):
-            s = r.starts(q)
-            csum += int(s[:1].sum())
         state["e2e_matches"] = int(gcounts.sum())
+        return rs[0], len(b)
+
+    def e2e_read(r, nq):
+        # the step's result is READ on the host: first start of the first and of the last query (waits for the copy)
+        return sum(int(r.starts(q)[:1].sum()) for q in (0, nq - 1))
+
+    def keep_result(r):
+        old = state.pop("e2e_result", None)
+        if old is not None:
+            old.free()
         state["e2e_result"] = r  # kept for the checksum below (read outside the timed region)
+
+    def step_e2e_serial():
+        # one call at a time: the call returns with the starts in host memory
+        r, nq = e2e_search(0)
+        e2e_read(r, nq)
+        keep_result(r)
+
+    def run_e2e_pipelined(k):
+        # a serving loop: batch i + 1 is parsed and searched while the starts of batch i travel to the host
+        # (VLGB_ASYNC_COPY); every result is read on the host before it is freed, the last one before the clock stops
+        prev = None
+        for _ in range(k):
+            r, nq = e2e_search(capi.ASYNC_COPY)
+            if prev is not None:
+                e2e_read(*prev)
+                prev[0].free()
+            prev = (r, nq)
+        e2e_read(*prev)
+        keep_result(prev[0])
 
     for _ in range(warmup):
         step_resident()
@@ -405,13 +429,16 @@ def main():
     ms_total = timed(step_resident_acc, steps)
     clocks = sampler.summary()
     checksum = num_results = None
+    ms_e2e_serial = float("nan")
     if args.no_e2e:
         ms_e2e = float("nan")
         state["e2e_h2d"] = state["e2e_d2h"] = 0
     else:
         for _ in range(warmup):
-            step_e2e()
-        ms_e2e = timed(step_e2e, steps)
+            step_e2e_serial()
+        ms_e2e_serial = timed(step_e2e_serial, steps)
+        run_e2e_pipelined(warmup)
+        ms_e2e = timed(lambda: run_e2e_pipelined(steps), 1)
         # gm_search's checksum (gm_search.cpp:110-114): sum of all match starts, here over all ranks
         r = state["e2e_result"]
         cs = 0
@@ -535,7 +562,13 @@ def main():
                            "list_path": state["stats"]["list_path"], "host_syncs_per_step": state["stats"]["host_syncs"]},
                 "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": state["e2e_h2d"],
                         "d2h_bytes_per_step": state["e2e_d2h"], "ms_per_step": ms_e2e / steps,
-                        "queries_per_s": NQ / (ms_e2e / steps * 1e-3)},
+                        "queries_per_s": NQ / (ms_e2e / steps * 1e-3),
+                        "mode": "pipelined serving loop: pattern-file image in host memory -> vlgb_parse_lines -> "
+                                "vlgb_search_sharded(WANT_STARTS | ASYNC_COPY) -> match starts in pinned host memory; the "
+                                "device-to-host copy of step i overlaps the search of step i + 1, every result is read on the "
+                                "host before it is freed, the last copy is waited for inside the timed region",
+                        "serial_ms_per_step": ms_e2e_serial / steps,
+                        "serial_note": "the same without ASYNC_COPY: one blocking call per step (latency of a single call)"},
                 "gpu_launches": launches, "index_build_ms": index_build_ms, "clocks": clocks,
                 "exchange_ms": float(np.mean(exch)) if exch else 0.0, "stage_ms_sum": stage_sum, "host_gap_ms": ms_step - stage_sum,
                 "roofline": {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -190,6 +190,11 @@ void vlgb_index_free(vlgb_index* idx);
 #define VLGB_WANT_STARTS 1u  /* + match starts         (search().positions, index_wcsearch3.hpp:418-420) */
 #define VLGB_WANT_TUPLES 2u  /* + all k positions/match (it[i],             vlg_index.hpp:337-340)        */
 #define VLGB_KEEP_ON_DEVICE 16u /* do not copy starts/tuples to the host (counts still are)            */
+#define VLGB_ASYNC_COPY 32u     /* return as soon as counts / cursors are known: the starts / tuples travel to the host on a
+                                 * second stream while the caller goes on (e.g. issues the next batch: the copy of batch i
+                                 * overlaps the search of batch i + 1).  vlgb_result_starts / _tuples / _wait / _free wait for
+                                 * the copy; everything else (counts, cursors, vlgb_result_fixup) does not.  Ignored with
+                                 * VLGB_KEEP_ON_DEVICE. */
 
 /* Run a whole batch.  entry_cursor (nullable, n_queries entries, whole-text positions): the
  * non-overlap cursor each query enters this shard with (pull_forward state, vlg_index.hpp:253-264);
@@ -209,6 +214,8 @@ const uint64_t* vlgb_result_tuples(const vlgb_result* r, uint32_t q);  /* host, 
  * for a query without matches or when not kept.  The memory belongs to the result and stays valid until
  * vlgb_result_free; it was written on vlgb_stream_handle() and the search call returns after that stream has been
  * synchronised, so any stream may read it. */
+/* Blocks until the host copies of an VLGB_ASYNC_COPY result have landed (no-op otherwise). */
+int vlgb_result_wait(const vlgb_result* r);
 const uint64_t* vlgb_result_device_starts(const vlgb_result* r, uint32_t q);
 const uint64_t* vlgb_result_device_tuples(const vlgb_result* r, uint32_t q);
 /* Non-overlap cursor each query leaves this shard with (= entry cursor of the next shard). */

@@ -351,3 +351,44 @@ def test_scan_hit_stream_paths(V):
             compare_with_oracle(V, dense, dq)     # 5 occurrences per position: every row overflows the stream
     finally:
         capi.check(capi.lib.vlgb_set_tuning(1 << 62, 0))  # back to "as much as the default rule allows"
+
+
+def test_async_copy_results_equal_blocking_results(V):
+    """VLGB_ASYNC_COPY: the call returns once counts and cursors are known, starts / tuples travel on a second stream.
+    Several searches in flight at once (the copy of batch i overlaps the search of batch i + 1) return exactly what the
+    blocking calls return; counts are readable at once; re-entry (vlgb_result_fixup) works on a result whose copy is
+    still pending; freeing without ever reading is safe."""
+    from vlg_matching_b200 import capi, synth
+    text = synth.make_text(2, 6 << 20)
+    idx = V.Index.build(text)
+    batches = [V.PackedBatch(synth.sample_queries(text, 300, k, (3, 7), [(5, 60), (100, 1000)], 500 + k, True)) for k in (2, 3, 2, 4)]
+    blocking = [idx.search(b, capi.WANT_TUPLES) for b in batches]
+    for want in (capi.WANT_STARTS, capi.WANT_TUPLES):
+        pending = [idx.search(b, want | capi.ASYNC_COPY) for b in batches]     # four results in flight
+        for r, ref in zip(pending, blocking):
+            assert np.array_equal(r.counts(), ref.counts()) and np.array_equal(r.exit_cursors(), ref.exit_cursors())
+        for r, ref, b in zip(reversed(pending), reversed(blocking), reversed(batches)):   # read in another order
+            for q in range(0, len(b), 7):
+                assert np.array_equal(r.starts(q), ref.starts(q))
+                if want == capi.WANT_TUPLES:
+                    assert np.array_equal(r.tuples(q), ref.tuples(q))
+        for r in pending:
+            r.wait()
+            r.free()
+    # never read: the blocks go back to the pools only after the copy has finished
+    for _ in range(3):
+        idx.search(batches[0], capi.WANT_STARTS | capi.ASYNC_COPY).free()
+    again = idx.search(batches[0], capi.WANT_STARTS)
+    for q in range(len(batches[0])):
+        assert np.array_equal(again.starts(q), blocking[0].starts(q))
+    # re-entry while the copy is pending: same as on a blocking result
+    ra = idx.search(batches[1], capi.WANT_STARTS | capi.ASYNC_COPY)
+    rb = idx.search(batches[1], capi.WANT_STARTS)   # (the retained state now belongs to rb: ra takes the slow path)
+    first = rb.first_starts()
+    entry = np.where(first != np.uint64(0xFFFFFFFFFFFFFFFF), first + np.uint64(1), np.uint64(0)).astype(np.uint64)
+    na, nb = ra.fixup(entry), rb.fixup(entry)
+    assert na == nb and nb > 0
+    for q in range(len(batches[1])):
+        assert np.array_equal(ra.starts(q), rb.starts(q)), q
+    assert np.array_equal(ra.counts(), rb.counts())
+    idx.free()

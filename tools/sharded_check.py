@@ -36,6 +36,17 @@ for j in range(per):
     shards.append(capi.Index.build(host, global_offset=g * n, owned_len=n, total_len=n * S))
 batch = capi.PackedBatch(queries)
 res, gcounts, st = capi.search_sharded(shards, batch, capi.WANT_STARTS)
+# the same with the result copies on the copy stream (VLGB_ASYNC_COPY): two calls in flight, re-entered queries follow
+# the first copy; must equal the blocking call
+ra1, gca, _ = capi.search_sharded(shards, batch, capi.WANT_STARTS | capi.ASYNC_COPY)
+ra2, gcb, _ = capi.search_sharded(shards, batch, capi.WANT_STARTS | capi.ASYNC_COPY)
+assert np.array_equal(gca, gcounts) and np.array_equal(gcb, gcounts)
+for j in range(per):
+    for q in range(len(queries)):
+        s0 = res[j].starts(q)
+        assert np.array_equal(ra2[j].starts(q), s0) and np.array_equal(ra1[j].starts(q), s0), (rank, j, q)
+for r in ra1 + ra2:
+    r.free()
 whole = np.concatenate([pieces[g] for g in range(S)])
 w = capi.Index.build(whole)
 rw = w.search(batch, capi.WANT_STARTS)

@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libvlgb200.so")
 OK, ERR_CUDA, ERR_ARG, ERR_LAZY, ERR_MINMAX, ERR_NUMBER, ERR_EMPTY_SUB, ERR_ZERO_SYMBOL, ERR_NOMEM, ERR_IO, \
     ERR_TOO_LARGE = 0, -1, -2, -3, -4, -5, -6, -7, -8, -9, -10
 SYNTAX_LIBRARY, SYNTAX_BENCHMARK = 0, 1
-WANT_COUNT, WANT_STARTS, WANT_TUPLES, KEEP_ON_DEVICE = 0, 1, 2, 16
+WANT_COUNT, WANT_STARTS, WANT_TUPLES, KEEP_ON_DEVICE, ASYNC_COPY = 0, 1, 2, 16, 32
 RANK_KEEP_SA, RANK_COMPACT = 0, 1
 PATH_AUTO, PATH_SCAN, PATH_RANK = 0, 1, 2
 MAX_STAGES = 16
@@ -30,7 +30,7 @@ SYMBOLS = [
     "vlgb_index_size", "vlgb_index_extract", "vlgb_index_free", "vlgb_search_batch", "vlgb_result_queries",
     "vlgb_result_status", "vlgb_result_count", "vlgb_result_total", "vlgb_result_counts", "vlgb_result_starts",
     "vlgb_result_tuples", "vlgb_result_exit_cursors", "vlgb_result_first_starts", "vlgb_result_occurrences",
-    "vlgb_result_fixup", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
+    "vlgb_result_fixup", "vlgb_result_wait", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
     "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
     "vlgb_parse_batch", "vlgb_parse_lines", "vlgb_index_attach_rank", "vlgb_index_rank_info", "vlgb_index_sa_extract", "vlgb_index_sa_extract_static",
     "vlgb_set_path", "vlgb_result_device_starts", "vlgb_result_device_tuples", "vlgb_comm_unique_id", "vlgb_comm_init",
@@ -104,6 +104,7 @@ for _f in ("vlgb_result_starts", "vlgb_result_tuples"):
 lib.vlgb_result_occurrences.argtypes = [_P, C.c_uint32]
 lib.vlgb_result_occurrences.restype = C.c_uint64
 lib.vlgb_result_fixup.argtypes = [_P, _P, C.POINTER(C.c_uint32)]
+lib.vlgb_result_wait.argtypes = [_P]
 lib.vlgb_result_free.argtypes = [_P]
 lib.vlgb_last_stats.argtypes = [C.POINTER(Stats)]
 lib.vlgb_stage_name.argtypes = [C.c_uint32]
@@ -305,6 +306,10 @@ class Result:
         if self.h and lib is not None:  # `lib` is gone during interpreter shutdown
             lib.vlgb_result_free(self.h)
         self.h = None
+
+    def wait(self):
+        """ASYNC_COPY results: block until the host lists have landed (starts() / tuples() do it implicitly)."""
+        check(lib.vlgb_result_wait(self.h))
 
     @property
     def n(self):

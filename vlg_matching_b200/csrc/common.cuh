@@ -190,6 +190,9 @@ struct Context {
     uint64_t join_budget = 0;    // 0 = default
     uint64_t serial = 0;         // searches run on this thread (validity of the state kept for vlgb_result_fixup)
     int list_path = 0;           // VLGB_PATH_AUTO / _SCAN / _RANK (vlgb_set_path)
+    cudaStream_t copy_stream = nullptr;  // result copies of VLGB_ASYNC_COPY searches (created on first use)
+    cudaEvent_t emit_done = nullptr;     // orders a copy on copy_stream behind the emit kernel on `stream`
+    bool copy_issued = false;            // the current search put something on copy_stream
 
     void begin(uint32_t stage)
     {
@@ -268,12 +271,24 @@ inline void h2d(Context& c, void* dst, const void* src, size_t bytes)
     }
     VLGB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream));
 }
+// Small results (list sizes, counts, cursors: a few KB) are WRITTEN into the pinned staging block by a kernel (the block
+// is mapped into the device's address space, unified addressing) instead of going through the copy engine: the
+// device-to-host engine serves its requests in order, and with VLGB_ASYNC_COPY the 58 MB result copy of the previous
+// search would hold up every one of these reads of the next search by up to a millisecond.
+static __global__ void small_d2h_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, uint32_t words)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < words; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
 inline void d2h(Context& c, void* host_dst, const void* dev_src, size_t bytes)  // lands in host_dst at the next sync_stream()
 {
     if (!bytes) return;
     void* p = c.stage_take(bytes);
     if (p) {
-        VLGB_CUDA(cudaMemcpyAsync(p, dev_src, bytes, cudaMemcpyDeviceToHost, c.stream));
+        if (bytes <= (64u << 10) && bytes % 4 == 0 && reinterpret_cast<uintptr_t>(dev_src) % 4 == 0) {
+            small_d2h_kernel<<<1, 256, 0, c.stream>>>(static_cast<uint32_t*>(p), static_cast<const uint32_t*>(dev_src), (uint32_t)(bytes / 4));
+        } else {
+            VLGB_CUDA(cudaMemcpyAsync(p, dev_src, bytes, cudaMemcpyDeviceToHost, c.stream));
+        }
         c.pending.push_back({host_dst, p, bytes});
     } else {
         VLGB_CUDA(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, c.stream));

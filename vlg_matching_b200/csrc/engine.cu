@@ -50,6 +50,8 @@ struct vlgb_result {
     std::vector<HostBlock> blocks;
     std::vector<DeviceBlock> dev_blocks;
     uint64_t total = 0;
+    // VLGB_ASYNC_COPY: recorded on the copy stream behind the last host copy of this result; null once waited for
+    mutable cudaEvent_t copy_done = nullptr;
 };
 
 namespace {
@@ -74,7 +76,7 @@ struct PinnedPool {
     }
     void give(HostBlock b)
     {
-        if (free_list.size() >= 8) {
+        if (free_list.size() >= 16) {  // several results in flight (VLGB_ASYNC_COPY) each hold a list block and re-entry blocks
             size_t small = 0;
             for (size_t i = 1; i < free_list.size(); i++)
                 if (free_list[i].cap < free_list[small].cap) small = i;
@@ -117,7 +119,7 @@ struct DevicePool {
     }
     void give(DeviceBlock b)
     {
-        if (free_list.size() >= 4) {
+        if (free_list.size() >= 8) {
             size_t small = 0;
             for (size_t i = 1; i < free_list.size(); i++)
                 if (free_list[i].cap < free_list[small].cap) small = i;
@@ -746,6 +748,9 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
     R.ext.first_start.assign(nq, ~uint64_t(0));
     const bool want_starts = (want & 3u) >= VLGB_WANT_STARTS, want_tuples = (want & 3u) >= VLGB_WANT_TUPLES;
     const bool keep_device = (want & VLGB_KEEP_ON_DEVICE) != 0;
+    const bool async_copy = (want & VLGB_ASYNC_COPY) != 0 && !keep_device;
+    if (!async_copy) want &= ~VLGB_ASYNC_COPY;
+    c.copy_issued = false;
     for (uint32_t q = 0; q < nq; q++) {
         R.ext.entry[q] = entry_cursor ? entry_cursor[q] : 0;
         R.exit_cursor[q] = R.ext.entry[q];
@@ -878,7 +883,8 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
                       return hb.p;
                   },
                   [&](size_t nbytes) -> void* {
-                      if (!keep_device) return c.out_buf.get(nbytes);
+                      // results that outlive the call on the device (kept there, or still being copied) own their block
+                      if (!keep_device && !async_copy) return c.out_buf.get(nbytes);
                       DeviceBlock db = device_pool().take(nbytes);
                       R.dev_blocks.push_back(db);
                       return db.p;
@@ -909,6 +915,11 @@ void do_search(Context& c, const vlgb_index* idx, const vlgb_batch* batch, const
     retained().serial = c.serial;
     R.ext.serial = c.serial;
     c.stats.segments = 1;
+    if (c.copy_issued) {  // VLGB_ASYNC_COPY: the result's host lists are complete once the copy stream passes this event
+        VLGB_CUDA(cudaEventCreateWithFlags(&R.copy_done, cudaEventDisableTiming));
+        VLGB_CUDA(cudaEventRecord(R.copy_done, c.copy_stream));
+        c.copy_issued = false;
+    }
     trace().mark("search done");
 }
 
@@ -939,6 +950,8 @@ extern "C" int vlgb_search_batch(const vlgb_index* idx, const vlgb_batch* batch,
         try {
             do_search(c, idx, batch, entry_cursor, want, *R);
         } catch (...) {
+            if (c.copy_stream) cudaStreamSynchronize(c.copy_stream);  // nothing may still be writing into the blocks
+            if (R->copy_done) cudaEventDestroy(R->copy_done);
             for (auto& b : R->blocks) pinned_pool().give(b);
             for (auto& b : R->dev_blocks) device_pool().give(b);
             throw;
@@ -958,8 +971,32 @@ extern "C" int32_t vlgb_result_status(const vlgb_result* r, uint32_t q) { return
 extern "C" uint64_t vlgb_result_count(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->counts[q] : 0; }
 extern "C" uint64_t vlgb_result_total(const vlgb_result* r) { return r ? r->total : 0; }
 extern "C" const uint64_t* vlgb_result_counts(const vlgb_result* r) { return r ? r->counts.data() : nullptr; }
-extern "C" const uint64_t* vlgb_result_starts(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->starts[q] : nullptr; }
-extern "C" const uint64_t* vlgb_result_tuples(const vlgb_result* r, uint32_t q) { return r && q < r->nq ? r->tuples[q] : nullptr; }
+// VLGB_ASYNC_COPY: the host lists may be read once the copy stream has passed the result's event
+static int wait_copies(const vlgb_result* r)
+{
+    if (!r || !r->copy_done) return VLGB_OK;
+    const cudaError_t e = cudaEventSynchronize(r->copy_done);
+    cudaEventDestroy(r->copy_done);
+    r->copy_done = nullptr;
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(VLGB_ERR_CUDA, "CUDA error %d (%s) while waiting for the result copy", (int)e, cudaGetErrorString(e));
+    }
+    return VLGB_OK;
+}
+extern "C" int vlgb_result_wait(const vlgb_result* r) { return wait_copies(r); }
+extern "C" const uint64_t* vlgb_result_starts(const vlgb_result* r, uint32_t q)
+{
+    if (!r || q >= r->nq) return nullptr;
+    if (wait_copies(r) != VLGB_OK) return nullptr;
+    return r->starts[q];
+}
+extern "C" const uint64_t* vlgb_result_tuples(const vlgb_result* r, uint32_t q)
+{
+    if (!r || q >= r->nq) return nullptr;
+    if (wait_copies(r) != VLGB_OK) return nullptr;
+    return r->tuples[q];
+}
 extern "C" const uint64_t* vlgb_result_exit_cursors(const vlgb_result* r) { return r ? r->exit_cursor.data() : nullptr; }
 extern "C" const uint64_t* vlgb_result_first_starts(const vlgb_result* r)
 {
@@ -973,6 +1010,7 @@ extern "C" const uint64_t* vlgb_result_device_tuples(const vlgb_result* r, uint3
 extern "C" void vlgb_result_free(vlgb_result* r)
 {
     if (!r) return;
+    wait_copies(r);  // the blocks go back to the pools: nothing may still be writing into them
     for (auto& b : r->blocks) pinned_pool().give(b);
     for (auto& b : r->dev_blocks) device_pool().give(b);
     delete static_cast<ResultImpl*>(r);
@@ -1027,20 +1065,30 @@ extern "C" int vlgb_result_fixup(vlgb_result* r, const uint64_t* entry_cursor, u
                 vlgb_stats keep = c.stats;
                 RefixOut ro;
                 const bool keep_dev = (R.want & VLGB_KEEP_ON_DEVICE) != 0;
+                // the re-emitted lists follow the result's first copy on the copy stream while that one is pending
+                const bool async_copy = !keep_dev && (R.want & VLGB_ASYNC_COPY) && R.copy_done;
                 static thread_local DeviceBuffer fix_out;
-                run_refix(c, T, rs, re, R.want & 3u, keep_dev,
+                c.copy_issued = false;
+                run_refix(c, T, rs, re, (R.want & 3u) | (async_copy ? VLGB_ASYNC_COPY : 0u), keep_dev,
                           [&](size_t nbytes) {
                               HostBlock hb = pinned_pool().take(nbytes ? nbytes : 8);
                               R.blocks.push_back(hb);
                               return hb.p;
                           },
                           [&](size_t nbytes) -> void* {
-                              if (!keep_dev) return fix_out.get(nbytes);
+                              if (!keep_dev && !async_copy) return fix_out.get(nbytes);
                               DeviceBlock db = device_pool().take(nbytes);
                               R.dev_blocks.push_back(db);
                               return db.p;
                           },
                           ro);
+                if (c.copy_issued) {  // one event behind everything this result has on the copy stream
+                    cudaEventDestroy(R.copy_done);
+                    R.copy_done = nullptr;
+                    VLGB_CUDA(cudaEventCreateWithFlags(&R.copy_done, cudaEventDisableTiming));
+                    VLGB_CUDA(cudaEventRecord(R.copy_done, c.copy_stream));
+                    c.copy_issued = false;
+                }
                 c.flush_timers();
                 c.stats = keep;
                 uint64_t m = 0;
@@ -1264,7 +1312,10 @@ extern "C" int vlgb_search_sharded(const vlgb_index* const* shards, uint32_t n_l
                 VLGB_CUDA(cudaMemcpyAsync(d_buf, h_buf, row_words * 8, cudaMemcpyHostToDevice, c.stream));
                 ncclResult_t nrc = api.AllGather(d_buf, d_buf + row_words, row_words, ncclUint64, cm.comm, c.stream);
                 if (nrc != ncclSuccess) return cleanup(fail(VLGB_ERR_CUDA, "ncclAllGather: %s", api.GetErrorString(nrc)));
-                VLGB_CUDA(cudaMemcpyAsync(h_buf + row_words, d_buf + row_words, G * row_words * 8, cudaMemcpyDeviceToHost, c.stream));
+                // written into the pinned buffer by a kernel: the copy engine may be busy with a result copy (VLGB_ASYNC_COPY)
+                small_d2h_kernel<<<8, 256, 0, c.stream>>>(reinterpret_cast<uint32_t*>(h_buf + row_words),
+                                                          reinterpret_cast<const uint32_t*>(d_buf + row_words), (uint32_t)(G * row_words * 2));
+                VLGB_CUDA(cudaGetLastError());
                 VLGB_CUDA(cudaStreamSynchronize(c.stream));
                 trace().mark("exchange: all-gather done (includes the wait for the slowest rank)");
                 memcpy(table.data(), h_buf + row_words, G * row_words * 8);

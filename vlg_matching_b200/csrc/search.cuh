@@ -1025,15 +1025,28 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
             if (!keep_device && (want_starts || want_tuples)) {
                 size_t hb = (want_starts ? co.matches * 8 : 0) + (want_tuples ? co.tuple_words * 8 : 0);
                 uint8_t* h = (uint8_t*)pinned_alloc(hb);
+                // VLGB_ASYNC_COPY: the lists travel on the copy stream, ordered behind the emit kernel by an event; the
+                // caller's stream is free for the next search (the device block belongs to the result, see do_search)
+                cudaStream_t cs = c.stream;
+                if (want & VLGB_ASYNC_COPY) {
+                    if (!c.copy_stream) {
+                        VLGB_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
+                        VLGB_CUDA(cudaEventCreateWithFlags(&c.emit_done, cudaEventDisableTiming));
+                    }
+                    VLGB_CUDA(cudaEventRecord(c.emit_done, c.stream));
+                    VLGB_CUDA(cudaStreamWaitEvent(c.copy_stream, c.emit_done, 0));
+                    cs = c.copy_stream;
+                    c.copy_issued = true;
+                }
                 if (want_starts) {
                     co.h_starts = (uint64_t*)h;
-                    VLGB_CUDA(cudaMemcpyAsync(h, d_starts, co.matches * 8, cudaMemcpyDeviceToHost, c.stream));
+                    VLGB_CUDA(cudaMemcpyAsync(h, d_starts, co.matches * 8, cudaMemcpyDeviceToHost, cs));
                     h += co.matches * 8;
                     c.stats.d2h_bytes += co.matches * 8;
                 }
                 if (want_tuples) {
                     co.h_tuples = (uint64_t*)h;
-                    VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, co.tuple_words * 8, cudaMemcpyDeviceToHost, c.stream));
+                    VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, co.tuple_words * 8, cudaMemcpyDeviceToHost, cs));
                     c.stats.d2h_bytes += co.tuple_words * 8;
                 }
             }
@@ -1155,15 +1168,22 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     if (!keep_device && (want_starts || want_tuples)) {
         size_t hb = (want_starts ? ro.matches * 8 : 0) + (want_tuples ? ro.tuple_words * 8 : 0);
         uint8_t* h = (uint8_t*)pinned_alloc(hb);
+        cudaStream_t cs = c.stream;
+        if ((want & VLGB_ASYNC_COPY) && c.copy_stream) {  // behind the result's first copy, which is still on its way
+            VLGB_CUDA(cudaEventRecord(c.emit_done, c.stream));
+            VLGB_CUDA(cudaStreamWaitEvent(c.copy_stream, c.emit_done, 0));
+            cs = c.copy_stream;
+            c.copy_issued = true;
+        }
         if (want_starts) {
             ro.h_starts = (uint64_t*)h;
-            VLGB_CUDA(cudaMemcpyAsync(h, d_starts, ro.matches * 8, cudaMemcpyDeviceToHost, c.stream));
+            VLGB_CUDA(cudaMemcpyAsync(h, d_starts, ro.matches * 8, cudaMemcpyDeviceToHost, cs));
             h += ro.matches * 8;
             c.stats.d2h_bytes += ro.matches * 8;
         }
         if (want_tuples) {
             ro.h_tuples = (uint64_t*)h;
-            VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, ro.tuple_words * 8, cudaMemcpyDeviceToHost, c.stream));
+            VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, ro.tuple_words * 8, cudaMemcpyDeviceToHost, cs));
             c.stats.d2h_bytes += ro.tuple_words * 8;
         }
     }
