@@ -241,6 +241,49 @@ def test_repeated_reentry_equals_fresh_search(V):
             assert np.array_equal(r.tuples(q), tup[q]), (q, queries[q])
 
 
+def test_reentry_over_many_tiles_equals_fresh_search(V):
+    """Re-entry walks tile by tile (select.cuh, sel_refix_kernel).  Periodic texts make orbits that NEVER coalesce
+    (`ab.{0,0}ab` on abab...: entered at 0 it reports 0, 4, 8, ..., entered at 2 it reports 2, 6, 10, ...), so every
+    one of the ~1500 tiles of the query changes; a cursor in the middle changes only the tiles behind it; tiles the
+    new orbit jumps over are emptied (sparse second pattern); cursors move right, left, beyond the end and back."""
+    from vlg_matching_b200 import capi
+    n = 3_200_000
+    text = np.frombuffer((b"ab" * (n // 2))[:n], dtype=np.uint8).copy()
+    text[1_000_001:1_000_400] = ord("c")            # a hole: orbits entered on either side of it differ
+    text[2_500_000:2_500_003] = np.frombuffer(b"xyz", dtype=np.uint8)
+    queries = [([b"ab", b"ab"], [(0, 0)]), ([b"a"], []), ([b"ab"], []), ([b"aba", b"b"], [(0, 2)]), ([b"b", b"xyz"], [(0, 3_000_000)]),
+               ([b"ab", b"a", b"b"], [(1, 5), (0, 8)]), ([b"c", b"ab"], [(0, 600)])]
+    idx = V.Index.build(text)
+    b = V.PackedBatch(queries)
+    nq = len(queries)
+    cursors = [np.full(nq, c, dtype=np.uint64) for c in (2, 0, 1_600_001, 3, 999_990, n + 7, 1, 1_000_200, 0)]
+    cursors.append(np.arange(nq, dtype=np.uint64) * np.uint64(333_333) + np.uint64(1))
+    r = idx.search(b, capi.WANT_STARTS)
+    for e in cursors:
+        rf = idx.search(b, capi.WANT_STARTS, entry_cursor=e)
+        want = ([rf.starts(q).copy() for q in range(nq)], rf.exit_cursors().copy(), rf.counts().copy())
+        rf.free()
+        r2 = idx.search(b, capi.WANT_STARTS)     # the retained selection state now belongs to r2 ...
+        r2.fixup(e)                              # ... which re-enters on the device (tile walk)
+        r.fixup(e)                               # and r through the general path
+        for res in (r2, r):
+            assert np.array_equal(res.counts(), want[2]), e[0]
+            assert np.array_equal(res.exit_cursors(), want[1]), e[0]
+            for q in range(nq):
+                assert np.array_equal(res.starts(q), want[0][q]), (int(e[0]), q)
+        # again on the same result, another cursor right away (the state left by the first re-entry is the old orbit now)
+        e2 = e + np.uint64(2)
+        rf = idx.search(b, capi.WANT_STARTS, entry_cursor=e2)
+        r2.fixup(e2)
+        assert np.array_equal(r2.counts(), rf.counts())
+        for q in range(nq):
+            assert np.array_equal(r2.starts(q), rf.starts(q)), (int(e2[0]), q)
+        rf.free()
+        r2.free()
+    assert idx.search(b, capi.WANT_COUNT).counts()[0] > 700_000   # ~1500 selection tiles for the first query
+    idx.free()
+
+
 @pytest.mark.parametrize("cfg", [3, 5])
 def test_large_dna_configs_vs_oracle(V, cfg):
     """Configs 3 (three subpatterns, mixed gaps, two scan passes) and 5 (occurrence lists > 10^7, several query

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -293,6 +294,16 @@ inline void d2h(Context& c, void* host_dst, const void* dev_src, size_t bytes)  
     } else {
         VLGB_CUDA(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, c.stream));
     }
+}
+// A result copy on the copy stream goes out in pieces: while ONE large device-to-host transfer is in flight, a kernel
+// writing a few KB into pinned memory (small_d2h_kernel: the next search's counts) waits 60-80 us in the median and up
+// to the whole transfer; behind pieces of 2 MB it waits ~20-30 us (idle link: 13 us; tools/microbench/d2h_contention.cu).
+inline void d2h_in_pieces(void* host_dst, const void* dev_src, size_t bytes, cudaStream_t st, bool pieces)
+{
+    const size_t piece = pieces ? (size_t)2 << 20 : bytes;
+    for (size_t o = 0; o < bytes; o += piece)
+        VLGB_CUDA(cudaMemcpyAsync(static_cast<char*>(host_dst) + o, static_cast<const char*>(dev_src) + o, std::min(piece, bytes - o),
+                                  cudaMemcpyDeviceToHost, st));
 }
 inline void sync_stream(Context& c)
 {

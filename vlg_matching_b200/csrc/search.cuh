@@ -1040,13 +1040,13 @@ inline void run_chunk(Context& c, const BatchView& v, const std::vector<PlanQuer
                 }
                 if (want_starts) {
                     co.h_starts = (uint64_t*)h;
-                    VLGB_CUDA(cudaMemcpyAsync(h, d_starts, co.matches * 8, cudaMemcpyDeviceToHost, cs));
+                    d2h_in_pieces(h, d_starts, co.matches * 8, cs, cs != c.stream);
                     h += co.matches * 8;
                     c.stats.d2h_bytes += co.matches * 8;
                 }
                 if (want_tuples) {
                     co.h_tuples = (uint64_t*)h;
-                    VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, co.tuple_words * 8, cudaMemcpyDeviceToHost, cs));
+                    d2h_in_pieces(h, d_tuples, co.tuple_words * 8, cs, cs != c.stream);
                     c.stats.d2h_bytes += co.tuple_words * 8;
                 }
             }
@@ -1105,13 +1105,16 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
     rd.q = (const uint32_t*)(fb + o_q);
     rd.entry_local = (const uint64_t*)(fb + o_e);
     rd.redo_flag = (uint32_t*)(fb + o_flag);
+    rd.dirty = S.spec;  // [tiles]; the speculative entries of the search are not needed any more
+    VLGB_CUDA(cudaMemsetAsync(S.spec, 0xFF, (size_t)T.ntiles * 4, c.stream));
     S.exit_cursor = (uint64_t*)(fb + o_exit);
     S.first_start = (uint64_t*)(fb + o_first);
     S.starts = nullptr;
     S.tuples = nullptr;
     c.begin(ST_SELECT_WALK);
-    sel_refix_kernel<<<(nr + 63) / 64, 64, 0, c.stream>>>(S, rd);
-    sel_recount_kernel<<<(T.ntiles * 32 + 255) / 256, 256, 0, c.stream>>>(S, rd.redo_flag);
+    // (one re-entered query per warp: a long tile walk does not hold up 31 short ones)
+    sel_refix_kernel<<<(nr + 3) / 4, 128, 0, c.stream>>>(S, rd);
+    sel_remark_kernel<<<(T.ntiles + MARK_WARPS - 1) / MARK_WARPS, MARK_WARPS * 32, 0, c.stream>>>(S, rd, T.ntiles);
     c.end(ST_SELECT_WALK, 2, (uint64_t)T.ntiles * 136);
     c.begin(ST_EMIT);
     uint32_t l = exclusive_scan(ValueU32{T.d_tile_count}, T.ntiles, T.d_tile_prefix, T.scratch, c.stream);
@@ -1177,13 +1180,13 @@ inline void run_refix(Context& c, Retained& T, const std::vector<uint32_t>& redo
         }
         if (want_starts) {
             ro.h_starts = (uint64_t*)h;
-            VLGB_CUDA(cudaMemcpyAsync(h, d_starts, ro.matches * 8, cudaMemcpyDeviceToHost, cs));
+            d2h_in_pieces(h, d_starts, ro.matches * 8, cs, cs != c.stream);
             h += ro.matches * 8;
             c.stats.d2h_bytes += ro.matches * 8;
         }
         if (want_tuples) {
             ro.h_tuples = (uint64_t*)h;
-            VLGB_CUDA(cudaMemcpyAsync(h, d_tuples, ro.tuple_words * 8, cudaMemcpyDeviceToHost, cs));
+            d2h_in_pieces(h, d_tuples, ro.tuple_words * 8, cs, cs != c.stream);
             c.stats.d2h_bytes += ro.tuple_words * 8;
         }
     }

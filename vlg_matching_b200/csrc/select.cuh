@@ -340,24 +340,19 @@ __global__ void sel_entry_kernel(SelDesc s)
 // warp-wide OR-reduction and one shuffle each; the successor of the segment's last orbit element enters the next
 // segment.  (Lane 0 walking the orbit alone -- one dependent shared-memory load per selected element, 3 of 32 lanes
 // active -- cost 110 M warp instructions, profiles/r02p.)
-__global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
+// The orbit of element `e` (a V_0 index inside the tile, or NONE32: nobody enters) marked in the tile's 32 flag words;
+// sc = the warp's staging block of SEL_TILE words.  All lanes of one warp; e is warp-uniform.
+__device__ __forceinline__ void sel_mark_tile(const SelDesc& s, uint32_t tile, uint32_t e, uint32_t* sc, uint32_t lane)
 {
-    __shared__ uint32_t s_succ[MARK_WARPS][SEL_TILE];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t ntiles = s.lay[1];
-    for (uint32_t tile = blockIdx.x * MARK_WARPS + warp; tile < ntiles; tile += gridDim.x * MARK_WARPS) {
-    __syncwarp();
-    const uint32_t e = s.entry[tile];
     if (e == NONE32) {  // tile not entered: no selected element (the flag words stay meaningful for re-entry)
         if (lane == 0) s.tile_count[tile] = 0;
         s.flagbits[tile * 32 + lane] = 0u;
-        continue;
+        return;
     }
     const uint32_t slot0 = tile * SEL_TILE;
     const uint32_t q = sel_query_of_tile(s, slot0);
     const uint32_t base = slot0 - s.sel_off[q];
     const uint32_t len = s.v0_len[q];
-    uint32_t* sc = s_succ[warp];
 #pragma unroll 8
     for (uint32_t i = lane; i < (uint32_t)SEL_TILE; i += 32) sc[i] = base + i < len ? s.succ[slot0 + i] : 0xFFFFFFF0u;
     __syncwarp();
@@ -383,6 +378,16 @@ __global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
     }
     s.flagbits[tile * 32 + lane] = my_bits;
     if (lane == 0) s.tile_count[tile] = cnt;
+}
+
+__global__ void __launch_bounds__(MARK_WARPS * 32) sel_mark_kernel(SelDesc s)
+{
+    __shared__ uint32_t s_succ[MARK_WARPS][SEL_TILE];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t ntiles = s.lay[1];
+    for (uint32_t tile = blockIdx.x * MARK_WARPS + warp; tile < ntiles; tile += gridDim.x * MARK_WARPS) {
+        __syncwarp();
+        sel_mark_tile(s, tile, s.entry[tile], s_succ[warp], lane);
     }
 }
 
@@ -461,53 +466,91 @@ __global__ void __launch_bounds__(EMIT_WARPS * 32) sel_emit_kernel(SelDesc s)
 }
 
 // ---- re-entry with new cursors (vlgb_result_fixup, multi-shard exactness) -----------------------------------
-// The selection state of the last chunk stays on the device: succ[] for every viable start and one flag bit
-// per start for the reported orbit.  A query that re-enters with another cursor starts its orbit at another
-// element; orbits of the monotone successor coalesce, so only the stretch before the first common element
-// changes: walk the new orbit until it meets a flagged element, clear the flags of the old orbit before that
-// point, set those of the new one.  One thread per re-entered query; the walks are a few hops long.
+// The selection state of the last chunk stays on the device: succ[] / exitp[] for every viable start and one flag bit
+// per start for the reported orbit.  A query that re-enters with another cursor starts its orbit at another element;
+// orbits of the monotone successor coalesce, so only the stretch before the first common element changes.
+//   refix  : one thread per re-entered query goes TILE BY TILE (exitp: one hop per tile of 1024 starts, where a walk
+//            along succ[] takes one dependent load per MATCH) from the tile of the earlier of the two starts: the old
+//            orbit's entry into a tile is the tile's first flagged start, the new one comes from the hops.  A tile both
+//            orbits enter at the same element ends the walk (from there on they are the same orbit); a tile they enter
+//            differently (or only one of them enters) is recorded as dirty with its new entry.
+//   remark : one warp per tile of the chunk: dirty tiles are marked afresh from their new entry (sel_mark_tile), the
+//            other tiles of re-entered queries are recounted from their flag words, all other tiles count 0, so that
+//            the prefix scan + emit kernels produce exactly the re-entered queries' matches, back to back.
 struct RefixDesc {
     uint32_t n;                  // queries that re-enter
     const uint32_t* q;           // [n] their index in the chunk
     const uint64_t* entry_local; // [n] new cursor relative to the shard start (bytes, saturated at 0)
     uint32_t* redo_flag;         // [nq] set for re-entered queries
+    uint32_t* dirty;             // [tiles] NONE32 = as it was; REFIX_EMPTY = no orbit element any more; else the new entry
 };
-
-__device__ __forceinline__ bool sel_flag_get(const uint32_t* fb, uint32_t slot) { return (fb[slot >> 5] >> (slot & 31)) & 1u; }
+constexpr uint32_t REFIX_EMPTY = 0xFFFFFFFEu;
 
 __global__ void sel_refix_kernel(SelDesc s, RefixDesc r)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= r.n) return;
+    // one query per WARP (lane 0 works): 32 walks of different lengths in one warp would run at the pace of the longest
+    const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (i >= r.n || (threadIdx.x & 31u)) return;
     const uint32_t q = r.q[i];
     r.redo_flag[q] = 1u;
     const uint32_t len = s.v0_len[q], off = s.sel_off[q];
     const uint32_t t_old = s.t0[q];
     const uint32_t t_new = full_lower_bound(s.v0[q], len, r.entry_local[i]);
     s.t0[q] = t_new;
-    // flag words are laid out [tile][warp] = one bit per slot in slot order, i.e. bit (slot & 31) of word slot >> 5
-    uint32_t* fb = s.flagbits;
-    uint32_t meet = t_new;  // first element of the new orbit that the old orbit reports too (or len)
-    while (meet < len && !sel_flag_get(fb, off + meet)) meet = s.succ[off + meet];
-    for (uint32_t u = t_old; u < len && u < meet; u = s.succ[off + u]) fb[(off + u) >> 5] &= ~(1u << ((off + u) & 31));
-    // an old orbit that started right of `meet` (the cursor moved left) is wholly kept: it is the tail of the new one
-    for (uint32_t m = t_new; m < len && m < meet; m = s.succ[off + m]) fb[(off + m) >> 5] |= 1u << ((off + m) & 31);
+    const uint32_t first_el = min(t_old, t_new);
+    if (first_el >= len) return;  // neither orbit has an element
+    const uint32_t tile0 = off / SEL_TILE, ntq = (len + SEL_TILE - 1) / SEL_TILE;
+    uint32_t cur = t_new;
+    for (uint32_t t = first_el / SEL_TILE; t < ntq; t++) {
+        const uint32_t gt = tile0 + t;
+        // independent loads: the tile's flag words and the hop out of the tile
+        const bool here = cur < len && cur / SEL_TILE == t;
+        const uint32_t nxt = here ? s.exitp[off + cur] : 0u;
+        const uint4* fw = reinterpret_cast<const uint4*>(s.flagbits + (size_t)gt * 32);
+        uint32_t old = NONE32;
+#pragma unroll
+        for (int w4 = 7; w4 >= 0; w4--) {
+            const uint4 v = fw[w4];
+            if (v.w) old = t * SEL_TILE + (w4 * 4 + 3) * 32 + (__ffs(v.w) - 1);
+            if (v.z) old = t * SEL_TILE + (w4 * 4 + 2) * 32 + (__ffs(v.z) - 1);
+            if (v.y) old = t * SEL_TILE + (w4 * 4 + 1) * 32 + (__ffs(v.y) - 1);
+            if (v.x) old = t * SEL_TILE + (w4 * 4 + 0) * 32 + (__ffs(v.x) - 1);
+        }
+        const uint32_t now = here ? cur : NONE32;
+        if (now == old) {
+            if (now != NONE32) break;  // both orbits enter the tile at the same element: identical from here on
+        } else {
+            r.dirty[gt] = here ? cur : REFIX_EMPTY;
+        }
+        if (here) cur = nxt;
+    }
 }
 
-// tile_count / entry from the flag words, for the re-entered queries only (all other tiles count 0, so that the
-// prefix scan + emit kernels produce exactly the re-entered queries' matches, back to back)
-__global__ void sel_recount_kernel(SelDesc s, const uint32_t* redo_flag)
+__global__ void __launch_bounds__(MARK_WARPS * 32) sel_remark_kernel(SelDesc s, RefixDesc r, uint32_t ntiles)
 {
-    const uint32_t tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (tile >= s.lay[1]) return;
+    __shared__ uint32_t s_succ[MARK_WARPS][SEL_TILE];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tile = blockIdx.x * MARK_WARPS + warp;
+    if (tile >= ntiles) return;
     const uint32_t q = sel_query_of_tile(s, tile * SEL_TILE);
-    uint32_t c = 0;
-    if (redo_flag[q]) c = __popc(s.flagbits[tile * 32 + lane]);
-    c = __reduce_add_sync(0xffffffffu, c);
-    if (lane == 0) {
-        s.tile_count[tile] = c;
-        s.entry[tile] = c ? 0u : NONE32;
+    const uint32_t d = r.dirty[tile];
+    if (!r.redo_flag[q]) {  // warp-uniform
+        if (lane == 0) {
+            s.tile_count[tile] = 0;
+            s.entry[tile] = NONE32;
+        }
+        return;
     }
+    uint32_t c;
+    if (d == NONE32) {
+        c = __reduce_add_sync(0xffffffffu, __popc(s.flagbits[tile * 32 + lane]));
+        if (lane == 0) s.tile_count[tile] = c;
+    } else {
+        sel_mark_tile(s, tile, d == REFIX_EMPTY ? NONE32 : d, s_succ[warp], lane);
+        __syncwarp();
+        c = __shfl_sync(0xffffffffu, lane == 0 ? s.tile_count[tile] : 0u, 0);
+    }
+    if (lane == 0) s.entry[tile] = c ? 0u : NONE32;  // emit skips tiles without a selected element
 }
 
 }  // namespace vlgb
