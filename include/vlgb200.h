@@ -286,6 +286,10 @@ typedef struct {
     uint32_t host_syncs;                /* host<->device synchronisations inside the call */
 } vlgb_stats;
 int vlgb_last_stats(vlgb_stats* out);
+/* The per-stage device times cost two CUDA event records per stage and one stream synchronisation + ~30 event queries
+ * per search (~0.05-0.1 ms of host time).  on = 0 switches them off for the calling thread (ms[] then stays 0; bytes,
+ * launches and the counters are still filled); default: on. */
+int vlgb_set_stage_timing(int on);
 const char* vlgb_stage_name(uint32_t stage);
 /* The CUDA stream (cudaStream_t) every kernel of the calling thread is launched on, for callers that
  * bracket calls with their own CUDA events.  NULL before the first device call. */

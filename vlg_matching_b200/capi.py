@@ -30,7 +30,7 @@ SYMBOLS = [
     "vlgb_index_size", "vlgb_index_extract", "vlgb_index_free", "vlgb_search_batch", "vlgb_result_queries",
     "vlgb_result_status", "vlgb_result_count", "vlgb_result_total", "vlgb_result_counts", "vlgb_result_starts",
     "vlgb_result_tuples", "vlgb_result_exit_cursors", "vlgb_result_first_starts", "vlgb_result_occurrences",
-    "vlgb_result_fixup", "vlgb_result_wait", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning",
+    "vlgb_result_fixup", "vlgb_result_wait", "vlgb_result_free", "vlgb_last_stats", "vlgb_stage_name", "vlgb_set_tuning", "vlgb_set_stage_timing",
     "vlgb_stream_handle", "vlgb_index_build_symbols", "vlgb_index_symbol_width", "vlgb_encode_symbols",
     "vlgb_parse_batch", "vlgb_parse_lines", "vlgb_index_attach_rank", "vlgb_index_rank_info", "vlgb_index_sa_extract", "vlgb_index_sa_extract_static",
     "vlgb_set_path", "vlgb_result_device_starts", "vlgb_result_device_tuples", "vlgb_comm_unique_id", "vlgb_comm_init",
@@ -110,6 +110,7 @@ lib.vlgb_last_stats.argtypes = [C.POINTER(Stats)]
 lib.vlgb_stage_name.argtypes = [C.c_uint32]
 lib.vlgb_stage_name.restype = C.c_char_p
 lib.vlgb_set_tuning.argtypes = [C.c_uint64, C.c_uint64]
+lib.vlgb_set_stage_timing.argtypes = [C.c_int]
 lib.vlgb_stream_handle.restype = C.c_void_p
 lib.vlgb_index_build_symbols.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_P)]
 lib.vlgb_index_symbol_width.argtypes = [_P]

@@ -195,8 +195,10 @@ struct Context {
     cudaEvent_t emit_done = nullptr;     // orders a copy on copy_stream behind the emit kernel on `stream`
     bool copy_issued = false;            // the current search put something on copy_stream
 
+    bool stage_timing = true;    // vlgb_set_stage_timing: CUDA events around every stage (vlgb_last_stats().ms)
     void begin(uint32_t stage)
     {
+        if (!stage_timing) return;
         if (!ev_ready) {
             for (auto& e : ev) cudaEventCreate(&e);
             ev_ready = true;
@@ -208,7 +210,7 @@ struct Context {
     }
     void end(uint32_t stage, uint32_t launches, uint64_t bytes)
     {
-        cudaEventRecord(ev[spans.back().e1], stream);
+        if (stage_timing) cudaEventRecord(ev[spans.back().e1], stream);
         stats.launches[stage] += launches;
         stats.bytes[stage] += bytes;
     }

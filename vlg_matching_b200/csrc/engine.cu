@@ -662,6 +662,14 @@ extern "C" int vlgb_index_frequent_phrases(const vlgb_index* idx, uint32_t lengt
     }
 }
 
+extern "C" int vlgb_set_stage_timing(int on)
+{
+    Context& c = ctx();
+    if (c.ready) c.flush_timers();
+    c.stage_timing = on != 0;
+    return VLGB_OK;
+}
+
 extern "C" int vlgb_set_path(int path)
 {
     if (path != VLGB_PATH_AUTO && path != VLGB_PATH_SCAN && path != VLGB_PATH_RANK) return fail(VLGB_ERR_ARG, "vlgb_set_path: unknown path %d", path);
