@@ -376,9 +376,7 @@ def main():
         if b is None:
             b = parse_batch()
         rs, gcounts, _ = capi.search_sharded([index], b, capi.WANT_STARTS | flags)
-        st = capi.last_stats()
-        state["e2e_h2d"], state["e2e_d2h"] = st["h2d_bytes"], st["d2h_bytes"]
-        state["e2e_matches"] = int(gcounts.sum())
+        state["e2e_gcounts"] = gcounts
         return rs[0], len(b)
 
     from concurrent.futures import ThreadPoolExecutor
@@ -459,6 +457,9 @@ def main():
         ms_e2e_serial = timed(step_e2e_serial, steps)
         run_e2e_pipelined(warmup)
         ms_e2e = timed(lambda: run_e2e_pipelined(steps), 1)
+        st = capi.last_stats()  # byte counters of the last search of the loop (the library counts what it copies)
+        state["e2e_h2d"], state["e2e_d2h"] = st["h2d_bytes"], st["d2h_bytes"]
+        state["e2e_matches"] = int(state["e2e_gcounts"].sum())
         # gm_search's checksum (gm_search.cpp:110-114): sum of all match starts, here over all ranks
         r = state["e2e_result"]
         cs = 0
