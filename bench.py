@@ -152,12 +152,13 @@ class ClockSampler(threading.Thread):
 
 
 def kernel_source_hash() -> str:
-    """sha256 over the CUDA sources: profiles/traffic.json records it, so that DRAM traffic captured for other kernels is
-    not reported beside this run's times (tools/make_profiles.py writes the same hash)."""
+    """sha256 over the kernel sources (csrc/*.cuh: every kernel of the search path lives in a header; engine.cu is the host
+    side of the ABI): profiles/traffic.json records it, so that DRAM traffic captured for other kernels is not reported
+    beside this run's times (tools/make_profiles.py writes the same hash)."""
     d = os.path.join(ROOT, "vlg_matching_b200", "csrc")
     h = hashlib.sha256()
     for f in sorted(os.listdir(d)):
-        if f.endswith((".cu", ".cuh", ".hpp")):
+        if f.endswith(".cuh"):
             h.update(f.encode())
             h.update(open(os.path.join(d, f), "rb").read())
     return h.hexdigest()[:16]
@@ -283,6 +284,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg")
     ap.add_argument("--no-config4", action="store_true", help="skip the 8 GiB / 10 000-query block")
+    ap.add_argument("--keep-stage-timing", action="store_true", help="debug: leave the library's per-stage CUDA events on everywhere")
     ap.add_argument("--no-rank-path", action="store_true", help="skip the rare-pattern latency block")
     ap.add_argument("--shard-bytes", type=int, default=SHARD_BYTES, help="debug only: smaller shard")
     args = ap.parse_args()
@@ -441,7 +443,7 @@ def main():
     ms_total_staged = timed(step_resident_acc, steps)
     # pass 2, the same loop with the per-stage events OFF (vlgb_set_stage_timing: ~50 event records and one extra stream
     # synchronisation per search are measurement, not search): `value` / `ms_per_step` come from this one
-    capi.check(capi.lib.vlgb_set_stage_timing(0))
+    capi.check(capi.lib.vlgb_set_stage_timing(1 if args.keep_stage_timing else 0))
     for _ in range(2):
         step_resident()
     ms_total = timed(step_resident, steps)
@@ -529,6 +531,7 @@ def main():
                 r.free()
 
         step4()  # warm-up (arena growth)
+        step4()  # and once more: the pools of result blocks settle in the second pass
         k4 = 2
         ms4 = timed(step4, k4) / k4
         # checksum of all match starts: one more pass with the starts in host memory

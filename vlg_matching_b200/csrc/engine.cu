@@ -58,13 +58,16 @@ namespace {
 
 // pinned blocks are recycled across results (cudaHostAlloc is slow)
 struct PinnedPool {
+    static constexpr size_t PINNED_POOL_BLOCKS = 16;
     std::vector<HostBlock> free_list;
     HostBlock take(size_t bytes)
     {
         size_t best = SIZE_MAX;
         for (size_t i = 0; i < free_list.size(); i++)
             if (free_list[i].cap >= bytes && (best == SIZE_MAX || free_list[i].cap < free_list[best].cap)) best = i;
-        if (best != SIZE_MAX && free_list[best].cap <= 4 * bytes + (1u << 20)) {
+        // a much larger block is left for a larger request -- unless the pool is full: allocating would then end in a
+        // cudaFreeHost when the block comes back, on every call (a small batch after a large one: 100 ms per search)
+        if (best != SIZE_MAX && (free_list[best].cap <= 4 * bytes + (1u << 20) || free_list.size() >= PINNED_POOL_BLOCKS)) {
             HostBlock b = free_list[best];
             free_list.erase(free_list.begin() + best);
             return b;
@@ -76,7 +79,7 @@ struct PinnedPool {
     }
     void give(HostBlock b)
     {
-        if (free_list.size() >= 16) {  // several results in flight (VLGB_ASYNC_COPY) each hold a list block and re-entry blocks
+        if (free_list.size() >= PINNED_POOL_BLOCKS) {  // several results in flight (VLGB_ASYNC_COPY) each hold a list block and re-entry blocks
             size_t small = 0;
             for (size_t i = 1; i < free_list.size(); i++)
                 if (free_list[i].cap < free_list[small].cap) small = i;
@@ -95,13 +98,14 @@ PinnedPool& pinned_pool()
 
 // device result blocks are recycled the same way (cudaMalloc / cudaFree synchronise the device)
 struct DevicePool {
+    static constexpr size_t DEVICE_POOL_BLOCKS = 8;
     std::vector<DeviceBlock> free_list;
     DeviceBlock take(size_t bytes)
     {
         size_t best = SIZE_MAX;
         for (size_t i = 0; i < free_list.size(); i++)
             if (free_list[i].cap >= bytes && (best == SIZE_MAX || free_list[i].cap < free_list[best].cap)) best = i;
-        if (best != SIZE_MAX && free_list[best].cap <= 4 * bytes + (1u << 20)) {
+        if (best != SIZE_MAX && (free_list[best].cap <= 4 * bytes + (1u << 20) || free_list.size() >= DEVICE_POOL_BLOCKS)) {  // as above
             DeviceBlock b = free_list[best];
             free_list.erase(free_list.begin() + best);
             return b;
@@ -119,7 +123,7 @@ struct DevicePool {
     }
     void give(DeviceBlock b)
     {
-        if (free_list.size() >= 8) {
+        if (free_list.size() >= DEVICE_POOL_BLOCKS) {
             size_t small = 0;
             for (size_t i = 1; i < free_list.size(); i++)
                 if (free_list[i].cap < free_list[small].cap) small = i;
